@@ -1,0 +1,867 @@
+// C-ABI implementation: stage executor (op program -> kernel launches -> CUDA graph),
+// single-layer entry point, and hand-off plumbing.  See include/adapt_b200.h.
+#include "../../include/adapt_b200.h"
+
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "conv_gemm_sm100.cuh"
+#include "simt_kernels.cuh"
+
+namespace {
+
+thread_local std::string g_last_error;
+
+int fail(int code, const char* fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_last_error = buf;
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                                     \
+    do {                                                                                                   \
+        cudaError_t _e = (expr);                                                                           \
+        if (_e != cudaSuccess)                                                                             \
+            return fail(_e == cudaErrorMemoryAllocation ? ADAPT_ENOMEM : ADAPT_ECUDA, "%s failed: %s (%s:%d)", \
+                        #expr, cudaGetErrorString(_e), __FILE__, __LINE__);                                \
+    } while (0)
+
+// ---------------------------------------------------------------- driver entry points
+// libcuda is resolved at run time through the runtime so that the library still dlopen()s
+// (and exports its symbols) on a machine without a driver.
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+typedef CUresult (*PFN_encodeIm2col)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                     const cuuint64_t*, const int*, const int*, cuuint32_t, cuuint32_t,
+                                     const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                     CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+typedef CUresult (*PFN_streamWriteValue32)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+typedef CUresult (*PFN_streamWaitValue32)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+
+struct DriverApi {
+    PFN_encodeTiled encodeTiled = nullptr;
+    PFN_encodeIm2col encodeIm2col = nullptr;
+    PFN_streamWriteValue32 writeValue32 = nullptr;
+    PFN_streamWaitValue32 waitValue32 = nullptr;
+    int driver_version = 0;
+    bool ok = false;
+};
+
+int get_driver(DriverApi** out) {
+    static DriverApi api;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        cudaDriverEntryPointQueryResult q;
+        void* fn = nullptr;
+        bool good = true;
+        auto load = [&](const char* name, void** dst) {
+            fn = nullptr;
+            cudaError_t e = cudaGetDriverEntryPoint(name, &fn, cudaEnableDefault, &q);
+            if (e != cudaSuccess || fn == nullptr || q != cudaDriverEntryPointSuccess) {
+                good = false;
+                cudaGetLastError();
+            } else {
+                *dst = fn;
+            }
+        };
+        load("cuTensorMapEncodeTiled", reinterpret_cast<void**>(&api.encodeTiled));
+        load("cuTensorMapEncodeIm2col", reinterpret_cast<void**>(&api.encodeIm2col));
+        load("cuStreamWriteValue32", reinterpret_cast<void**>(&api.writeValue32));
+        load("cuStreamWaitValue32", reinterpret_cast<void**>(&api.waitValue32));
+        cudaDriverGetVersion(&api.driver_version);
+        api.ok = good;
+    }
+    if (!api.ok) return fail(ADAPT_ENODEV, "CUDA driver entry points unavailable (no GPU / no driver)");
+    *out = &api;
+    return ADAPT_OK;
+}
+
+int require_device(int device) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        return fail(ADAPT_ENODEV, "no CUDA device visible (this library has no CPU fallback)");
+    }
+    if (device < 0 || device >= n) return fail(ADAPT_EINVAL, "device %d out of range (count %d)", device, n);
+    CUDA_TRY(cudaSetDevice(device));
+    return ADAPT_OK;
+}
+
+// ---------------------------------------------------------------- tensor maps
+int encode_tiled_2d_bf16(CUtensorMap* m, const void* base, uint64_t inner, uint64_t rows, uint32_t box_inner,
+                         uint32_t box_rows) {
+    DriverApi* d;
+    int rc = get_driver(&d);
+    if (rc) return rc;
+    cuuint64_t dims[2] = {inner, rows};
+    cuuint64_t strides[1] = {inner * 2};
+    cuuint32_t box[2] = {box_inner, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = d->encodeTiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box,
+                                estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return fail(ADAPT_ECUDA, "cuTensorMapEncodeTiled failed (%d) inner=%llu rows=%llu box=%ux%u base=%p", (int)r,
+                    (unsigned long long)inner, (unsigned long long)rows, box_inner, box_rows, base);
+    return ADAPT_OK;
+}
+
+// NHWC activation tensor described as (C, W, H, N) for im2col-mode loads of a
+// kh x kw / stride / symmetric-pad convolution; one load = 128 output pixels x 64 channels.
+int encode_im2col_bf16(CUtensorMap* m, const void* base, int C, int W, int H, int N, int kh, int kw, int stride,
+                       int pad) {
+    DriverApi* d;
+    int rc = get_driver(&d);
+    if (rc) return rc;
+    cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+    cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+    int lower[2] = {-pad, -pad};
+    int upper[2] = {pad - (kw - 1), pad - (kh - 1)};
+    cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+    CUresult r = d->encodeIm2col(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides,
+                                 lower, upper, /*channelsPerPixel=*/adapt::kBlockK, /*pixelsPerColumn=*/adapt::kBlockM,
+                                 estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return fail(ADAPT_ECUDA, "cuTensorMapEncodeIm2col failed (%d) C=%d W=%d H=%d N=%d k=%dx%d s=%d p=%d", (int)r, C,
+                    W, H, N, kh, kw, stride, pad);
+    // Known driver issue (also worked around by CUTLASS): for tensors smaller than 128 KiB
+    // older drivers set a descriptor bit that makes im2col loads fault; clear it.
+    if (d->driver_version <= 13010) {
+        const uint64_t bytes = (uint64_t)C * W * H * N * 2;
+        if (bytes < 131072) reinterpret_cast<uint64_t*>(m)[1] &= ~(1ull << 21);
+    }
+    return ADAPT_OK;
+}
+
+// ---------------------------------------------------------------- conv launch records
+struct ConvGeom {
+    int batch, H, W, Cin, Ho, Wo, Cout, kh, kw, stride, pad;
+};
+
+struct ConvLaunch {
+    CUtensorMap tmap_a;
+    CUtensorMap tmap_b;
+    adapt::ConvGemmParams p;
+    int block_n = 0;
+    int a_mode = 0;
+    int grid = 0;
+};
+
+int g_force_a_mode = -2;  // -2 = read env lazily
+int g_force_block_n = -2;
+
+int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
+
+int pick_block_n(int m_tiles, int N, int num_sms) {
+    const int cands[3] = {256, 128, 64};
+    const float penalty[3] = {1.0f, 1.1f, 1.5f};  // narrower tiles re-read A from smem more often
+    int best = 64;
+    float best_cost = 1e30f;
+    for (int i = 0; i < 3; ++i) {
+        const int bn = cands[i];
+        if (bn > 64 && N < bn) continue;
+        const int n_tiles = (N + bn - 1) / bn;
+        // do not waste more than ~12% of the MMA columns on padding
+        if ((float)(n_tiles * bn - N) > 0.125f * (float)N && bn > 64) continue;
+        const int tiles = m_tiles * n_tiles;
+        const int waves = (tiles + num_sms - 1) / num_sms;
+        const float cost = (float)waves * (float)bn * penalty[i];
+        if (cost < best_cost) {
+            best_cost = cost;
+            best = bn;
+        }
+    }
+    return best;
+}
+
+template <int BN, int MODE>
+int set_smem_attr() {
+    CUDA_TRY(cudaFuncSetAttribute(adapt::conv_gemm_kernel<BN, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  adapt::ConvGemmCfg<BN>::kSmemBytes));
+    return ADAPT_OK;
+}
+
+int init_conv_kernels_for_device() {
+    int rc;
+#define SET(BN, MODE)                        \
+    rc = set_smem_attr<BN, adapt::MODE>();   \
+    if (rc) return rc;
+    SET(64, A_TILED) SET(128, A_TILED) SET(256, A_TILED)
+    SET(64, A_IM2COL) SET(128, A_IM2COL) SET(256, A_IM2COL)
+    SET(64, A_GATHER) SET(128, A_GATHER) SET(256, A_GATHER)
+#undef SET
+    return ADAPT_OK;
+}
+
+// Build the launch record (tensor maps + params) for one convolution.
+int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const void* w_bf16, const float* scale,
+                      const float* bias, const void* residual, void* out, bool out_f32, int relu, int a_mode_req,
+                      int block_n_req, int num_sms) {
+    if (g.Cin % 8 != 0) return fail(ADAPT_EINVAL, "conv: stored Cin=%d must be a multiple of 8", g.Cin);
+    if (g.Cout % 8 != 0) return fail(ADAPT_EINVAL, "conv: Cout=%d must be a multiple of 8", g.Cout);
+    if (g_force_a_mode == -2) g_force_a_mode = env_int("ADAPT_FORCE_A_MODE", -1);
+    if (g_force_block_n == -2) g_force_block_n = env_int("ADAPT_FORCE_BLOCK_N", 0);
+    const int K = g.kh * g.kw * g.Cin;
+    const long long M = (long long)g.batch * g.Ho * g.Wo;
+    if (M <= 0 || M > 0x7fffffffLL) return fail(ADAPT_EINVAL, "conv: bad M=%lld", M);
+
+    int a_mode = a_mode_req >= 0 ? a_mode_req : g_force_a_mode;
+    const bool plain = g.kh == 1 && g.kw == 1 && g.stride == 1 && g.pad == 0;
+    if (a_mode < 0) {
+        if (g.Cin % 64 != 0)
+            a_mode = adapt::A_GATHER;
+        else if (plain)
+            a_mode = adapt::A_TILED;
+        else
+            a_mode = adapt::A_IM2COL;
+    }
+    if (a_mode == adapt::A_TILED && !plain) a_mode = adapt::A_IM2COL;
+    if (a_mode != adapt::A_GATHER && g.Cin % 64 != 0) a_mode = adapt::A_GATHER;
+
+    adapt::ConvGemmParams& p = L->p;
+    memset(&p, 0, sizeof(p));
+    p.M = (int)M;
+    p.N = g.Cout;
+    p.num_k_blocks = (K + adapt::kBlockK - 1) / adapt::kBlockK;
+    p.m_tiles = (int)((M + adapt::kBlockM - 1) / adapt::kBlockM);
+    int bn = block_n_req > 0 ? block_n_req : (g_force_block_n > 0 ? g_force_block_n : 0);
+    if (bn == 0) bn = pick_block_n(p.m_tiles, g.Cout, num_sms);
+    if (bn != 64 && bn != 128 && bn != 256) return fail(ADAPT_EINVAL, "conv: block_n=%d unsupported", bn);
+    p.n_tiles = (g.Cout + bn - 1) / bn;
+    p.H = g.H; p.W = g.W; p.Cin = g.Cin; p.Ho = g.Ho; p.Wo = g.Wo;
+    p.kh = g.kh; p.kw = g.kw; p.stride = g.stride; p.pad = g.pad;
+    p.c_blocks = g.Cin / adapt::kBlockK;
+    p.K_real = K;
+    p.scale = scale;
+    p.bias = bias;
+    p.residual = reinterpret_cast<const __nv_bfloat16*>(residual);
+    p.out_bf16 = out_f32 ? nullptr : reinterpret_cast<__nv_bfloat16*>(out);
+    p.out_f32 = out_f32 ? reinterpret_cast<float*>(out) : nullptr;
+    p.relu = relu;
+    p.in = reinterpret_cast<const __nv_bfloat16*>(in);
+    L->block_n = bn;
+    L->a_mode = a_mode;
+    const int tiles = p.m_tiles * p.n_tiles;
+    L->grid = tiles < num_sms ? tiles : num_sms;
+
+    int rc = encode_tiled_2d_bf16(&L->tmap_b, w_bf16, (uint64_t)K, (uint64_t)g.Cout, adapt::kBlockK, (uint32_t)bn);
+    if (rc) return rc;
+    if (a_mode == adapt::A_TILED) {
+        rc = encode_tiled_2d_bf16(&L->tmap_a, in, (uint64_t)g.Cin, (uint64_t)M, adapt::kBlockK, adapt::kBlockM);
+        if (rc) return rc;
+    } else if (a_mode == adapt::A_IM2COL) {
+        rc = encode_im2col_bf16(&L->tmap_a, in, g.Cin, g.W, g.H, g.batch, g.kh, g.kw, g.stride, g.pad);
+        if (rc) return rc;
+    } else {
+        L->tmap_a = L->tmap_b;  // unused by the gather kernel
+    }
+    return ADAPT_OK;
+}
+
+template <int BN>
+void launch_conv_bn(const ConvLaunch& L, cudaStream_t s) {
+    using Cfg = adapt::ConvGemmCfg<BN>;
+    switch (L.a_mode) {
+        case adapt::A_TILED:
+            adapt::conv_gemm_kernel<BN, adapt::A_TILED><<<L.grid, 192, Cfg::kSmemBytes, s>>>(L.tmap_a, L.tmap_b, L.p);
+            break;
+        case adapt::A_IM2COL:
+            adapt::conv_gemm_kernel<BN, adapt::A_IM2COL><<<L.grid, 192, Cfg::kSmemBytes, s>>>(L.tmap_a, L.tmap_b, L.p);
+            break;
+        default:
+            adapt::conv_gemm_kernel<BN, adapt::A_GATHER><<<L.grid, 320, Cfg::kSmemBytes, s>>>(L.tmap_a, L.tmap_b, L.p);
+            break;
+    }
+}
+
+int run_conv_launch(const ConvLaunch& L, cudaStream_t s) {
+    if (L.block_n == 64)
+        launch_conv_bn<64>(L, s);
+    else if (L.block_n == 128)
+        launch_conv_bn<128>(L, s);
+    else
+        launch_conv_bn<256>(L, s);
+    CUDA_TRY(cudaGetLastError());
+    return ADAPT_OK;
+}
+
+// ---------------------------------------------------------------- stage
+struct WeightDev {
+    int kh = 0, kw = 0, cin = 0, cin_store = 0, cout = 0;
+    void* kernel = nullptr;  // bf16 [cout][kh][kw][cin_store]  or  fp32 HWIO in check mode
+    float* scale = nullptr;
+    float* bias = nullptr;
+};
+
+struct Step {
+    int kind = 0;
+    ConvLaunch conv;  // bf16 CONV
+    // generic pointers / geometry for the SIMT kernels
+    const void* in = nullptr;
+    const void* res = nullptr;
+    void* out = nullptr;
+    adapt_op_desc op;
+    int batch = 0;
+};
+
+struct Plan {
+    int batch = 0;
+    std::vector<Step> steps[2];
+    bool built[2] = {false, false};
+    cudaGraphExec_t exec[2] = {nullptr, nullptr};
+};
+
+}  // namespace
+
+struct adapt_stage {
+    int device = 0;
+    int mode = 0;
+    int max_batch = 0;
+    int num_sms = 0;
+    bool use_graph = true;
+    std::vector<WeightDev> weights;
+    std::vector<adapt_tensor_desc> tdesc;
+    std::vector<void*> tptr;
+    std::vector<adapt_op_desc> ops;
+    void* io_in[2] = {nullptr, nullptr};
+    void* io_out[2] = {nullptr, nullptr};
+    std::map<int, std::unique_ptr<Plan>> plans;
+};
+
+namespace {
+
+size_t elem_size(const adapt_stage* st, int dtype) {
+    if (dtype == ADAPT_DT_F32) return 4;
+    return st->mode == ADAPT_MODE_BF16 ? 2 : 4;
+}
+
+void drop_plans(adapt_stage* st) {
+    for (auto& kv : st->plans)
+        for (int s = 0; s < 2; ++s)
+            if (kv.second->exec[s]) cudaGraphExecDestroy(kv.second->exec[s]);
+    st->plans.clear();
+}
+
+void free_tensors(adapt_stage* st) {
+    for (void* p : st->tptr)
+        if (p) cudaFree(p);
+    st->tptr.clear();
+    st->tdesc.clear();
+}
+
+int install_program(adapt_stage* st, const adapt_tensor_desc* tensors, int n_tensors, const adapt_op_desc* ops,
+                    int n_ops) {
+    if (n_tensors <= 0 || n_ops <= 0 || !tensors || !ops) return fail(ADAPT_EINVAL, "empty stage program");
+    // validate before touching state
+    int n_in = 0, n_out = 0;
+    for (int i = 0; i < n_tensors; ++i) {
+        if (tensors[i].elems_per_image <= 0) return fail(ADAPT_EINVAL, "tensor %d: bad size", i);
+        if (tensors[i].role == ADAPT_T_INPUT) ++n_in;
+        if (tensors[i].role == ADAPT_T_OUTPUT) ++n_out;
+    }
+    if (n_in != 1 || n_out != 1) return fail(ADAPT_EINVAL, "program needs exactly one INPUT and one OUTPUT tensor");
+    for (int i = 0; i < n_ops; ++i) {
+        const adapt_op_desc& o = ops[i];
+        auto bad_t = [&](int t, bool optional) { return !(optional && t == -1) && (t < 0 || t >= n_tensors); };
+        if (bad_t(o.in_tensor, false) || bad_t(o.out_tensor, false) || bad_t(o.res_tensor, true))
+            return fail(ADAPT_EINVAL, "op %d: tensor index out of range", i);
+        if (o.kind == ADAPT_OP_CONV) {
+            if (o.weight < 0 || o.weight >= (int)st->weights.size())
+                return fail(ADAPT_EINVAL, "op %d: weight index %d out of range", i, o.weight);
+            const WeightDev& w = st->weights[o.weight];
+            const int cin_expect = st->mode == ADAPT_MODE_BF16 ? w.cin_store : w.cin;
+            if (w.kh != o.kh || w.kw != o.kw || w.cout != o.Cout || cin_expect != o.Cin)
+                return fail(ADAPT_EINVAL, "op %d: geometry %dx%dx%d->%d does not match weight %d (%dx%dx%d->%d)", i,
+                            o.kh, o.kw, o.Cin, o.Cout, o.weight, w.kh, w.kw, cin_expect, w.cout);
+        } else if (o.kind < ADAPT_OP_INGEST || o.kind > ADAPT_OP_SOFTMAX) {
+            return fail(ADAPT_EINVAL, "op %d: unknown kind %d", i, o.kind);
+        }
+    }
+    drop_plans(st);
+    free_tensors(st);
+    st->tdesc.assign(tensors, tensors + n_tensors);
+    st->tptr.assign(n_tensors, nullptr);
+    st->ops.assign(ops, ops + n_ops);
+    for (int i = 0; i < n_tensors; ++i) {
+        if (tensors[i].role != ADAPT_T_INTERNAL) continue;
+        const size_t bytes = (size_t)tensors[i].elems_per_image * st->max_batch * elem_size(st, tensors[i].dtype);
+        CUDA_TRY(cudaMalloc(&st->tptr[i], bytes));
+    }
+    return ADAPT_OK;
+}
+
+void* resolve(adapt_stage* st, int t, int slot) {
+    if (t < 0) return nullptr;
+    const int role = st->tdesc[t].role;
+    if (role == ADAPT_T_INPUT) return st->io_in[slot];
+    if (role == ADAPT_T_OUTPUT) return st->io_out[slot];
+    return st->tptr[t];
+}
+
+int build_steps(adapt_stage* st, Plan* plan, int slot) {
+    if (!st->io_in[slot] || !st->io_out[slot]) return fail(ADAPT_ESTATE, "slot %d has no bound I/O buffers", slot);
+    std::vector<Step>& steps = plan->steps[slot];
+    steps.clear();
+    for (size_t i = 0; i < st->ops.size(); ++i) {
+        const adapt_op_desc& o = st->ops[i];
+        Step s;
+        s.kind = o.kind;
+        s.op = o;
+        s.batch = plan->batch;
+        s.in = resolve(st, o.in_tensor, slot);
+        s.res = resolve(st, o.res_tensor, slot);
+        s.out = resolve(st, o.out_tensor, slot);
+        if (o.kind == ADAPT_OP_CONV && st->mode == ADAPT_MODE_BF16) {
+            const WeightDev& w = st->weights[o.weight];
+            ConvGeom g{plan->batch, o.H, o.W, o.Cin, o.Ho, o.Wo, o.Cout, o.kh, o.kw, o.stride, o.pad};
+            int rc = build_conv_launch(&s.conv, g, s.in, w.kernel, w.scale, w.bias, s.res, s.out, o.out_f32 != 0,
+                                       o.relu, -1, 0, st->num_sms);
+            if (rc) return rc;
+        }
+        steps.push_back(s);
+    }
+    plan->built[slot] = true;
+    return ADAPT_OK;
+}
+
+int run_steps(adapt_stage* st, const std::vector<Step>& steps, cudaStream_t stream) {
+    for (const Step& s : steps) {
+        const adapt_op_desc& o = s.op;
+        const int B = s.batch;
+        switch (s.kind) {
+            case ADAPT_OP_INGEST: {
+                const long long pixels = (long long)B * o.H * o.W;
+                if (st->mode == ADAPT_MODE_BF16) {
+                    if (o.Cout != 8 || o.Cin > 8) return fail(ADAPT_EINVAL, "ingest: expects Cin<=8 -> 8 channels");
+                    const int threads = 256;
+                    const long long blocks = (pixels + threads - 1) / threads;
+                    adapt::ingest_f32_to_bf16_pad8_kernel<<<(unsigned)blocks, threads, 0, stream>>>(
+                        reinterpret_cast<const float*>(s.in), reinterpret_cast<__nv_bfloat16*>(s.out), pixels, o.Cin);
+                } else {
+                    CUDA_TRY(cudaMemcpyAsync(s.out, s.in, (size_t)pixels * o.Cin * 4, cudaMemcpyDeviceToDevice,
+                                             stream));
+                }
+                break;
+            }
+            case ADAPT_OP_CONV: {
+                if (st->mode == ADAPT_MODE_BF16) {
+                    int rc = run_conv_launch(s.conv, stream);
+                    if (rc) return rc;
+                } else {
+                    const WeightDev& w = st->weights[o.weight];
+                    const int M = B * o.Ho * o.Wo;
+                    constexpr int PIX = 8;
+                    dim3 block(o.Cout >= 128 ? 128 : 64);
+                    dim3 grid((o.Cout + block.x - 1) / block.x, (M + PIX - 1) / PIX);
+                    adapt::conv_fp32_direct_kernel<PIX><<<grid, block, 0, stream>>>(
+                        reinterpret_cast<const float*>(s.in), reinterpret_cast<const float*>(w.kernel), w.scale,
+                        w.bias, reinterpret_cast<const float*>(s.res), reinterpret_cast<float*>(s.out), M, o.H, o.W,
+                        o.Cin, o.Ho, o.Wo, o.Cout, o.kh, o.kw, o.stride, o.pad, o.relu);
+                }
+                break;
+            }
+            case ADAPT_OP_MAXPOOL: {
+                const long long total = (long long)B * o.Ho * o.Wo * (o.Cin / 8);
+                const int threads = 256;
+                const unsigned blocks = (unsigned)((total + threads - 1) / threads);
+                if (st->mode == ADAPT_MODE_BF16)
+                    adapt::maxpool_zeropad_kernel<__nv_bfloat16><<<blocks, threads, 0, stream>>>(
+                        reinterpret_cast<const __nv_bfloat16*>(s.in), reinterpret_cast<__nv_bfloat16*>(s.out), B, o.H,
+                        o.W, o.Cin, o.Ho, o.Wo, o.kh, o.stride, o.pad);
+                else
+                    adapt::maxpool_zeropad_kernel<float><<<blocks, threads, 0, stream>>>(
+                        reinterpret_cast<const float*>(s.in), reinterpret_cast<float*>(s.out), B, o.H, o.W, o.Cin,
+                        o.Ho, o.Wo, o.kh, o.stride, o.pad);
+                break;
+            }
+            case ADAPT_OP_GAP: {
+                const int total = B * (o.Cin / 8);
+                const int threads = 128;
+                const unsigned blocks = (unsigned)((total + threads - 1) / threads);
+                if (st->mode == ADAPT_MODE_BF16)
+                    adapt::global_avgpool_kernel<__nv_bfloat16, __nv_bfloat16><<<blocks, threads, 0, stream>>>(
+                        reinterpret_cast<const __nv_bfloat16*>(s.in), reinterpret_cast<__nv_bfloat16*>(s.out), B,
+                        o.H * o.W, o.Cin);
+                else
+                    adapt::global_avgpool_kernel<float, float><<<blocks, threads, 0, stream>>>(
+                        reinterpret_cast<const float*>(s.in), reinterpret_cast<float*>(s.out), B, o.H * o.W, o.Cin);
+                break;
+            }
+            case ADAPT_OP_SOFTMAX: {
+                const int warps_per_block = 4;
+                const unsigned blocks = (unsigned)((B + warps_per_block - 1) / warps_per_block);
+                adapt::softmax_rows_kernel<<<blocks, warps_per_block * 32, 0, stream>>>(
+                    reinterpret_cast<const float*>(s.in), reinterpret_cast<float*>(s.out), B, o.Cin);
+                break;
+            }
+            default:
+                return fail(ADAPT_EINVAL, "unknown op kind %d", s.kind);
+        }
+        CUDA_TRY(cudaGetLastError());
+    }
+    return ADAPT_OK;
+}
+
+int upload_weights(adapt_stage* st, const adapt_weight_desc* weights, int n_weights) {
+    st->weights.resize(n_weights);
+    for (int i = 0; i < n_weights; ++i) {
+        const adapt_weight_desc& h = weights[i];
+        if (!h.kernel || !h.scale || !h.bias || h.kh <= 0 || h.kw <= 0 || h.cin <= 0 || h.cout <= 0)
+            return fail(ADAPT_EINVAL, "weight %d: bad descriptor", i);
+        WeightDev& w = st->weights[i];
+        w.kh = h.kh; w.kw = h.kw; w.cin = h.cin; w.cout = h.cout;
+        w.cin_store = (h.cin + 7) / 8 * 8;
+        const size_t cout_pad = (size_t)(h.cout + 7) / 8 * 8;
+        CUDA_TRY(cudaMalloc(&w.scale, cout_pad * sizeof(float)));
+        CUDA_TRY(cudaMalloc(&w.bias, cout_pad * sizeof(float)));
+        CUDA_TRY(cudaMemset(w.scale, 0, cout_pad * sizeof(float)));
+        CUDA_TRY(cudaMemset(w.bias, 0, cout_pad * sizeof(float)));
+        CUDA_TRY(cudaMemcpy(w.scale, h.scale, (size_t)h.cout * sizeof(float), cudaMemcpyHostToDevice));
+        CUDA_TRY(cudaMemcpy(w.bias, h.bias, (size_t)h.cout * sizeof(float), cudaMemcpyHostToDevice));
+        if (st->mode == ADAPT_MODE_BF16) {
+            // HWIO fp32 -> [cout][kh][kw][cin_store] bf16 (round-to-nearest-even), zero channel padding
+            const size_t K = (size_t)h.kh * h.kw * w.cin_store;
+            std::vector<__nv_bfloat16> t((size_t)h.cout * K, __float2bfloat16_rn(0.0f));
+            for (int r = 0; r < h.kh; ++r)
+                for (int s = 0; s < h.kw; ++s)
+                    for (int c = 0; c < h.cin; ++c) {
+                        const float* src = h.kernel + ((size_t)(r * h.kw + s) * h.cin + c) * h.cout;
+                        for (int o = 0; o < h.cout; ++o)
+                            t[(size_t)o * K + (size_t)(r * h.kw + s) * w.cin_store + c] = __float2bfloat16_rn(src[o]);
+                    }
+            CUDA_TRY(cudaMalloc(&w.kernel, t.size() * sizeof(__nv_bfloat16)));
+            CUDA_TRY(cudaMemcpy(w.kernel, t.data(), t.size() * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice));
+        } else {
+            const size_t n = (size_t)h.kh * h.kw * h.cin * h.cout;
+            CUDA_TRY(cudaMalloc(&w.kernel, n * sizeof(float)));
+            CUDA_TRY(cudaMemcpy(w.kernel, h.kernel, n * sizeof(float), cudaMemcpyHostToDevice));
+        }
+    }
+    return ADAPT_OK;
+}
+
+}  // namespace
+
+// =============================================================================== C ABI
+extern "C" {
+
+const char* adapt_version(void) { return "adapt_b200 0.1 (sm_100a)"; }
+
+const char* adapt_last_error(void) { return g_last_error.c_str(); }
+
+int adapt_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+int adapt_stage_create(int device, int dtype_mode, int max_batch, const adapt_weight_desc* weights, int n_weights,
+                       const adapt_tensor_desc* tensors, int n_tensors, const adapt_op_desc* ops, int n_ops,
+                       adapt_stage_t** out) {
+    if (!out) return fail(ADAPT_EINVAL, "out is null");
+    *out = nullptr;
+    if (dtype_mode != ADAPT_MODE_BF16 && dtype_mode != ADAPT_MODE_FP32_CHECK)
+        return fail(ADAPT_EINVAL, "unknown dtype_mode %d", dtype_mode);
+    if (max_batch <= 0 || !weights || n_weights <= 0) return fail(ADAPT_EINVAL, "bad max_batch / weights");
+    int rc = require_device(device);
+    if (rc) return rc;
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) return fail(ADAPT_ENODEV, "device %d is sm_%d%d; this library is sm_100a only", device,
+                                      prop.major, prop.minor);
+    rc = init_conv_kernels_for_device();
+    if (rc) return rc;
+    std::unique_ptr<adapt_stage> st(new adapt_stage());
+    st->device = device;
+    st->mode = dtype_mode;
+    st->max_batch = max_batch;
+    st->num_sms = prop.multiProcessorCount;
+    st->use_graph = env_int("ADAPT_NO_GRAPH", 0) == 0;
+    rc = upload_weights(st.get(), weights, n_weights);
+    if (rc == ADAPT_OK) rc = install_program(st.get(), tensors, n_tensors, ops, n_ops);
+    if (rc) {
+        adapt_stage_destroy(st.release());
+        return rc;
+    }
+    *out = st.release();
+    return ADAPT_OK;
+}
+
+int adapt_stage_reslice(adapt_stage_t* st, const adapt_tensor_desc* tensors, int n_tensors, const adapt_op_desc* ops,
+                        int n_ops) {
+    if (!st) return fail(ADAPT_EINVAL, "stage is null");
+    int rc = require_device(st->device);
+    if (rc) return rc;
+    CUDA_TRY(cudaDeviceSynchronize());
+    st->io_in[0] = st->io_in[1] = st->io_out[0] = st->io_out[1] = nullptr;
+    return install_program(st, tensors, n_tensors, ops, n_ops);
+}
+
+int adapt_stage_bind_io(adapt_stage_t* st, int slot, void* in_ptr, void* out_ptr) {
+    if (!st || slot < 0 || slot > 1 || !in_ptr || !out_ptr) return fail(ADAPT_EINVAL, "bind_io: bad argument");
+    if (st->io_in[slot] == in_ptr && st->io_out[slot] == out_ptr) return ADAPT_OK;
+    st->io_in[slot] = in_ptr;
+    st->io_out[slot] = out_ptr;
+    // cached launch records / graphs of this slot hold the old pointers
+    for (auto& kv : st->plans) {
+        Plan* p = kv.second.get();
+        p->built[slot] = false;
+        if (p->exec[slot]) {
+            cudaGraphExecDestroy(p->exec[slot]);
+            p->exec[slot] = nullptr;
+        }
+    }
+    return ADAPT_OK;
+}
+
+int adapt_stage_enqueue(adapt_stage_t* st, int slot, int batch, void* stream_v) {
+    if (!st || slot < 0 || slot > 1) return fail(ADAPT_EINVAL, "enqueue: bad argument");
+    if (batch <= 0 || batch > st->max_batch) return fail(ADAPT_EINVAL, "enqueue: batch %d not in [1, %d]", batch,
+                                                         st->max_batch);
+    if (st->ops.empty()) return fail(ADAPT_ESTATE, "enqueue: no program installed");
+    int rc = require_device(st->device);
+    if (rc) return rc;
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
+    auto it = st->plans.find(batch);
+    if (it == st->plans.end()) {
+        std::unique_ptr<Plan> p(new Plan());
+        p->batch = batch;
+        it = st->plans.emplace(batch, std::move(p)).first;
+    }
+    Plan* plan = it->second.get();
+    if (!plan->built[slot]) {
+        rc = build_steps(st, plan, slot);
+        if (rc) return rc;
+    }
+    if (!st->use_graph) return run_steps(st, plan->steps[slot], stream);
+    if (!plan->exec[slot]) {
+        cudaStream_t cap;
+        CUDA_TRY(cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking));
+        cudaGraph_t graph = nullptr;
+        cudaError_t e = cudaStreamBeginCapture(cap, cudaStreamCaptureModeThreadLocal);
+        if (e != cudaSuccess) {
+            cudaStreamDestroy(cap);
+            return fail(ADAPT_ECUDA, "cudaStreamBeginCapture: %s", cudaGetErrorString(e));
+        }
+        rc = run_steps(st, plan->steps[slot], cap);
+        e = cudaStreamEndCapture(cap, &graph);
+        cudaStreamDestroy(cap);
+        if (rc) {
+            if (graph) cudaGraphDestroy(graph);
+            return rc;
+        }
+        if (e != cudaSuccess) return fail(ADAPT_ECUDA, "cudaStreamEndCapture: %s", cudaGetErrorString(e));
+        e = cudaGraphInstantiate(&plan->exec[slot], graph, 0);
+        cudaGraphDestroy(graph);
+        if (e != cudaSuccess) return fail(ADAPT_ECUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e));
+    }
+    CUDA_TRY(cudaGraphLaunch(plan->exec[slot], stream));
+    return ADAPT_OK;
+}
+
+int adapt_stage_read_tensor(adapt_stage_t* st, int tensor, void* host_dst, size_t bytes, void* stream_v) {
+    if (!st || tensor < 0 || tensor >= (int)st->tdesc.size() || !host_dst)
+        return fail(ADAPT_EINVAL, "read_tensor: bad argument");
+    if (st->tdesc[tensor].role != ADAPT_T_INTERNAL) return fail(ADAPT_EINVAL, "read_tensor: tensor is not internal");
+    const size_t cap = (size_t)st->tdesc[tensor].elems_per_image * st->max_batch * elem_size(st, st->tdesc[tensor].dtype);
+    if (bytes > cap) return fail(ADAPT_EINVAL, "read_tensor: %zu bytes > capacity %zu", bytes, cap);
+    int rc = require_device(st->device);
+    if (rc) return rc;
+    CUDA_TRY(cudaStreamSynchronize(reinterpret_cast<cudaStream_t>(stream_v)));
+    CUDA_TRY(cudaMemcpy(host_dst, st->tptr[tensor], bytes, cudaMemcpyDeviceToHost));
+    return ADAPT_OK;
+}
+
+int adapt_stage_num_launches(adapt_stage_t* st, int batch) {
+    if (!st) return fail(ADAPT_EINVAL, "stage is null");
+    (void)batch;
+    return (int)st->ops.size();
+}
+
+void adapt_stage_destroy(adapt_stage_t* st) {
+    if (!st) return;
+    if (cudaSetDevice(st->device) == cudaSuccess) {
+        cudaDeviceSynchronize();
+        drop_plans(st);
+        free_tensors(st);
+        for (WeightDev& w : st->weights) {
+            if (w.kernel) cudaFree(w.kernel);
+            if (w.scale) cudaFree(w.scale);
+            if (w.bias) cudaFree(w.bias);
+        }
+    }
+    cudaGetLastError();
+    delete st;
+}
+
+int adapt_conv2d_bf16(int device, const void* in, const void* w, const float* scale, const float* bias,
+                      const void* residual, void* out, int out_is_f32, int batch, int H, int W, int Cin, int Cout,
+                      int kh, int kw, int stride, int pad, int relu, int a_mode, int block_n, void* stream) {
+    if (!in || !w || !scale || !bias || !out) return fail(ADAPT_EINVAL, "conv2d: null pointer");
+    if (batch <= 0 || H <= 0 || W <= 0 || kh <= 0 || kw <= 0 || stride <= 0 || pad < 0)
+        return fail(ADAPT_EINVAL, "conv2d: bad geometry");
+    int rc = require_device(device);
+    if (rc) return rc;
+    static bool attr_done[64] = {false};
+    if (device < 64 && !attr_done[device]) {
+        rc = init_conv_kernels_for_device();
+        if (rc) return rc;
+        attr_done[device] = true;
+    }
+    int num_sms = 0;
+    CUDA_TRY(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, device));
+    const int Ho = (H + 2 * pad - kh) / stride + 1;
+    const int Wo = (W + 2 * pad - kw) / stride + 1;
+    if (Ho <= 0 || Wo <= 0) return fail(ADAPT_EINVAL, "conv2d: empty output");
+    ConvGeom g{batch, H, W, Cin, Ho, Wo, Cout, kh, kw, stride, pad};
+    ConvLaunch L;
+    rc = build_conv_launch(&L, g, in, w, scale, bias, residual, out, out_is_f32 != 0, relu, a_mode, block_n, num_sms);
+    if (rc) return rc;
+    return run_conv_launch(L, reinterpret_cast<cudaStream_t>(stream));
+}
+
+// ---------------------------------------------------------------- hand-off plumbing
+int adapt_device_alloc(int device, size_t bytes, void** out) {
+    if (!out || bytes == 0) return fail(ADAPT_EINVAL, "device_alloc: bad argument");
+    int rc = require_device(device);
+    if (rc) return rc;
+    CUDA_TRY(cudaMalloc(out, bytes));
+    CUDA_TRY(cudaMemset(*out, 0, bytes));
+    return ADAPT_OK;
+}
+
+int adapt_device_free(int device, void* ptr) {
+    int rc = require_device(device);
+    if (rc) return rc;
+    CUDA_TRY(cudaFree(ptr));
+    return ADAPT_OK;
+}
+
+int adapt_peer_enable(int a, int b) {
+    if (a == b) return ADAPT_OK;
+    int rc = require_device(a);
+    if (rc) return rc;
+    for (int dir = 0; dir < 2; ++dir) {
+        const int from = dir == 0 ? a : b, to = dir == 0 ? b : a;
+        int can = 0;
+        CUDA_TRY(cudaDeviceCanAccessPeer(&can, from, to));
+        if (!can) return fail(ADAPT_ECUDA, "device %d cannot access peer %d", from, to);
+        CUDA_TRY(cudaSetDevice(from));
+        cudaError_t e = cudaDeviceEnablePeerAccess(to, 0);
+        if (e == cudaErrorPeerAccessAlreadyEnabled) {
+            cudaGetLastError();
+        } else if (e != cudaSuccess) {
+            return fail(ADAPT_ECUDA, "cudaDeviceEnablePeerAccess(%d->%d): %s", from, to, cudaGetErrorString(e));
+        }
+    }
+    return ADAPT_OK;
+}
+
+int adapt_ipc_export(int device, void* ptr, void* handle64_out) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    if (!ptr || !handle64_out) return fail(ADAPT_EINVAL, "ipc_export: null");
+    int rc = require_device(device);
+    if (rc) return rc;
+    cudaIpcMemHandle_t h;
+    CUDA_TRY(cudaIpcGetMemHandle(&h, ptr));
+    memcpy(handle64_out, &h, 64);
+    return ADAPT_OK;
+}
+
+int adapt_ipc_import(int device, const void* handle64, void** out) {
+    if (!handle64 || !out) return fail(ADAPT_EINVAL, "ipc_import: null");
+    int rc = require_device(device);
+    if (rc) return rc;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    CUDA_TRY(cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess));
+    return ADAPT_OK;
+}
+
+int adapt_ipc_close(int device, void* ptr) {
+    int rc = require_device(device);
+    if (rc) return rc;
+    CUDA_TRY(cudaIpcCloseMemHandle(ptr));
+    return ADAPT_OK;
+}
+
+int adapt_stream_write_flag(int device, void* stream, void* flag_ptr, uint32_t value) {
+    int rc = require_device(device);
+    if (rc) return rc;
+    DriverApi* d;
+    rc = get_driver(&d);
+    if (rc) return rc;
+    CUresult r = d->writeValue32(reinterpret_cast<CUstream>(stream), reinterpret_cast<CUdeviceptr>(flag_ptr), value,
+                                 CU_STREAM_WRITE_VALUE_DEFAULT);
+    if (r != CUDA_SUCCESS) return fail(ADAPT_ECUDA, "cuStreamWriteValue32 failed (%d)", (int)r);
+    return ADAPT_OK;
+}
+
+int adapt_stream_wait_flag_geq(int device, void* stream, void* flag_ptr, uint32_t value) {
+    int rc = require_device(device);
+    if (rc) return rc;
+    DriverApi* d;
+    rc = get_driver(&d);
+    if (rc) return rc;
+    CUresult r = d->waitValue32(reinterpret_cast<CUstream>(stream), reinterpret_cast<CUdeviceptr>(flag_ptr), value,
+                                CU_STREAM_WAIT_VALUE_GEQ);
+    if (r != CUDA_SUCCESS) return fail(ADAPT_ECUDA, "cuStreamWaitValue32 failed (%d)", (int)r);
+    return ADAPT_OK;
+}
+
+int adapt_memcpy_h2d(int device, void* dst, const void* src, size_t bytes, void* stream) {
+    int rc = require_device(device);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, reinterpret_cast<cudaStream_t>(stream)));
+    return ADAPT_OK;
+}
+int adapt_memcpy_d2h(int device, void* dst, const void* src, size_t bytes, void* stream) {
+    int rc = require_device(device);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, reinterpret_cast<cudaStream_t>(stream)));
+    return ADAPT_OK;
+}
+int adapt_memcpy_d2d(int device, void* dst, const void* src, size_t bytes, void* stream) {
+    int rc = require_device(device);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, reinterpret_cast<cudaStream_t>(stream)));
+    return ADAPT_OK;
+}
+int adapt_memset(int device, void* dst, int value, size_t bytes, void* stream) {
+    int rc = require_device(device);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemsetAsync(dst, value, bytes, reinterpret_cast<cudaStream_t>(stream)));
+    return ADAPT_OK;
+}
+int adapt_stream_sync(int device, void* stream) {
+    int rc = require_device(device);
+    if (rc) return rc;
+    CUDA_TRY(cudaStreamSynchronize(reinterpret_cast<cudaStream_t>(stream)));
+    return ADAPT_OK;
+}
+
+}  // extern "C"

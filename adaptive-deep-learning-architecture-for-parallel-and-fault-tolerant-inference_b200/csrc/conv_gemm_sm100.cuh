@@ -1,0 +1,331 @@
+// Implicit-GEMM convolution for one pipeline stage's Conv2D+bias+BN(+Add)(+ReLU) layers.
+//
+// Replaces the arithmetic the reference delegates to `model.predict` (reference
+// src/node.py:177) for every Conv2D / BatchNormalization / Add / ReLU group of the Keras
+// ResNet-50 graph, and for the final Dense layer (as a 1x1 "convolution" over M = batch).
+//
+//   out[m, n] = act( (sum_k A[m, k] * Wt[n, k]) * scale[n] + bias[n] (+ residual[m, n]) )
+//
+//   A  : NHWC bf16 activations, viewed as the im2col matrix [M = B*Ho*Wo, K = kh*kw*Cin]
+//   Wt : bf16 weights [Cout, kh, kw, Cin]  (K-major "B" operand)
+//   acc: fp32 in TMEM (tcgen05.mma kind::f16), epilogue in fp32, output bf16 (or fp32)
+//
+// Structure: persistent CTAs (one per SM), warp-specialised:
+//   warp 0      TMA producer   (A tile: tiled 2-D box, or im2col box; B tile: tiled 2-D box)
+//   warp 1      MMA issuer     (one elected lane issues tcgen05.mma; owns the TMEM allocation)
+//   warps 2..5  epilogue       (tcgen05.ld -> scale/bias/residual/ReLU -> bf16 -> global)
+//   warps 6..9  (A_GATHER only) software im2col producers for thin-channel inputs (the stem)
+// Three pipelines: smem full/empty ring (TMA <-> MMA), TMEM full/empty double buffer
+// (MMA <-> epilogue), and a static round-robin tile schedule.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <cuda.h>
+#include <cstdint>
+#include "ptx_sm100.cuh"
+
+namespace adapt {
+
+enum AMode : int { A_TILED = 0, A_IM2COL = 1, A_GATHER = 2 };
+
+struct ConvGemmParams {
+    int M;             // output pixels in this launch: batch * Ho * Wo
+    int N;             // output channels
+    int num_k_blocks;  // ceil(K / 64)
+    int m_tiles, n_tiles;
+    // convolution geometry (A_IM2COL / A_GATHER)
+    int H, W, Cin;  // stored input channels per pixel
+    int Ho, Wo;
+    int kh, kw, stride, pad;
+    int c_blocks;  // Cin / 64 (A_IM2COL)
+    int K_real;    // kh*kw*Cin (A_GATHER zero-fills beyond it)
+    // epilogue
+    const float* scale;             // [N] folded BN scale (gamma / sqrt(var + eps)), or 1
+    const float* bias;              // [N] folded (conv_bias - mean) * scale + beta
+    const __nv_bfloat16* residual;  // [M, N] or nullptr
+    __nv_bfloat16* out_bf16;        // [M, N] or nullptr
+    float* out_f32;                 // [M, N] or nullptr (Dense logits)
+    int relu;
+    // A_GATHER source
+    const __nv_bfloat16* in;
+};
+
+constexpr int kBlockM = 128;
+constexpr int kBlockK = 64;  // 64 bf16 = one 128-byte swizzle row
+constexpr int kUmmaK = 16;
+constexpr int kABytes = kBlockM * kBlockK * 2;
+
+template <int BLOCK_N>
+struct ConvGemmCfg {
+    static constexpr int kBBytes = BLOCK_N * kBlockK * 2;
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kStagesRaw = (196 * 1024) / kStageBytes;
+    static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+    static constexpr int kTmemCols = 2 * BLOCK_N;  // double-buffered accumulator (power of 2 >= 32)
+    static constexpr int kBarrierBytes = 256;
+    static constexpr int kSmemBytes = kStages * kStageBytes + kBarrierBytes + 1024;  // +1024 alignment slack
+};
+
+template <int A_MODE>
+constexpr int conv_gemm_threads() {
+    return A_MODE == A_GATHER ? 320 : 192;
+}
+
+template <int BLOCK_N, int A_MODE>
+__global__ void __launch_bounds__(conv_gemm_threads<A_MODE>(), 1)
+conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                 const ConvGemmParams p) {
+    using Cfg = ConvGemmCfg<BLOCK_N>;
+    constexpr int kStages = Cfg::kStages;
+    static_assert(BLOCK_N % 32 == 0 && BLOCK_N >= 64 && BLOCK_N <= 256, "BLOCK_N");
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem_a = smem;
+    uint8_t* smem_b = smem + kStages * kABytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+    uint64_t* full_bar = bars;
+    uint64_t* empty_bar = bars + kStages;
+    uint64_t* tmem_full_bar = bars + 2 * kStages;
+    uint64_t* tmem_empty_bar = bars + 2 * kStages + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+
+    const int warp_idx = __shfl_sync(0xffffffff, threadIdx.x / 32, 0);
+    const int lane = threadIdx.x % 32;
+    const int num_tiles = p.m_tiles * p.n_tiles;
+
+    if (warp_idx == 0 && lane == 0) {
+        if (A_MODE != A_GATHER) ptx::prefetch_tmap(&tmap_a);
+        ptx::prefetch_tmap(&tmap_b);
+        constexpr uint32_t full_count = (A_MODE == A_GATHER) ? (1 + 128) : 1;
+        for (int i = 0; i < kStages; ++i) {
+            ptx::mbar_init(&full_bar[i], full_count);
+            ptx::mbar_init(&empty_bar[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            ptx::mbar_init(&tmem_full_bar[i], 1);
+            ptx::mbar_init(&tmem_empty_bar[i], 4);  // one arrive per epilogue warp
+        }
+        ptx::fence_mbar_init();
+    }
+    if (warp_idx == 1) {
+        ptx::tmem_alloc(tmem_slot, Cfg::kTmemCols);
+        ptx::tmem_relinquish();
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp_idx == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int it = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const int m_blk = tile / p.n_tiles;
+                const int n_blk = tile % p.n_tiles;
+                int img = 0, base_w = 0, base_h = 0;
+                if (A_MODE == A_IM2COL) {
+                    const int m0 = m_blk * kBlockM;
+                    const int hw = p.Ho * p.Wo;
+                    img = m0 / hw;
+                    const int rem = m0 - img * hw;
+                    const int po = rem / p.Wo;
+                    const int qo = rem - po * p.Wo;
+                    base_w = qo * p.stride - p.pad;
+                    base_h = po * p.stride - p.pad;
+                }
+                for (int kb = 0; kb < p.num_k_blocks; ++kb, ++it) {
+                    const int stage = it % kStages;
+                    const uint32_t phase = (it / kStages) & 1;
+                    ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+                    if (A_MODE == A_GATHER) {
+                        ptx::mbar_expect_tx(&full_bar[stage], Cfg::kBBytes);
+                    } else {
+                        ptx::mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+                    }
+                    if (A_MODE == A_TILED) {
+                        ptx::tma_load_2d(smem_a + stage * kABytes, &tmap_a, &full_bar[stage], kb * kBlockK,
+                                         m_blk * kBlockM);
+                    } else if (A_MODE == A_IM2COL) {
+                        const int tap = kb / p.c_blocks;
+                        const int c0 = (kb - tap * p.c_blocks) * kBlockK;
+                        const int r = tap / p.kw;
+                        const int s = tap - r * p.kw;
+                        ptx::tma_load_im2col_4d(smem_a + stage * kABytes, &tmap_a, &full_bar[stage], c0, base_w,
+                                                base_h, img, static_cast<uint16_t>(s), static_cast<uint16_t>(r));
+                    }
+                    ptx::tma_load_2d(smem_b + stage * Cfg::kBBytes, &tmap_b, &full_bar[stage], kb * kBlockK,
+                                     n_blk * BLOCK_N);
+                }
+            }
+        }
+    } else if (warp_idx == 1) {
+        // ===================== MMA issuer =====================
+        constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(kBlockM, BLOCK_N);
+        int it = 0;
+        int tile_iter = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tile_iter) {
+            const int acc_stage = tile_iter & 1;
+            const uint32_t acc_phase = (tile_iter >> 1) & 1;
+            ptx::mbar_wait(&tmem_empty_bar[acc_stage], acc_phase ^ 1);
+            ptx::tc_fence_after();
+            const uint32_t tmem_d = tmem_base + acc_stage * BLOCK_N;
+            for (int kb = 0; kb < p.num_k_blocks; ++kb, ++it) {
+                const int stage = it % kStages;
+                const uint32_t phase = (it / kStages) & 1;
+                ptx::mbar_wait(&full_bar[stage], phase);
+                ptx::tc_fence_after();
+                if (ptx::elect_one()) {
+                    const uint64_t a_desc = ptx::make_kmajor_sw128_desc(ptx::smem_u32(smem_a + stage * kABytes));
+                    const uint64_t b_desc = ptx::make_kmajor_sw128_desc(ptx::smem_u32(smem_b + stage * Cfg::kBBytes));
+#pragma unroll
+                    for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+                        // advance 16 elements (32 B) along K inside the swizzle atom: +2 in 16-byte units
+                        ptx::umma_bf16_ss(tmem_d, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                    }
+                    ptx::umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
+                    if (kb == p.num_k_blocks - 1) ptx::umma_commit(&tmem_full_bar[acc_stage]);
+                }
+                __syncwarp();
+            }
+        }
+    } else if (warp_idx < 6) {
+        // ===================== epilogue =====================
+        const int lane_group = warp_idx & 3;  // TMEM lanes this warp may touch: [32*lane_group, +32)
+        int tile_iter = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tile_iter) {
+            const int m_blk = tile / p.n_tiles;
+            const int n_blk = tile % p.n_tiles;
+            const int acc_stage = tile_iter & 1;
+            const uint32_t acc_phase = (tile_iter >> 1) & 1;
+            ptx::mbar_wait(&tmem_full_bar[acc_stage], acc_phase);
+            ptx::tc_fence_after();
+            const int m = m_blk * kBlockM + lane_group * 32 + lane;
+            const bool row_ok = m < p.M;
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lane_group * 32) << 16) + acc_stage * BLOCK_N;
+#pragma unroll 1
+            for (int chunk = 0; chunk < BLOCK_N / 32; ++chunk) {
+                uint32_t v[32];
+                ptx::tmem_ld_32x32b_x32(taddr + chunk * 32, v);
+                ptx::tmem_ld_wait();
+                if (chunk == BLOCK_N / 32 - 1) {
+                    // accumulator fully drained into registers: hand the TMEM buffer back to the MMA warp
+                    ptx::tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) ptx::mbar_arrive(&tmem_empty_bar[acc_stage]);
+                }
+                const int n0 = n_blk * BLOCK_N + chunk * 32;
+                if (n0 >= p.N) continue;
+                const size_t row_off = static_cast<size_t>(m) * p.N + n0;
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {  // 8 columns per group
+                    const int n = n0 + g * 8;
+                    if (n >= p.N) break;  // N is a multiple of 8
+                    const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.scale + n));
+                    const float4 s1 = __ldg(reinterpret_cast<const float4*>(p.scale + n + 4));
+                    const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + n));
+                    const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + n + 4));
+                    float y[8];
+                    y[0] = fmaf(__uint_as_float(v[g * 8 + 0]), s0.x, b0.x);
+                    y[1] = fmaf(__uint_as_float(v[g * 8 + 1]), s0.y, b0.y);
+                    y[2] = fmaf(__uint_as_float(v[g * 8 + 2]), s0.z, b0.z);
+                    y[3] = fmaf(__uint_as_float(v[g * 8 + 3]), s0.w, b0.w);
+                    y[4] = fmaf(__uint_as_float(v[g * 8 + 4]), s1.x, b1.x);
+                    y[5] = fmaf(__uint_as_float(v[g * 8 + 5]), s1.y, b1.y);
+                    y[6] = fmaf(__uint_as_float(v[g * 8 + 6]), s1.z, b1.z);
+                    y[7] = fmaf(__uint_as_float(v[g * 8 + 7]), s1.w, b1.w);
+                    if (!row_ok) continue;
+                    if (p.residual != nullptr) {
+                        const uint4 rv = *reinterpret_cast<const uint4*>(p.residual + row_off + g * 8);
+                        const __nv_bfloat162* r2 = reinterpret_cast<const __nv_bfloat162*>(&rv);
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const float2 f = __bfloat1622float2(r2[j]);
+                            y[2 * j] += f.x;
+                            y[2 * j + 1] += f.y;
+                        }
+                    }
+                    if (p.relu) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) y[j] = fmaxf(y[j], 0.0f);
+                    }
+                    if (p.out_f32 != nullptr) {
+                        float4* o = reinterpret_cast<float4*>(p.out_f32 + row_off + g * 8);
+                        o[0] = make_float4(y[0], y[1], y[2], y[3]);
+                        o[1] = make_float4(y[4], y[5], y[6], y[7]);
+                    }
+                    if (p.out_bf16 != nullptr) {
+                        uint4 ov;
+                        __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&ov);
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) o2[j] = __floats2bfloat162_rn(y[2 * j], y[2 * j + 1]);
+                        *reinterpret_cast<uint4*>(p.out_bf16 + row_off + g * 8) = ov;
+                    }
+                }
+            }
+        }
+    } else {
+        // ===================== software im2col producers (A_GATHER) =====================
+        if (A_MODE == A_GATHER) {
+            const int row = threadIdx.x - 192;  // 0..127 : one A-tile row per thread
+            const int hw = p.Ho * p.Wo;
+            int it = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const int m_blk = tile / p.n_tiles;
+                const int m = m_blk * kBlockM + row;
+                const bool row_ok = m < p.M;
+                int img = 0, hi0 = 0, wi0 = 0;
+                if (row_ok) {
+                    img = m / hw;
+                    const int rem = m - img * hw;
+                    const int po = rem / p.Wo;
+                    const int qo = rem - po * p.Wo;
+                    hi0 = po * p.stride - p.pad;
+                    wi0 = qo * p.stride - p.pad;
+                }
+                for (int kb = 0; kb < p.num_k_blocks; ++kb, ++it) {
+                    const int stage = it % kStages;
+                    const uint32_t phase = (it / kStages) & 1;
+                    uint4 vals[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const int k = kb * kBlockK + j * 8;
+                        uint4 val = make_uint4(0u, 0u, 0u, 0u);
+                        if (row_ok && k < p.K_real) {
+                            const int tap = k / p.Cin;
+                            const int c = k - tap * p.Cin;
+                            const int r = tap / p.kw;
+                            const int s = tap - r * p.kw;
+                            const int hi = hi0 + r;
+                            const int wi = wi0 + s;
+                            if (hi >= 0 && hi < p.H && wi >= 0 && wi < p.W) {
+                                val = __ldg(reinterpret_cast<const uint4*>(
+                                    p.in + (static_cast<size_t>(img * p.H + hi) * p.W + wi) * p.Cin + c));
+                            }
+                        }
+                        vals[j] = val;
+                    }
+                    ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t* dst = smem_a + stage * kABytes + row * 128;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        *reinterpret_cast<uint4*>(dst + ((j ^ (row & 7)) << 4)) = vals[j];
+                    }
+                    ptx::fence_proxy_async_smem();
+                    ptx::mbar_arrive(&full_bar[stage]);
+                }
+            }
+        }
+    }
+
+    // ===================== teardown =====================
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp_idx == 1) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc(tmem_base, Cfg::kTmemCols);
+    }
+}
+
+}  // namespace adapt

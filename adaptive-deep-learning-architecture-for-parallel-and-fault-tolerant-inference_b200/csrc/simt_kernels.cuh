@@ -1,0 +1,237 @@
+// Bandwidth-bound layer kernels of a stage (everything that is not a dense contraction), plus
+// the true-fp32 "check mode" kernels.  All are coalesced over the NHWC channel axis with
+// 128-bit accesses; reductions use warp shuffles.  They restate, layer by layer, what the
+// reference obtains from `model.predict` (reference src/node.py:177) for the Keras layers
+// ZeroPadding2D+MaxPooling2D (pool1_pad/pool1_pool), GlobalAveragePooling2D (avg_pool),
+// the softmax of `predictions`, and the fp32->bf16 ingest of the input image.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <cstdint>
+
+namespace adapt {
+
+// ---------------------------------------------------------------------------------------------
+// fp32 NHWC (B,H,W,Cin) -> bf16 NHWC (B,H,W,Cpad) with zero channel padding (Cpad = 8 for the stem)
+// One thread per output pixel: reads Cin floats, writes one 16-byte vector.
+__global__ void ingest_f32_to_bf16_pad8_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out,
+                                               long long num_pixels, int Cin) {
+    const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+    if (i >= num_pixels) return;
+    float v[8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) v[c] = (c < Cin) ? __ldg(in + i * Cin + c) : 0.0f;
+    uint4 o;
+    __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) o2[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+    reinterpret_cast<uint4*>(out)[i] = o;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Zero-pad `pad` on every side, then k x k max-pool with stride s, VALID (Keras pool1_pad + pool1_pool).
+// The padding value takes part in the max, exactly like the Keras graph.  8 channels per thread.
+template <typename T>
+struct Vec8;
+template <>
+struct Vec8<__nv_bfloat16> {
+    uint4 raw;
+    __device__ void load(const __nv_bfloat16* p) { raw = __ldg(reinterpret_cast<const uint4*>(p)); }
+    __device__ void store(__nv_bfloat16* p) const { *reinterpret_cast<uint4*>(p) = raw; }
+    __device__ void to_float(float (&f)[8]) const {
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float2 t = __bfloat1622float2(h[j]);
+            f[2 * j] = t.x;
+            f[2 * j + 1] = t.y;
+        }
+    }
+    __device__ void from_float(const float (&f)[8]) {
+        __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&raw);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) h[j] = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
+    }
+};
+template <>
+struct Vec8<float> {
+    float4 a, b;
+    __device__ void load(const float* p) {
+        a = __ldg(reinterpret_cast<const float4*>(p));
+        b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+    }
+    __device__ void store(float* p) const {
+        reinterpret_cast<float4*>(p)[0] = a;
+        reinterpret_cast<float4*>(p)[1] = b;
+    }
+    __device__ void to_float(float (&f)[8]) const {
+        f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w;
+        f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+    }
+    __device__ void from_float(const float (&f)[8]) {
+        a = make_float4(f[0], f[1], f[2], f[3]);
+        b = make_float4(f[4], f[5], f[6], f[7]);
+    }
+};
+
+template <typename T>
+__global__ void maxpool_zeropad_kernel(const T* __restrict__ in, T* __restrict__ out, int B, int H, int W, int C,
+                                       int Ho, int Wo, int k, int s, int pad) {
+    const int cvecs = C / 8;
+    const long long total = static_cast<long long>(B) * Ho * Wo * cvecs;
+    const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+    if (i >= total) return;
+    const int cv = static_cast<int>(i % cvecs);
+    long long pix = i / cvecs;
+    const int qo = static_cast<int>(pix % Wo);
+    pix /= Wo;
+    const int po = static_cast<int>(pix % Ho);
+    const int b = static_cast<int>(pix / Ho);
+    float m[8];
+    bool any_pad = false;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) m[j] = -INFINITY;
+    for (int r = 0; r < k; ++r) {
+        const int hi = po * s - pad + r;
+        for (int t = 0; t < k; ++t) {
+            const int wi = qo * s - pad + t;
+            if (hi < 0 || hi >= H || wi < 0 || wi >= W) {
+                any_pad = true;
+                continue;
+            }
+            Vec8<T> v;
+            v.load(in + ((static_cast<long long>(b) * H + hi) * W + wi) * C + cv * 8);
+            float f[8];
+            v.to_float(f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) m[j] = fmaxf(m[j], f[j]);
+        }
+    }
+    if (any_pad) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) m[j] = fmaxf(m[j], 0.0f);  // the ZeroPadding2D samples
+    }
+    Vec8<T> o;
+    o.from_float(m);
+    o.store(out + ((static_cast<long long>(b) * Ho + po) * Wo + qo) * C + cv * 8);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Global average pool: (B, HW, C) -> (B, C).  One thread per (b, 8 channels); consecutive threads
+// read consecutive 16-byte vectors of the same pixel (coalesced), fp32 accumulation.
+template <typename TIn, typename TOut>
+__global__ void global_avgpool_kernel(const TIn* __restrict__ in, TOut* __restrict__ out, int B, int HW, int C) {
+    const int cvecs = C / 8;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= B * cvecs) return;
+    const int b = i / cvecs;
+    const int cv = i - b * cvecs;
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.0f;
+    const TIn* base = in + static_cast<long long>(b) * HW * C + cv * 8;
+    for (int px = 0; px < HW; ++px) {
+        Vec8<TIn> v;
+        v.load(base + static_cast<long long>(px) * C);
+        float f[8];
+        v.to_float(f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += f[j];
+    }
+    const float inv = 1.0f / static_cast<float>(HW);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] *= inv;
+    Vec8<TOut> o;
+    o.from_float(acc);
+    o.store(out + static_cast<long long>(b) * C + cv * 8);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Row softmax over fp32 logits (B, N) -> fp32 probabilities.  One warp per row, shuffle reductions.
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffff, v, o));
+    return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffff, v, o);
+    return v;
+}
+
+__global__ void softmax_rows_kernel(const float* __restrict__ logits, float* __restrict__ probs, int B, int N) {
+    const int row = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
+    const int lane = threadIdx.x % 32;
+    if (row >= B) return;
+    const float* x = logits + static_cast<long long>(row) * N;
+    float mx = -INFINITY;
+    for (int i = lane; i < N; i += 32) mx = fmaxf(mx, x[i]);
+    mx = warp_max(mx);
+    float sum = 0.0f;
+    for (int i = lane; i < N; i += 32) sum += expf(x[i] - mx);
+    sum = warp_sum(sum);
+    const float inv = 1.0f / sum;
+    float* y = probs + static_cast<long long>(row) * N;
+    for (int i = lane; i < N; i += 32) y[i] = expf(x[i] - mx) * inv;
+}
+
+// ---------------------------------------------------------------------------------------------
+// fp32 check mode: direct convolution with true fp32 FMAs (no tensor cores, no TF32).
+//   in  : NHWC fp32 (B,H,W,Cin),  w : HWIO fp32 (kh,kw,Cin,Cout)  (the Keras kernel layout as is)
+//   out = act((conv + 0) * scale + bias (+ residual))
+// Thread (x) owns one output channel (coalesced weight reads), block.y strides over PIX pixels.
+template <int PIX>
+__global__ void conv_fp32_direct_kernel(const float* __restrict__ in, const float* __restrict__ w,
+                                        const float* __restrict__ scale, const float* __restrict__ bias,
+                                        const float* __restrict__ residual, float* __restrict__ out, int M, int H,
+                                        int W, int Cin, int Ho, int Wo, int Cout, int kh, int kw, int stride, int pad,
+                                        int relu) {
+    const int co = blockIdx.x * blockDim.x + threadIdx.x;
+    const int m0 = blockIdx.y * PIX;
+    if (co >= Cout) return;
+    float acc[PIX];
+    int img[PIX], hi0[PIX], wi0[PIX];
+#pragma unroll
+    for (int i = 0; i < PIX; ++i) {
+        acc[i] = 0.0f;
+        const int m = m0 + i;
+        const int mm = m < M ? m : M - 1;
+        img[i] = mm / (Ho * Wo);
+        const int rem = mm - img[i] * (Ho * Wo);
+        hi0[i] = (rem / Wo) * stride - pad;
+        wi0[i] = (rem % Wo) * stride - pad;
+    }
+    for (int r = 0; r < kh; ++r) {
+        for (int s = 0; s < kw; ++s) {
+            const float* wp = w + (static_cast<long long>(r * kw + s) * Cin) * Cout + co;
+            const float* ip[PIX];
+            bool ok[PIX];
+#pragma unroll
+            for (int i = 0; i < PIX; ++i) {
+                const int hi = hi0[i] + r, wi = wi0[i] + s;
+                ok[i] = hi >= 0 && hi < H && wi >= 0 && wi < W;
+                ip[i] = in + ((static_cast<long long>(img[i]) * H + (ok[i] ? hi : 0)) * W + (ok[i] ? wi : 0)) * Cin;
+            }
+            for (int c = 0; c < Cin; ++c) {
+                const float wv = __ldg(wp + static_cast<long long>(c) * Cout);
+#pragma unroll
+                for (int i = 0; i < PIX; ++i) {
+                    const float xv = ok[i] ? __ldg(ip[i] + c) : 0.0f;
+                    acc[i] = fmaf(xv, wv, acc[i]);
+                }
+            }
+        }
+    }
+    const float sc = scale[co], bi = bias[co];
+#pragma unroll
+    for (int i = 0; i < PIX; ++i) {
+        const int m = m0 + i;
+        if (m >= M) break;
+        float y = fmaf(acc[i], sc, bi);
+        if (residual != nullptr) y += residual[static_cast<long long>(m) * Cout + co];
+        if (relu) y = fmaxf(y, 0.0f);
+        out[static_cast<long long>(m) * Cout + co] = y;
+    }
+}
+
+}  // namespace adapt

@@ -1,0 +1,166 @@
+/*
+ * adapt_b200.h -- C ABI of the B200 stage executor behind ADAPT/DEFER's pipeline-partitioned
+ * ResNet-50 inference path.
+ *
+ * The reference (pure Python, /root/reference) has no FFI of its own: its operator boundary is
+ * the Python surface DEFER / Node, and the arithmetic is delegated to TensorFlow through
+ * `model.predict` (reference src/node.py:177).  This header is the boundary a maintainer would
+ * bind instead of that call (ctypes stub in INTEGRATION.md).  Every entry point names the
+ * reference interface it stands in for.
+ *
+ * Conventions
+ *   - plain C: pointers, sizes, ints.  No torch / C++ types cross this boundary.
+ *   - every function returns 0 on success and a negative ADAPT_E* code on failure;
+ *     adapt_last_error() returns a thread-local human-readable message for the last failure.
+ *   - device pointers are ordinary CUDA device pointers (e.g. torch.Tensor.data_ptr()).
+ *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream).
+ *   - a stage handle is owned by one host thread at a time (not internally locked).
+ *   - no CPU fallback exists: without a CUDA device every compute entry point fails.
+ */
+#ifndef ADAPT_B200_H_
+#define ADAPT_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ADAPT_OK 0
+#define ADAPT_EINVAL (-1)   /* bad argument / inconsistent program            */
+#define ADAPT_ECUDA (-2)    /* a CUDA runtime or driver call failed           */
+#define ADAPT_ENODEV (-3)   /* no usable sm_100 device                        */
+#define ADAPT_ENOMEM (-4)   /* device allocation failed                       */
+#define ADAPT_ESTATE (-5)   /* call not valid in the handle's current state   */
+
+/* numeric mode of a stage (north_star: bf16 activations + fp32 accumulate; fp32 check mode) */
+#define ADAPT_MODE_BF16 0
+#define ADAPT_MODE_FP32_CHECK 1
+
+/* op kinds of a stage program.  One op = one fused group of Keras layers. */
+#define ADAPT_OP_INGEST 0   /* fp32 NHWC input image -> working dtype, channel-padded (input_1)          */
+#define ADAPT_OP_CONV 1     /* [ZeroPadding2D+]Conv2D+bias+BatchNormalization[+Add][+ReLU]; Dense = 1x1  */
+#define ADAPT_OP_MAXPOOL 2  /* pool1_pad + pool1_pool                                                    */
+#define ADAPT_OP_GAP 3      /* avg_pool (GlobalAveragePooling2D)                                         */
+#define ADAPT_OP_SOFTMAX 4  /* softmax activation of `predictions`                                       */
+
+/* tensor roles inside a stage program */
+#define ADAPT_T_INTERNAL 0  /* library-owned scratch activation                       */
+#define ADAPT_T_INPUT 1     /* stage input, caller-owned, bound per slot (bind_io)    */
+#define ADAPT_T_OUTPUT 2    /* stage output, caller-owned, bound per slot (bind_io)   */
+
+/* tensor element types */
+#define ADAPT_DT_WORK 0     /* bf16 in ADAPT_MODE_BF16, fp32 in ADAPT_MODE_FP32_CHECK */
+#define ADAPT_DT_F32 1
+
+/* One Conv2D/Dense layer's parameters in Keras layout (what `get_weights()` returns,
+ * reference src/dispatcher.py:243) with BatchNormalization already folded on the host into
+ * a per-output-channel fp32 scale and bias:  y = conv(x) * scale + bias. */
+typedef struct adapt_weight_desc {
+    const float* kernel; /* host, HWIO: [kh][kw][cin][cout] fp32 (Dense: [in][out])  */
+    const float* scale;  /* host, [cout]                                             */
+    const float* bias;   /* host, [cout]                                             */
+    int32_t kh, kw, cin, cout;
+} adapt_weight_desc;
+
+typedef struct adapt_tensor_desc {
+    int64_t elems_per_image; /* stored elements per image (channel padding included) */
+    int32_t dtype;           /* ADAPT_DT_*                                           */
+    int32_t role;            /* ADAPT_T_*                                            */
+} adapt_tensor_desc;
+
+typedef struct adapt_op_desc {
+    int32_t kind;                    /* ADAPT_OP_*                                             */
+    int32_t in_tensor;               /* index into the tensor table                            */
+    int32_t res_tensor;              /* residual (shortcut) input of a fused Add, or -1        */
+    int32_t out_tensor;
+    int32_t H, W, Cin;               /* input spatial size and STORED channels per pixel       */
+    int32_t Ho, Wo, Cout;            /* output spatial size and channels                       */
+    int32_t kh, kw, stride, pad;     /* filter / pool window, stride, symmetric zero padding   */
+    int32_t relu;                    /* apply ReLU in the epilogue                             */
+    int32_t weight;                  /* index into the weight table (CONV) or -1               */
+    int32_t out_f32;                 /* CONV: write fp32 instead of the working dtype (logits) */
+    int32_t reserved;
+} adapt_op_desc;
+
+typedef struct adapt_stage adapt_stage_t;
+
+/* Library / device probes.  adapt_device_count() is 0 on a machine without a GPU. */
+const char* adapt_version(void);
+const char* adapt_last_error(void);
+int adapt_device_count(void);
+
+/* Replaces: `model_from_json` + `set_weights` on the worker (reference src/node.py:40,45,77-78)
+ * and the weight shipping of `_send_full_configuration` (reference src/dispatcher.py:223-264).
+ * Uploads ALL layers' weights of the model to `device` once (so a later re-slice is metadata
+ * only) and installs the stage program `ops` over `tensors` (the layer range (start, end] that
+ * `DEFER._partition` / `construct_model` would cut, reference src/dispatcher.py:39-53,
+ * src/dag_util.py:50-62). */
+int adapt_stage_create(int device, int dtype_mode, int max_batch, const adapt_weight_desc* weights, int n_weights,
+                       const adapt_tensor_desc* tensors, int n_tensors, const adapt_op_desc* ops, int n_ops,
+                       adapt_stage_t** out);
+
+/* Replaces: re-configuring a worker with another partition (`_send_full_configuration`,
+ * reference src/dispatcher.py:223-264) after a failure; weights are already resident. */
+int adapt_stage_reslice(adapt_stage_t* stage, const adapt_tensor_desc* tensors, int n_tensors,
+                        const adapt_op_desc* ops, int n_ops);
+
+/* Replaces: the socket payload hand-off into / out of `model.predict` (reference
+ * src/node.py:137-179).  Binds the caller-owned input and output buffers of double-buffer
+ * `slot` (0 or 1).  `out_ptr` may be a peer-mapped pointer on the next stage's GPU: the last
+ * layer's epilogue then stores the cut tensor straight over NVLink. */
+int adapt_stage_bind_io(adapt_stage_t* stage, int slot, void* in_ptr, void* out_ptr);
+
+/* Replaces: `model.predict(inpt)` (reference src/node.py:177).  Asynchronously runs the stage
+ * program on `batch` images from slot's input buffer into slot's output buffer on `stream`. */
+int adapt_stage_enqueue(adapt_stage_t* stage, int slot, int batch, void* stream);
+
+/* Debug/test tap: copy an INTERNAL tensor (first `bytes` bytes) to host memory after
+ * synchronising `stream`.  No reference counterpart (the reference never inspects activations). */
+int adapt_stage_read_tensor(adapt_stage_t* stage, int tensor, void* host_dst, size_t bytes, void* stream);
+
+/* Number of kernel launches one enqueue() of `batch` images performs (for bench accounting). */
+int adapt_stage_num_launches(adapt_stage_t* stage, int batch);
+
+void adapt_stage_destroy(adapt_stage_t* stage);
+
+/* Single-layer entry point (kernel-level parity tests and micro-benchmarks):
+ *   out = act((conv(in, w) * scale + bias) (+ residual)),  all pointers DEVICE pointers.
+ *   in   : bf16 NHWC [batch][H][W][Cin]      (Cin a multiple of 8)
+ *   w    : bf16      [Cout][kh][kw][Cin]
+ *   out  : bf16 NHWC [batch][Ho][Wo][Cout], or fp32 when out_is_f32 != 0
+ * a_mode: -1 auto, 0 tiled TMA, 1 im2col TMA, 2 software gather.  block_n: 0 auto, 64/128/256.
+ * Stands in for one Conv2D+BatchNormalization(+Add)(+ReLU) group inside `model.predict`
+ * (reference src/node.py:177). */
+int adapt_conv2d_bf16(int device, const void* in, const void* w, const float* scale, const float* bias,
+                      const void* residual, void* out, int out_is_f32, int batch, int H, int W, int Cin, int Cout,
+                      int kh, int kw, int stride, int pad, int relu, int a_mode, int block_n, void* stream);
+
+/* ---- stage-to-stage hand-off plumbing (replaces the TCP framing of reference
+ *      src/node_state.py:39-161 and the routing of src/dispatcher.py:176-220) ---- */
+
+/* cudaMalloc / cudaFree on `device` (cut buffers and flags must be raw allocations to be
+ * exportable over CUDA IPC). */
+int adapt_device_alloc(int device, size_t bytes, void** out);
+int adapt_device_free(int device, void* ptr);
+/* Enable peer access device a <-> b (same process). */
+int adapt_peer_enable(int a, int b);
+/* CUDA IPC: export a raw allocation as a 64-byte handle / map a peer process's handle. */
+int adapt_ipc_export(int device, void* ptr, void* handle64_out);
+int adapt_ipc_import(int device, const void* handle64, void** out);
+int adapt_ipc_close(int device, void* ptr);
+/* Stream-ordered 32-bit flag write / wait-until->= on (possibly peer-mapped) device memory. */
+int adapt_stream_write_flag(int device, void* stream, void* flag_ptr, uint32_t value);
+int adapt_stream_wait_flag_geq(int device, void* stream, void* flag_ptr, uint32_t value);
+/* Async copies on `stream` (host memory should be pinned). */
+int adapt_memcpy_h2d(int device, void* dst, const void* src, size_t bytes, void* stream);
+int adapt_memcpy_d2h(int device, void* dst, const void* src, size_t bytes, void* stream);
+int adapt_memcpy_d2d(int device, void* dst, const void* src, size_t bytes, void* stream);
+int adapt_memset(int device, void* dst, int value, size_t bytes, void* stream);
+int adapt_stream_sync(int device, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ADAPT_B200_H_ */

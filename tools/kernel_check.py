@@ -1,0 +1,200 @@
+"""Developer harness (GPU): exercise adapt_conv2d_bf16 over shapes x A-modes x tile widths and
+compare with an fp32 torch convolution of the same bf16-rounded operands.  Each group runs in
+its own subprocess so that a faulting kernel cannot poison the other groups.
+
+    python tools/kernel_check.py            # all groups
+    python tools/kernel_check.py --group tiled
+"""
+from __future__ import annotations
+
+import argparse
+import importlib.util
+import json
+import os
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "adaptive-deep-learning-architecture-for-parallel-and-fault-tolerant-inference_b200")
+
+
+def load_native():
+    spec = importlib.util.spec_from_file_location("adapt_native", os.path.join(PKG, "_native.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+# (name, B, H, W, Cin, Cout, k, stride, pad, residual, relu, out_f32)
+CASES = {
+    "tiled": [
+        ("t64", 2, 14, 14, 64, 64, 1, 1, 0, 0, 0, 0),
+        ("t_res_relu", 2, 14, 14, 64, 64, 1, 1, 0, 1, 1, 0),
+        ("t256to128", 4, 28, 28, 256, 128, 1, 1, 0, 1, 1, 0),
+        ("t128to512", 4, 28, 28, 128, 512, 1, 1, 0, 1, 1, 0),
+        ("t_bigM", 32, 56, 56, 64, 256, 1, 1, 0, 0, 1, 0),
+        ("t_k2048", 8, 7, 7, 2048, 512, 1, 1, 0, 0, 1, 0),
+        ("fc", 128, 1, 1, 2048, 1000, 1, 1, 0, 0, 0, 1),
+        ("fc_b1", 1, 1, 1, 2048, 1000, 1, 1, 0, 0, 0, 1),
+    ],
+    "im2col": [
+        ("c3_14", 2, 14, 14, 64, 64, 3, 1, 1, 0, 1, 0),
+        ("c3_28", 3, 28, 28, 128, 128, 3, 1, 1, 0, 1, 0),
+        ("c3_7_straddle", 5, 7, 7, 512, 512, 3, 1, 1, 0, 1, 0),
+        ("c3_56", 2, 56, 56, 64, 64, 3, 1, 1, 0, 1, 0),
+        ("s2_56", 2, 56, 56, 256, 128, 1, 2, 0, 0, 1, 0),
+        ("s2_28_512", 3, 28, 28, 512, 1024, 1, 2, 0, 0, 0, 0),
+        ("s2_14", 5, 14, 14, 1024, 512, 1, 2, 0, 0, 1, 0),
+        ("c7s2", 2, 32, 32, 64, 64, 7, 2, 3, 0, 1, 0),
+        ("c3_small_b1", 1, 7, 7, 64, 64, 3, 1, 1, 0, 0, 0),
+    ],
+    "gather": [
+        ("g_c3_14", 2, 14, 14, 64, 64, 3, 1, 1, 0, 1, 0),
+        ("g_c3_7_straddle", 5, 7, 7, 512, 512, 3, 1, 1, 0, 1, 0),
+        ("g_s2_56", 2, 56, 56, 256, 128, 1, 2, 0, 0, 1, 0),
+        ("g_stem", 2, 224, 224, 8, 64, 7, 2, 3, 0, 1, 0),
+        ("g_cin24", 2, 20, 20, 24, 64, 3, 1, 1, 1, 1, 0),
+    ],
+}
+MODE = {"tiled": 0, "im2col": 1, "gather": 2}
+
+
+def run_group(group: str) -> int:
+    import torch
+    import torch.nn.functional as F
+
+    nat = load_native()
+    lib = nat.lib()
+    dev = torch.device("cuda:0")
+    torch.manual_seed(0)
+    worst = 0.0
+    ok_all = True
+    for (name, B, H, W, Cin, Cout, k, stride, pad, use_res, relu, out_f32) in CASES[group]:
+        for bn in (64, 128, 256):
+            if bn > 64 and Cout < bn:
+                continue
+            x = torch.randn(B, H, W, Cin, device=dev).to(torch.bfloat16)
+            w = (torch.randn(Cout, k, k, Cin, device=dev) / (k * k * Cin) ** 0.5).to(torch.bfloat16)
+            scale = torch.rand(Cout, device=dev) + 0.5
+            bias = torch.randn(Cout, device=dev)
+            Ho = (H + 2 * pad - k) // stride + 1
+            Wo = (W + 2 * pad - k) // stride + 1
+            res = torch.randn(B, Ho, Wo, Cout, device=dev).to(torch.bfloat16) if use_res else None
+            out = torch.full((B, Ho, Wo, Cout), float("nan"), device=dev,
+                             dtype=torch.float32 if out_f32 else torch.bfloat16)
+            torch.cuda.synchronize()
+            rc = lib.adapt_conv2d_bf16(0, x.data_ptr(), w.data_ptr(), scale.data_ptr(), bias.data_ptr(),
+                                       res.data_ptr() if use_res else None, out.data_ptr(), out_f32, B, H, W, Cin,
+                                       Cout, k, k, stride, pad, relu, MODE[group], bn, None)
+            if rc != 0:
+                print(json.dumps({"case": name, "bn": bn, "error": lib.adapt_last_error().decode()}), flush=True)
+                ok_all = False
+                continue
+            try:
+                torch.cuda.synchronize()
+            except Exception as e:  # noqa: BLE001
+                print(json.dumps({"case": name, "bn": bn, "cuda_error": str(e)[:300]}), flush=True)
+                return 2
+            ref = F.conv2d(x.float().permute(0, 3, 1, 2), w.float().permute(0, 3, 1, 2), stride=stride, padding=pad)
+            ref = ref.permute(0, 2, 3, 1) * scale + bias
+            if use_res:
+                ref = ref + res.float()
+            if relu:
+                ref = ref.clamp_min(0)
+            got = out.float()
+            err = (got - ref).abs()
+            tol = 2e-2 * ref.abs().clamp_min(1.0) if not out_f32 else 2e-3 * ref.abs().clamp_min(1.0)
+            bad = int((~(err <= tol)).sum().item())
+            mx = float(err.max().item()) if bad == 0 or not torch.isnan(err).any() else float("nan")
+            worst = max(worst, mx if mx == mx else 1e9)
+            rec = {"case": name, "bn": bn, "M": B * Ho * Wo, "max_abs_err": mx, "bad": bad,
+                   "nan": int(torch.isnan(got).sum().item())}
+            if bad:
+                ok_all = False
+                idx = torch.nonzero(~(err <= tol))[:4].tolist()
+                rec["first_bad"] = idx
+            print(json.dumps(rec), flush=True)
+    print(json.dumps({"group": group, "ok": ok_all, "worst": worst}), flush=True)
+    return 0 if ok_all else 1
+
+
+def run_perf() -> int:
+    import torch
+
+    nat = load_native()
+    lib = nat.lib()
+    dev = torch.device("cuda:0")
+    B = 128
+    layers = [
+        ("conv2_1x1_64_256", 56, 56, 64, 256, 1, 1, 0),
+        ("conv2_1x1_256_64", 56, 56, 256, 64, 1, 1, 0),
+        ("conv2_3x3_64", 56, 56, 64, 64, 3, 1, 1),
+        ("conv3_3x3_128", 28, 28, 128, 128, 3, 1, 1),
+        ("conv3_1x1_128_512", 28, 28, 128, 512, 1, 1, 0),
+        ("conv4_3x3_256", 14, 14, 256, 256, 3, 1, 1),
+        ("conv4_1x1_1024_256", 14, 14, 1024, 256, 1, 1, 0),
+        ("conv4_1x1_256_1024", 14, 14, 256, 1024, 1, 1, 0),
+        ("conv5_3x3_512", 7, 7, 512, 512, 3, 1, 1),
+        ("conv5_1x1_512_2048", 7, 7, 512, 2048, 1, 1, 0),
+        ("conv3_s2_256_128", 56, 56, 256, 128, 1, 2, 0),
+        ("stem_gather", 224, 224, 8, 64, 7, 2, 3),
+    ]
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+    for (name, H, W, Cin, Cout, k, stride, pad) in layers:
+        x = torch.randn(B, H, W, Cin, device=dev).to(torch.bfloat16)
+        w = (torch.randn(Cout, k, k, Cin, device=dev) / (k * k * Cin) ** 0.5).to(torch.bfloat16)
+        scale = torch.ones(Cout, device=dev)
+        bias = torch.zeros(Cout, device=dev)
+        Ho = (H + 2 * pad - k) // stride + 1
+        Wo = (W + 2 * pad - k) // stride + 1
+        out = torch.empty(B, Ho, Wo, Cout, device=dev, dtype=torch.bfloat16)
+        for bn in (64, 128, 256):
+            if bn > 64 and Cout < bn:
+                continue
+            times = []
+            for it in range(6):
+                flush.zero_()
+                e0 = torch.cuda.Event(enable_timing=True)
+                e1 = torch.cuda.Event(enable_timing=True)
+                e0.record()
+                rc = lib.adapt_conv2d_bf16(0, x.data_ptr(), w.data_ptr(), scale.data_ptr(), bias.data_ptr(), None,
+                                           out.data_ptr(), 0, B, H, W, Cin, Cout, k, k, stride, pad, 1, -1, bn,
+                                           torch.cuda.current_stream().cuda_stream)
+                e1.record()
+                torch.cuda.synchronize()
+                if rc != 0:
+                    print(json.dumps({"layer": name, "bn": bn, "error": lib.adapt_last_error().decode()}))
+                    break
+                if it >= 2:
+                    times.append(e0.elapsed_time(e1))
+            if not times:
+                continue
+            ms = sum(times) / len(times)
+            M = B * Ho * Wo
+            flops = 2.0 * M * Cout * k * k * Cin
+            bytes_ = 2.0 * (B * H * W * Cin + M * Cout + Cout * k * k * Cin)
+            print(json.dumps({"layer": name, "bn": bn, "ms": round(ms, 4), "tflops": round(flops / ms / 1e9, 1),
+                              "gbs": round(bytes_ / ms / 1e6, 1)}), flush=True)
+    return 0
+
+
+def main() -> int:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--group", default=None)
+    args = ap.parse_args()
+    if args.group == "perf":
+        return run_perf()
+    if args.group:
+        return run_group(args.group)
+    rc_all = 0
+    for g in ("tiled", "im2col", "gather", "perf"):
+        t0 = time.time()
+        p = subprocess.run([sys.executable, os.path.abspath(__file__), "--group", g], timeout=600)
+        print(f"== group {g}: exit {p.returncode} in {time.time() - t0:.1f}s", flush=True)
+        rc_all |= p.returncode
+    return rc_all
+
+
+if __name__ == "__main__":
+    sys.exit(main())
