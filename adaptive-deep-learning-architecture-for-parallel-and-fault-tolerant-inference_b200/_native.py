@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libadapt_b200.so")
 # mirror of include/adapt_b200.h -------------------------------------------------------------
 OK, EINVAL, ECUDA, ENODEV, ENOMEM, ESTATE = 0, -1, -2, -3, -4, -5
 MODE_BF16, MODE_FP32_CHECK = 0, 1
-OP_INGEST, OP_CONV, OP_MAXPOOL, OP_GAP, OP_SOFTMAX = 0, 1, 2, 3, 4
+OP_INGEST, OP_CONV, OP_MAXPOOL, OP_GAP, OP_SOFTMAX, OP_AFFINE, OP_ZEROPAD = 0, 1, 2, 3, 4, 5, 6
 T_INTERNAL, T_INPUT, T_OUTPUT = 0, 1, 2
 DT_WORK, DT_F32 = 0, 1
 

@@ -394,7 +394,12 @@ int install_program(adapt_stage* st, const adapt_tensor_desc* tensors, int n_ten
             if (w.kh != o.kh || w.kw != o.kw || w.cout != o.Cout || cin_expect != o.Cin)
                 return fail(ADAPT_EINVAL, "op %d: geometry %dx%dx%d->%d does not match weight %d (%dx%dx%d->%d)", i,
                             o.kh, o.kw, o.Cin, o.Cout, o.weight, w.kh, w.kw, cin_expect, w.cout);
-        } else if (o.kind < ADAPT_OP_INGEST || o.kind > ADAPT_OP_SOFTMAX) {
+        } else if (o.kind == ADAPT_OP_AFFINE) {
+            if (o.weight >= (int)st->weights.size()) return fail(ADAPT_EINVAL, "op %d: weight index out of range", i);
+            if (o.weight >= 0 && st->weights[o.weight].cout != o.Cin)
+                return fail(ADAPT_EINVAL, "op %d: affine channels %d != weight %d", i, o.Cin, st->weights[o.weight].cout);
+            if (o.Cin % 8 != 0) return fail(ADAPT_EINVAL, "op %d: affine needs C %% 8 == 0", i);
+        } else if (o.kind < ADAPT_OP_INGEST || o.kind > ADAPT_OP_ZEROPAD) {
             return fail(ADAPT_EINVAL, "op %d: unknown kind %d", i, o.kind);
         }
     }
@@ -515,6 +520,36 @@ int run_steps(adapt_stage* st, const std::vector<Step>& steps, cudaStream_t stre
                     reinterpret_cast<const float*>(s.in), reinterpret_cast<float*>(s.out), B, o.Cin);
                 break;
             }
+            case ADAPT_OP_AFFINE: {
+                const long long vecs = (long long)B * o.H * o.W * o.Cin / 8;
+                const float* sc = o.weight >= 0 ? st->weights[o.weight].scale : nullptr;
+                const float* bi = o.weight >= 0 ? st->weights[o.weight].bias : nullptr;
+                const int threads = 256;
+                const unsigned blocks = (unsigned)((vecs + threads - 1) / threads);
+                if (st->mode == ADAPT_MODE_BF16)
+                    adapt::affine_relu_kernel<__nv_bfloat16><<<blocks, threads, 0, stream>>>(
+                        reinterpret_cast<const __nv_bfloat16*>(s.in), reinterpret_cast<__nv_bfloat16*>(s.out), sc, bi,
+                        vecs, o.Cin, o.relu);
+                else
+                    adapt::affine_relu_kernel<float><<<blocks, threads, 0, stream>>>(
+                        reinterpret_cast<const float*>(s.in), reinterpret_cast<float*>(s.out), sc, bi, vecs, o.Cin,
+                        o.relu);
+                break;
+            }
+            case ADAPT_OP_ZEROPAD: {
+                const long long total = (long long)B * (o.H + 2 * o.pad) * (o.W + 2 * o.pad) * o.Cin;
+                const int threads = 256;
+                const unsigned blocks = (unsigned)((total + threads - 1) / threads);
+                if (st->mode == ADAPT_MODE_BF16)
+                    adapt::zeropad_kernel<__nv_bfloat16><<<blocks, threads, 0, stream>>>(
+                        reinterpret_cast<const __nv_bfloat16*>(s.in), reinterpret_cast<__nv_bfloat16*>(s.out), B, o.H,
+                        o.W, o.Cin, o.pad);
+                else
+                    adapt::zeropad_kernel<float><<<blocks, threads, 0, stream>>>(
+                        reinterpret_cast<const float*>(s.in), reinterpret_cast<float*>(s.out), B, o.H, o.W, o.Cin,
+                        o.pad);
+                break;
+            }
             default:
                 return fail(ADAPT_EINVAL, "unknown op kind %d", s.kind);
         }
@@ -527,7 +562,8 @@ int upload_weights(adapt_stage* st, const adapt_weight_desc* weights, int n_weig
     st->weights.resize(n_weights);
     for (int i = 0; i < n_weights; ++i) {
         const adapt_weight_desc& h = weights[i];
-        if (!h.kernel || !h.scale || !h.bias || h.kh <= 0 || h.kw <= 0 || h.cin <= 0 || h.cout <= 0)
+        const bool affine_only = h.kernel == nullptr && h.kh == 0 && h.kw == 0;
+        if (!h.scale || !h.bias || h.cout <= 0 || (!affine_only && (!h.kernel || h.kh <= 0 || h.kw <= 0 || h.cin <= 0)))
             return fail(ADAPT_EINVAL, "weight %d: bad descriptor", i);
         WeightDev& w = st->weights[i];
         w.kh = h.kh; w.kw = h.kw; w.cin = h.cin; w.cout = h.cout;
@@ -539,6 +575,7 @@ int upload_weights(adapt_stage* st, const adapt_weight_desc* weights, int n_weig
         CUDA_TRY(cudaMemset(w.bias, 0, cout_pad * sizeof(float)));
         CUDA_TRY(cudaMemcpy(w.scale, h.scale, (size_t)h.cout * sizeof(float), cudaMemcpyHostToDevice));
         CUDA_TRY(cudaMemcpy(w.bias, h.bias, (size_t)h.cout * sizeof(float), cudaMemcpyHostToDevice));
+        if (affine_only) continue;
         if (st->mode == ADAPT_MODE_BF16) {
             // HWIO fp32 -> [cout][kh][kw][cin_store] bf16 (round-to-nearest-even), zero channel padding
             const size_t K = (size_t)h.kh * h.kw * w.cin_store;

@@ -117,6 +117,49 @@ __global__ void maxpool_zeropad_kernel(const T* __restrict__ in, T* __restrict__
 }
 
 // ---------------------------------------------------------------------------------------------
+// Stand-alone per-channel affine (+ReLU): a BatchNormalization / Activation that a cut separated
+// from its convolution.  scale == nullptr means ReLU only.  8 channels per thread.
+template <typename T>
+__global__ void affine_relu_kernel(const T* __restrict__ in, T* __restrict__ out, const float* __restrict__ scale,
+                                   const float* __restrict__ bias, long long num_vecs, int C, int relu) {
+    const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+    if (i >= num_vecs) return;
+    const int c0 = static_cast<int>((i * 8) % C);
+    Vec8<T> v;
+    v.load(in + i * 8);
+    float f[8];
+    v.to_float(f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        if (scale != nullptr) f[j] = fmaf(f[j], __ldg(scale + c0 + j), __ldg(bias + c0 + j));
+        if (relu) f[j] = fmaxf(f[j], 0.0f);
+    }
+    Vec8<T> o;
+    o.from_float(f);
+    o.store(out + i * 8);
+}
+
+// Stand-alone ZeroPadding2D: (B,H,W,C) -> (B,H+2p,W+2p,C).  Rare path (a cut exactly at a padding
+// layer), so a plain element-per-thread kernel.
+template <typename T>
+__global__ void zeropad_kernel(const T* __restrict__ in, T* __restrict__ out, int B, int H, int W, int C, int pad) {
+    const int Hp = H + 2 * pad, Wp = W + 2 * pad;
+    const long long total = static_cast<long long>(B) * Hp * Wp * C;
+    const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+    if (i >= total) return;
+    const int c = static_cast<int>(i % C);
+    long long pix = i / C;
+    const int w = static_cast<int>(pix % Wp);
+    pix /= Wp;
+    const int h = static_cast<int>(pix % Hp);
+    const int b = static_cast<int>(pix / Hp);
+    const int hi = h - pad, wi = w - pad;
+    T v = static_cast<T>(0.0f);
+    if (hi >= 0 && hi < H && wi >= 0 && wi < W) v = in[((static_cast<long long>(b) * H + hi) * W + wi) * C + c];
+    out[i] = v;
+}
+
+// ---------------------------------------------------------------------------------------------
 // Global average pool: (B, HW, C) -> (B, C).  One thread per (b, 8 channels); consecutive threads
 // read consecutive 16-byte vectors of the same pixel (coalesced), fp32 accumulation.
 template <typename TIn, typename TOut>

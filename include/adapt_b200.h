@@ -44,6 +44,9 @@ extern "C" {
 #define ADAPT_OP_MAXPOOL 2  /* pool1_pad + pool1_pool                                                    */
 #define ADAPT_OP_GAP 3      /* avg_pool (GlobalAveragePooling2D)                                         */
 #define ADAPT_OP_SOFTMAX 4  /* softmax activation of `predictions`                                       */
+#define ADAPT_OP_AFFINE 5   /* stand-alone BatchNormalization and/or ReLU (a cut separated it from its  */
+                            /* convolution): y = relu?(x * scale[c] + bias[c]); weight = -1: ReLU only  */
+#define ADAPT_OP_ZEROPAD 6  /* stand-alone ZeroPadding2D (a cut at conv1_pad / pool1_pad)               */
 
 /* tensor roles inside a stage program */
 #define ADAPT_T_INTERNAL 0  /* library-owned scratch activation                       */
@@ -58,7 +61,8 @@ extern "C" {
  * reference src/dispatcher.py:243) with BatchNormalization already folded on the host into
  * a per-output-channel fp32 scale and bias:  y = conv(x) * scale + bias. */
 typedef struct adapt_weight_desc {
-    const float* kernel; /* host, HWIO: [kh][kw][cin][cout] fp32 (Dense: [in][out])  */
+    const float* kernel; /* host, HWIO: [kh][kw][cin][cout] fp32 (Dense: [in][out]);  */
+                         /* NULL with kh = kw = 0: scale/bias only (ADAPT_OP_AFFINE)  */
     const float* scale;  /* host, [cout]                                             */
     const float* bias;   /* host, [cout]                                             */
     int32_t kh, kw, cin, cout;
