@@ -70,6 +70,7 @@ SYMBOLS = {
                                 C.POINTER(_VP)]),
     "adapt_stage_reslice": (_I, [_VP, C.POINTER(TensorDesc), _I, C.POINTER(OpDesc), _I]),
     "adapt_stage_bind_io": (_I, [_VP, _I, _VP, _VP]),
+    "adapt_stage_prepare": (_I, [_VP, _I, _I]),
     "adapt_stage_enqueue": (_I, [_VP, _I, _I, _VP]),
     "adapt_stage_read_tensor": (_I, [_VP, _I, _VP, _SZ, _VP]),
     "adapt_stage_num_launches": (_I, [_VP, _I]),
@@ -89,6 +90,18 @@ SYMBOLS = {
     "adapt_memcpy_d2d": (_I, [_I, _VP, _VP, _SZ, _VP]),
     "adapt_memset": (_I, [_I, _VP, _I, _SZ, _VP]),
     "adapt_stream_sync": (_I, [_I, _VP]),
+    "adapt_heartbeat_start": (_I, [_VP, _I, C.POINTER(_VP)]),
+    "adapt_heartbeat_stop": (_I, [_VP]),
+    "adapt_stream_query": (_I, [_I, _VP, C.POINTER(_I)]),
+    "adapt_host_register": (_I, [_I, _VP, _SZ, C.POINTER(_VP)]),
+    "adapt_host_unregister": (_I, [_I, _VP]),
+    "adapt_stream_create": (_I, [_I, C.POINTER(_VP)]),
+    "adapt_stream_destroy": (_I, [_I, _VP]),
+    "adapt_event_create": (_I, [_I, C.POINTER(_VP)]),
+    "adapt_event_record": (_I, [_I, _VP, _VP]),
+    "adapt_event_sync": (_I, [_I, _VP]),
+    "adapt_event_elapsed_ms": (_I, [_I, _VP, _VP, C.POINTER(C.c_float)]),
+    "adapt_event_destroy": (_I, [_I, _VP]),
 }
 
 

@@ -6,6 +6,11 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 
+#include <atomic>
+#include <chrono>
+#include <thread>
+#include <time.h>
+
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -675,14 +680,13 @@ int adapt_stage_bind_io(adapt_stage_t* st, int slot, void* in_ptr, void* out_ptr
     return ADAPT_OK;
 }
 
-int adapt_stage_enqueue(adapt_stage_t* st, int slot, int batch, void* stream_v) {
-    if (!st || slot < 0 || slot > 1) return fail(ADAPT_EINVAL, "enqueue: bad argument");
-    if (batch <= 0 || batch > st->max_batch) return fail(ADAPT_EINVAL, "enqueue: batch %d not in [1, %d]", batch,
-                                                         st->max_batch);
-    if (st->ops.empty()) return fail(ADAPT_ESTATE, "enqueue: no program installed");
+namespace {
+int get_plan(adapt_stage_t* st, int slot, int batch, Plan** out) {
+    if (!st || slot < 0 || slot > 1) return fail(ADAPT_EINVAL, "stage call: bad argument");
+    if (batch <= 0 || batch > st->max_batch) return fail(ADAPT_EINVAL, "batch %d not in [1, %d]", batch, st->max_batch);
+    if (st->ops.empty()) return fail(ADAPT_ESTATE, "no program installed");
     int rc = require_device(st->device);
     if (rc) return rc;
-    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
     auto it = st->plans.find(batch);
     if (it == st->plans.end()) {
         std::unique_ptr<Plan> p(new Plan());
@@ -691,33 +695,54 @@ int adapt_stage_enqueue(adapt_stage_t* st, int slot, int batch, void* stream_v) 
     }
     Plan* plan = it->second.get();
     if (!plan->built[slot]) {
-        rc = build_steps(st, plan, slot);
+        rc = build_steps(st, plan, slot);  // host-only work: tensor-map encodes
         if (rc) return rc;
     }
-    if (!st->use_graph) return run_steps(st, plan->steps[slot], stream);
-    if (!plan->exec[slot]) {
-        cudaStream_t cap;
-        CUDA_TRY(cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking));
-        cudaGraph_t graph = nullptr;
-        cudaError_t e = cudaStreamBeginCapture(cap, cudaStreamCaptureModeThreadLocal);
-        if (e != cudaSuccess) {
-            cudaStreamDestroy(cap);
-            return fail(ADAPT_ECUDA, "cudaStreamBeginCapture: %s", cudaGetErrorString(e));
-        }
-        rc = run_steps(st, plan->steps[slot], cap);
-        e = cudaStreamEndCapture(cap, &graph);
-        cudaStreamDestroy(cap);
-        if (rc) {
-            if (graph) cudaGraphDestroy(graph);
-            return rc;
-        }
-        if (e != cudaSuccess) return fail(ADAPT_ECUDA, "cudaStreamEndCapture: %s", cudaGetErrorString(e));
-        e = cudaGraphInstantiate(&plan->exec[slot], graph, 0);
-        cudaGraphDestroy(graph);
-        if (e != cudaSuccess) return fail(ADAPT_ECUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e));
-    }
-    CUDA_TRY(cudaGraphLaunch(plan->exec[slot], stream));
+    *out = plan;
     return ADAPT_OK;
+}
+}  // namespace
+
+int adapt_stage_prepare(adapt_stage_t* st, int slot, int batch) {
+    Plan* plan = nullptr;
+    int rc = get_plan(st, slot, batch, &plan);
+    if (rc) return rc;
+    if (!st->use_graph || plan->exec[slot]) return ADAPT_OK;
+    cudaStream_t cap;
+    CUDA_TRY(cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking));
+    cudaGraph_t graph = nullptr;
+    cudaError_t e = cudaStreamBeginCapture(cap, cudaStreamCaptureModeThreadLocal);
+    if (e != cudaSuccess) {
+        cudaStreamDestroy(cap);
+        return fail(ADAPT_ECUDA, "cudaStreamBeginCapture: %s", cudaGetErrorString(e));
+    }
+    rc = run_steps(st, plan->steps[slot], cap);
+    e = cudaStreamEndCapture(cap, &graph);
+    cudaStreamDestroy(cap);
+    if (rc) {
+        if (graph) cudaGraphDestroy(graph);
+        return rc;
+    }
+    if (e != cudaSuccess) return fail(ADAPT_ECUDA, "cudaStreamEndCapture: %s", cudaGetErrorString(e));
+    e = cudaGraphInstantiate(&plan->exec[slot], graph, 0);
+    cudaGraphDestroy(graph);
+    if (e != cudaSuccess) return fail(ADAPT_ECUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e));
+    return ADAPT_OK;
+}
+
+int adapt_stage_enqueue(adapt_stage_t* st, int slot, int batch, void* stream_v) {
+    Plan* plan = nullptr;
+    int rc = get_plan(st, slot, batch, &plan);
+    if (rc) return rc;
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
+    // a batch size that was prepared runs as one CUDA graph; any other runs as plain launches
+    // (graph capture / instantiation never happens here: it can synchronise the device, which
+    // must not occur while peer stages are blocked on this stage's flags)
+    if (plan->exec[slot]) {
+        CUDA_TRY(cudaGraphLaunch(plan->exec[slot], stream));
+        return ADAPT_OK;
+    }
+    return run_steps(st, plan->steps[slot], stream);
 }
 
 int adapt_stage_read_tensor(adapt_stage_t* st, int tensor, void* host_dst, size_t bytes, void* stream_v) {
@@ -898,6 +923,125 @@ int adapt_stream_sync(int device, void* stream) {
     int rc = require_device(device);
     if (rc) return rc;
     CUDA_TRY(cudaStreamSynchronize(reinterpret_cast<cudaStream_t>(stream)));
+    return ADAPT_OK;
+}
+
+struct adapt_heartbeat {
+    std::thread th;
+    std::atomic<bool> stop{false};
+};
+
+int adapt_heartbeat_start(volatile int64_t* word, int interval_us, void** handle_out) {
+    if (!word || interval_us <= 0 || !handle_out) return fail(ADAPT_EINVAL, "heartbeat_start: bad argument");
+    adapt_heartbeat* hb = new adapt_heartbeat();
+    hb->th = std::thread([hb, word, interval_us]() {
+        while (!hb->stop.load(std::memory_order_relaxed)) {
+            timespec ts;
+            clock_gettime(CLOCK_MONOTONIC, &ts);
+            __atomic_store_n(const_cast<int64_t*>(word), (int64_t)ts.tv_sec * 1000000000LL + ts.tv_nsec, __ATOMIC_RELEASE);
+            std::this_thread::sleep_for(std::chrono::microseconds(interval_us));
+        }
+    });
+    *handle_out = hb;
+    return ADAPT_OK;
+}
+
+int adapt_heartbeat_stop(void* handle) {
+    if (!handle) return ADAPT_OK;
+    adapt_heartbeat* hb = reinterpret_cast<adapt_heartbeat*>(handle);
+    hb->stop.store(true);
+    if (hb->th.joinable()) hb->th.join();
+    delete hb;
+    return ADAPT_OK;
+}
+
+int adapt_stream_query(int device, void* stream, int* busy_out) {
+    if (!busy_out) return fail(ADAPT_EINVAL, "stream_query: null");
+    int rc = require_device(device);
+    if (rc) return rc;
+    cudaError_t e = cudaStreamQuery(reinterpret_cast<cudaStream_t>(stream));
+    if (e == cudaSuccess) {
+        *busy_out = 0;
+    } else if (e == cudaErrorNotReady) {
+        cudaGetLastError();
+        *busy_out = 1;
+    } else {
+        return fail(ADAPT_ECUDA, "cudaStreamQuery: %s", cudaGetErrorString(e));
+    }
+    return ADAPT_OK;
+}
+int adapt_host_register(int device, void* host_ptr, size_t bytes, void** dev_ptr_out) {
+    if (!host_ptr || !bytes || !dev_ptr_out) return fail(ADAPT_EINVAL, "host_register: bad argument");
+    int rc = require_device(device);
+    if (rc) return rc;
+    // several workers of one process share the result ring: the second registration is a no-op
+    cudaError_t e = cudaHostRegister(host_ptr, bytes, cudaHostRegisterPortable | cudaHostRegisterMapped);
+    if (e == cudaErrorHostMemoryAlreadyRegistered) {
+        cudaGetLastError();
+    } else if (e != cudaSuccess) {
+        return fail(ADAPT_ECUDA, "cudaHostRegister failed: %s", cudaGetErrorString(e));
+    }
+    CUDA_TRY(cudaHostGetDevicePointer(dev_ptr_out, host_ptr, 0));
+    return ADAPT_OK;
+}
+int adapt_host_unregister(int device, void* host_ptr) {
+    int rc = require_device(device);
+    if (rc) return rc;
+    cudaError_t e = cudaHostUnregister(host_ptr);
+    if (e == cudaErrorHostMemoryNotRegistered) {
+        cudaGetLastError();  // another worker of this process already released the shared range
+    } else if (e != cudaSuccess) {
+        return fail(ADAPT_ECUDA, "cudaHostUnregister failed: %s", cudaGetErrorString(e));
+    }
+    return ADAPT_OK;
+}
+int adapt_stream_create(int device, void** stream_out) {
+    if (!stream_out) return fail(ADAPT_EINVAL, "stream_create: null");
+    int rc = require_device(device);
+    if (rc) return rc;
+    cudaStream_t s;
+    CUDA_TRY(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    *stream_out = s;
+    return ADAPT_OK;
+}
+int adapt_stream_destroy(int device, void* stream) {
+    int rc = require_device(device);
+    if (rc) return rc;
+    CUDA_TRY(cudaStreamDestroy(reinterpret_cast<cudaStream_t>(stream)));
+    return ADAPT_OK;
+}
+int adapt_event_create(int device, void** event_out) {
+    if (!event_out) return fail(ADAPT_EINVAL, "event_create: null");
+    int rc = require_device(device);
+    if (rc) return rc;
+    cudaEvent_t e;
+    CUDA_TRY(cudaEventCreate(&e));
+    *event_out = e;
+    return ADAPT_OK;
+}
+int adapt_event_record(int device, void* event, void* stream) {
+    int rc = require_device(device);
+    if (rc) return rc;
+    CUDA_TRY(cudaEventRecord(reinterpret_cast<cudaEvent_t>(event), reinterpret_cast<cudaStream_t>(stream)));
+    return ADAPT_OK;
+}
+int adapt_event_sync(int device, void* event) {
+    int rc = require_device(device);
+    if (rc) return rc;
+    CUDA_TRY(cudaEventSynchronize(reinterpret_cast<cudaEvent_t>(event)));
+    return ADAPT_OK;
+}
+int adapt_event_elapsed_ms(int device, void* start, void* stop, float* ms_out) {
+    if (!ms_out) return fail(ADAPT_EINVAL, "event_elapsed: null");
+    int rc = require_device(device);
+    if (rc) return rc;
+    CUDA_TRY(cudaEventElapsedTime(ms_out, reinterpret_cast<cudaEvent_t>(start), reinterpret_cast<cudaEvent_t>(stop)));
+    return ADAPT_OK;
+}
+int adapt_event_destroy(int device, void* event) {
+    int rc = require_device(device);
+    if (rc) return rc;
+    CUDA_TRY(cudaEventDestroy(reinterpret_cast<cudaEvent_t>(event)));
     return ADAPT_OK;
 }
 

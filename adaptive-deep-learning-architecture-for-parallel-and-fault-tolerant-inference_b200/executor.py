@@ -71,6 +71,10 @@ class StageExecutor:
     def bind_io(self, slot: int, in_ptr: int, out_ptr: int) -> None:
         N.check(self.lib.adapt_stage_bind_io(self.handle, slot, in_ptr, out_ptr))
 
+    def prepare(self, slot: int, batch: int) -> None:
+        """Capture the CUDA graph of (slot, batch).  Configuration-time only (may sync the device)."""
+        N.check(self.lib.adapt_stage_prepare(self.handle, slot, batch))
+
     def enqueue(self, slot: int, batch: int, stream: int = 0) -> None:
         N.check(self.lib.adapt_stage_enqueue(self.handle, slot, batch, stream))
 
@@ -157,6 +161,7 @@ class LocalPredictor:
         self.d_in = DeviceBuffer(device, self.ex.in_bytes_per_image * max_batch)
         self.d_out = DeviceBuffer(device, self.ex.out_bytes_per_image * max_batch)
         self.ex.bind_io(0, self.d_in.ptr, self.d_out.ptr)
+        self.ex.prepare(0, max_batch)
 
     def run_raw(self, x_wire: np.ndarray, batch: int) -> np.ndarray:
         """x_wire: host array already in wire format for the stage input; returns raw output bytes."""

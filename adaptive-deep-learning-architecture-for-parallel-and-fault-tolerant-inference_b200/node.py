@@ -1,0 +1,396 @@
+"""Worker role: one pipeline stage bound to one B200.
+
+Mirror of reference src/node.py `Node` (config server + data server + predict/forward loop,
+src/node.py:29-194): a worker receives a partition ("configuration"), then for every
+micro-batch takes the incoming activation, runs its model slice and forwards the result to the
+next hop (`to_send.get -> model.predict -> _comp -> socket_send`, src/node.py:173-179).  Here
+  - the configuration is a row of the dispatcher's partition table (weights are already
+    resident on every GPU, so (re)configuration is metadata only);
+  - the incoming activation was stored into this worker's double-buffered input arena by the
+    previous stage's last kernel (peer stores over NVLink), announced by a 32-bit ready flag;
+  - `model.predict` is one CUDA-graph launch of the stage's kernels;
+  - forwarding is the epilogue of the stage's last kernel writing into the next worker's arena,
+    followed by stream-ordered flag writes; the host never touches activation data and never
+    blocks on the GPU except to apply back-pressure on result slots.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import threading
+import time
+import traceback
+from typing import Callable, Dict, List, Optional
+
+import numpy as np
+
+from . import _native as N
+from .dag_util import construct_model
+from .fabric import (G_EPOCH, G_PHASE, KIND_DATA, KIND_PINNED, KIND_STOP, PHASE_CONFIGURE, PHASE_QUIESCE, PHASE_RUN,
+                     PHASE_SHUTDOWN, POISON, W_ACK_QUIESCE, W_ACK_READY, W_DEVICE, W_ERRORS, W_HEARTBEAT, W_KILL, W_LAST_K, W_PID,
+                     ControlRing, CudaBackend, HealthTable, ResultRing, ShmRegion, StateEnum)
+
+# uint32 word indices inside a worker's flag block.  Flags live in the pinned, device-mapped
+# control segment (host memory): GPUs write / wait on them with stream memory operations, and the
+# host can overwrite them with plain stores -- which is what lets a reconfiguration release a
+# blocked stream without having to get a copy scheduled behind it.
+F_IN_READY, F_OUT_FREE, F_H2D_DONE, F_IN_CONSUMED = 0, 2, 4, 6
+FLAG_WORDS = 64
+IMAGE_BYTES = 224 * 224 * 3 * 4
+OUT_ROW_BYTES = 1000 * 4
+
+
+def arena_slot_bytes(model, mode: str, max_batch: int) -> int:
+    """Largest per-slot input a stage can be handed: the fp32 image batch or the biggest cut tensor."""
+    from .dag_util import cut_tensor_elems
+    from .executor import MODES, elem_bytes
+
+    m = MODES[mode]
+    biggest = max(cut_tensor_elems(model, l.name, m) for l in model.layers[1:-1])
+    shp = model.layers[0].output_shape[1:]
+    return max(int(np.prod(shp)) * 4, biggest * elem_bytes(N.DT_WORK, m)) * max_batch
+
+
+class NodeState:
+    """Per-worker state record (reference src/node_state.py:9-36): chunk_size, dispatcher address
+    and the worker's state enum -- backed by a row of the dispatcher's health table instead of an
+    etcd key `/workers/<ip>`."""
+
+    def __init__(self, chunk_size: int = 512 * 1000, dispatcher_ip: str = "in-process", health: Optional[HealthTable] = None,
+                 wid: int = 0):
+        self.chunk_size = chunk_size
+        self.dispatcher_ip = dispatcher_ip
+        self._health = health
+        self._wid = wid
+        self._state_enum = StateEnum.IDLE
+        self._lock = threading.Lock()
+        self.etcd_key = f"/workers/{wid}"
+
+    @property
+    def state(self) -> int:
+        return self._state_enum
+
+    @state.setter
+    def state(self, v: int) -> None:
+        with self._lock:
+            self._state_enum = v
+            if self._health is not None:
+                self._health.set_state(self._wid, v)
+
+
+class StageWorker:
+    """Engine of one worker.  `session` is the dict the dispatcher publishes (fabric layout)."""
+
+    def __init__(self, wid: int, device: int, model, session: dict, backend=None):
+        self.wid = wid
+        self.device = device
+        self.model = model
+        self.session = session
+        self.mode = session["mode"]
+        self.max_batch = session["max_batch"]
+        self.backend = backend if backend is not None else CudaBackend(device)
+        self.region = ShmRegion(session["shm"], create=False) if isinstance(session["shm"], str) else session["shm"]
+        self.health = HealthTable(self.region, session["health_off"])
+        self.ring = ControlRing(self.region, session["ring_off"] + wid * ControlRing.BYTES)
+        self.rings = [ControlRing(self.region, session["ring_off"] + i * ControlRing.BYTES) for i in range(session["n_workers"])]
+        self.results = ResultRing(self.region, session["result_off"], self.max_batch * OUT_ROW_BYTES)
+        self.state = NodeState(health=self.health, wid=wid)
+        self.slot_bytes = session["slot_bytes"]
+        self.arena = 0
+        self.peers: Dict[int, int] = {}
+        self.executor = None
+        self.epoch = -1
+        self.stage_index = -1
+        self.n_stages = 0
+        self.prev_wid = self.next_wid = -1
+        self.thread: Optional[threading.Thread] = None
+        self.dead = False
+        self.error: Optional[str] = None
+        self._stop = threading.Event()
+        self._hb_thread: Optional[threading.Thread] = None
+        self.launches = 0
+        self.on_kill: Optional[Callable[[], None]] = None
+        if hasattr(self.backend, "abort_check"):  # synchronous test backends must be able to give up a wait
+            self.backend.abort_check = lambda: (self.health.phase != PHASE_RUN or bool(self.health.w[self.wid, W_KILL])
+                                                or self._stop.is_set())
+
+    # ------------------------------------------------------------------ set-up
+    def allocate(self):
+        """Allocate this worker's arena [in_buf 0 | in_buf 1], its result scratch, its pinned input
+        staging and its streams; returns the token peers use to map the arena."""
+        b = self.backend
+        self.arena = b.alloc(2 * self.slot_bytes)
+        self.d_out = b.alloc(self.max_batch * OUT_ROW_BYTES)
+        self.stream = b.new_stream()
+        self.copy_stream = b.new_stream()
+        # pinned staging for pageable inputs (only the first stage of a session uses it)
+        stage_bytes = self.max_batch * self.session["in_row_bytes"]
+        self._stage_np = np.zeros(2 * stage_bytes + 4096, dtype=np.uint8)
+        base = (self._stage_np.ctypes.data + 4095) // 4096 * 4096
+        b.register_host(base, 2 * stage_bytes)
+        self.stage_addr = [base, base + stage_bytes]
+        # the whole control segment (flags + result ring) is pinned and mapped into this device
+        self.ctl_dev = b.register_host(self.region.addr, self.region.size)
+        self.results_dev = self.ctl_dev + self.session["result_off"]
+        self.flags_host = self.region.view(np.uint32, self.session["flag_off"],
+                                           self.session["n_workers"] * FLAG_WORDS).reshape(-1, FLAG_WORDS)
+        self.health.w[self.wid, W_PID] = os.getpid()
+        self.health.w[self.wid, W_DEVICE] = self.device
+        if self.session.get("ipc", False):
+            return b.export(self.arena)
+        return self.arena
+
+    def connect(self, tokens: Dict[int, object], devices: Dict[int, int]) -> None:
+        for w, tok in tokens.items():
+            if w == self.wid:
+                self.peers[w] = self.arena
+            elif self.session.get("ipc", False):
+                self.peers[w] = self.backend.open(tok)
+            else:
+                if devices[w] != self.device:
+                    self.backend.peer_enable(devices[w])
+                self.peers[w] = int(tok)
+
+    def flag(self, wid: int, word: int) -> int:
+        """Device-side address of flag `word` of worker `wid` (in the mapped control segment)."""
+        return self.ctl_dev + self.session["flag_off"] + 4 * (wid * FLAG_WORDS + word)
+
+    def in_buf(self, wid: int, slot: int) -> int:
+        return self.peers[wid] + slot * self.slot_bytes
+
+    # ------------------------------------------------------------------ reconfiguration
+    def _write_own_flags(self, value: int) -> None:
+        self.flags_host[self.wid, :] = value
+
+    def _drain(self) -> None:
+        """Release every GPU-side wait that will never be satisfied and let the queued work run
+        out.  A stale flag write from a draining peer can overwrite the poison, so it is re-applied
+        until both streams are idle."""
+        t0 = time.monotonic()
+        while True:
+            self._write_own_flags(POISON)
+            if not self.backend.busy(self.copy_stream) and not self.backend.busy(self.stream):
+                return
+            if time.monotonic() - t0 > 20:
+                raise TimeoutError("stage streams did not drain")
+            time.sleep(200e-6)
+
+    def _quiesce(self, epoch: int) -> None:
+        self._drain()
+        self.health.w[self.wid, W_ACK_QUIESCE] = epoch
+
+    def _configure(self, epoch: int) -> None:
+        table = self.health.read_table()
+        assert table["epoch"] == epoch, (table, epoch)
+        order: List[int] = table["order"]
+        self._write_own_flags(0)
+        self.ring.clear()
+        self.k_expect = 0
+        if self.wid not in order:
+            self.stage_index, self.n_stages = -1, len(order)
+        else:
+            i = order.index(self.wid)
+            bounds = [self.model.layers[0].name] + list(table["part_at"]) + [self.model.layers[-1].name]
+            part = construct_model(self.model, bounds[i], bounds[i + 1], f"part{i + 1}")
+            if self.executor is None:
+                self.executor = self.backend.make_executor(self.model, part, self.mode, self.max_batch)
+            else:
+                self.executor.reslice(part)
+            self.stage_index, self.n_stages = i, len(order)
+            self.prev_wid = order[i - 1] if i > 0 else -1
+            self.next_wid = order[i + 1] if i + 1 < len(order) else -1
+            for s in (0, 1):
+                out_ptr = self.in_buf(self.next_wid, s) if self.next_wid >= 0 else self.d_out
+                self.executor.bind_io(s, self.in_buf(self.wid, s), out_ptr)
+            if table.get("warm_batches"):
+                self._warm(table["warm_batches"])
+        self.epoch = epoch
+        self.health.w[self.wid, W_ACK_READY] = epoch
+
+    def _warm(self, batches) -> None:
+        """Build launch records + graphs for the batch sizes the dispatcher announces, so the
+        first real micro-batch does not pay for graph capture.  Output goes to real buffers, but
+        no flag is written, so downstream never consumes it."""
+        for b in batches:
+            for s in (0, 1):
+                if hasattr(self.executor, "prepare"):
+                    self.executor.prepare(s, int(b))
+                self.executor.enqueue(s, int(b), self.stream)
+        self.backend.sync(self.stream)
+
+    # ------------------------------------------------------------------ steady state
+    def _process(self, rec) -> None:
+        kind, epoch, k, seq, batch, aux = rec
+        b, ex = self.backend, self.executor
+        s = k & 1
+        first = self.stage_index == 0
+        last = self.stage_index == self.n_stages - 1
+        if first:
+            # host -> device copy of the input on the copy stream, double buffered against compute
+            nbytes = batch * self.session["in_row_bytes"]
+            src = aux
+            if not (kind & KIND_PINNED):
+                # Pageable input: stage it through this worker's pinned slot so that the copy below is
+                # truly asynchronous.  (A pageable cudaMemcpyAsync blocks the host until the stream gets
+                # there, i.e. possibly forever behind a flag a dead stage never writes.)
+                fl = self.flags_host[self.wid]
+                t0 = time.monotonic()
+                while k >= 2 and ((int(fl[F_H2D_DONE + s]) - (k - 1)) & 0xFFFFFFFF) >= 0x80000000:
+                    if self.health.phase != PHASE_RUN or self._stop.is_set():
+                        return
+                    if time.monotonic() - t0 > 30:
+                        raise TimeoutError("input staging slot never drained")
+                    time.sleep(20e-6)
+                ctypes.memmove(self.stage_addr[s], aux, nbytes)
+                src = self.stage_addr[s]
+            if k >= 2:
+                b.wait_flag(self.copy_stream, self.flag(self.wid, F_IN_CONSUMED + s), k - 1)
+            b.h2d(self.in_buf(self.wid, s), src, nbytes, self.copy_stream)
+            b.write_flag(self.copy_stream, self.flag(self.wid, F_H2D_DONE + s), k + 1)
+            b.wait_flag(self.stream, self.flag(self.wid, F_H2D_DONE + s), k + 1)
+        else:
+            b.wait_flag(self.stream, self.flag(self.wid, F_IN_READY + s), k + 1)
+        if not last and k >= 2:
+            b.wait_flag(self.stream, self.flag(self.wid, F_OUT_FREE + s), k - 1)
+        if last:
+            r = k % ResultRing.SLOTS
+            hdr = self.results.hdr[r]
+            t0 = time.monotonic()
+            while k >= ResultRing.SLOTS and int(hdr[1]) < k - ResultRing.SLOTS + 1:  # back-pressure
+                if self.health.epoch != self.epoch or self._stop.is_set():
+                    return
+                if time.monotonic() - t0 > 30:
+                    raise TimeoutError("result slot never freed")
+                time.sleep(20e-6)
+        ex.enqueue(s, batch, self.stream)
+        self.launches += ex.num_launches
+        if first:
+            b.write_flag(self.stream, self.flag(self.wid, F_IN_CONSUMED + s), k + 1)
+        else:
+            b.write_flag(self.stream, self.flag(self.prev_wid, F_OUT_FREE + s), k + 1)
+        if last:
+            hdr[2], hdr[3], hdr[4] = epoch, seq, batch
+            off = r * self.results.stride
+            b.d2h(self.results_dev + off + ResultRing.HDR, self.d_out, batch * OUT_ROW_BYTES, self.stream)
+            b.write_flag(self.stream, self.results_dev + off, k + 1)
+        else:
+            b.write_flag(self.stream, self.flag(self.next_wid, F_IN_READY + s), k + 1)
+            self.rings[self.next_wid].push((kind, epoch, k, seq, batch, 0))
+        self.health.w[self.wid, W_LAST_K] = k
+
+    def _heartbeat_loop(self) -> None:
+        while not self._stop.is_set() and not self.dead:
+            self.health.beat(self.wid)
+            time.sleep(self.session.get("heartbeat_s", 0.005))
+
+    def _start_heartbeat(self) -> None:
+        self.health.beat(self.wid)
+        self._hb_native = None
+        if hasattr(self.backend, "start_heartbeat"):
+            # native beacon thread: a Python thread can be starved by the GIL for tens of ms
+            addr = self.health.w[self.wid:self.wid + 1, W_HEARTBEAT:W_HEARTBEAT + 1].ctypes.data
+            self._hb_native = self.backend.start_heartbeat(addr, self.session.get("heartbeat_s", 0.005))
+        else:
+            self._hb_thread = threading.Thread(target=self._heartbeat_loop, daemon=True, name=f"hb{self.wid}")
+            self._hb_thread.start()
+
+    def _stop_heartbeat(self) -> None:
+        if getattr(self, "_hb_native", None):
+            self.backend.stop_heartbeat(self._hb_native)
+            self._hb_native = None
+
+    def _die(self) -> None:
+        """Injected stage kill: go silent (no more heartbeats, no more work, in-flight micro-batches
+        are lost) after draining the GPU queue so a zombie cannot scribble on live peers."""
+        self.dead = True
+        self._stop_heartbeat()
+        if not self.session.get("silent_kill", False):
+            self.state.state = StateEnum.DEAD  # a crash would not announce itself; see `silent_kill`
+        if self.on_kill is not None:
+            self.on_kill()
+        try:
+            self._drain()
+        except Exception:
+            pass
+
+    def run(self) -> None:
+        """Blocking worker loop (the reference's `Node.run`, src/node.py:181-194)."""
+        h = self.health
+        try:
+            self._start_heartbeat()
+            while not self._stop.is_set():
+                phase, epoch = h.phase, h.epoch
+                if phase == PHASE_SHUTDOWN:
+                    break
+                if int(h.w[self.wid, W_KILL]):
+                    self._die()
+                    break
+                if phase == PHASE_QUIESCE and int(h.w[self.wid, W_ACK_QUIESCE]) != epoch:
+                    self.state.state = StateEnum.IDLE
+                    self._quiesce(epoch)
+                    continue
+                if phase == PHASE_CONFIGURE and int(h.w[self.wid, W_ACK_READY]) != epoch:
+                    if int(h.w[self.wid, W_ACK_QUIESCE]) != epoch:
+                        self._quiesce(epoch)
+                    self._configure(epoch)
+                    continue
+                if phase != PHASE_RUN or self.epoch != epoch or self.stage_index < 0:
+                    time.sleep(100e-6)
+                    continue
+                rec = self.ring.pop(timeout=0.002)
+                if rec is None:
+                    self.state.state = StateEnum.IDLE
+                    continue
+                if (rec[0] & 0xFF) == KIND_STOP:
+                    if self.next_wid >= 0:
+                        self.rings[self.next_wid].push(rec)
+                    continue
+                if rec[1] != self.epoch:
+                    continue  # stale header from before a reconfiguration
+                self.state.state = StateEnum.BUSY
+                self._process(rec)
+        except Exception as e:  # noqa: BLE001 - surfaced to the dispatcher through the health table
+            self.error = f"{type(e).__name__}: {e}\n{traceback.format_exc()}"
+            self.state.state = StateEnum.ERROR
+            self.health.w[self.wid, W_ERRORS] += 1
+            self.dead = True
+        finally:
+            self._stop_heartbeat()
+            try:
+                self.backend.sync(self.stream)
+            except Exception:
+                pass
+
+    def start(self) -> None:
+        self.thread = threading.Thread(target=self.run, daemon=True, name=f"stage-worker-{self.wid}")
+        self.thread.start()
+
+    def stop(self) -> None:
+        self._stop.set()
+        if self.thread is not None:
+            self.thread.join(timeout=10)
+
+    def close(self) -> None:
+        self.stop()
+        if self.executor is not None:
+            self.executor.close()
+            self.executor = None
+        try:
+            self.backend.close()
+        except Exception:
+            pass
+
+
+class Node:
+    """Reference-compatible shell: `Node().run()` (reference src/node.py:181,210-211) turns this
+    process into the worker for one GPU of a torchrun-launched session.  It blocks until the
+    dispatcher (rank 0) shuts the session down."""
+
+    def __init__(self, model=None, device: Optional[int] = None):
+        self.model = model
+        self.device = device
+
+    def run(self) -> None:
+        from .dispatcher import join_session_as_worker
+
+        join_session_as_worker(self.model, self.device)

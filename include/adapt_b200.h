@@ -116,6 +116,12 @@ int adapt_stage_reslice(adapt_stage_t* stage, const adapt_tensor_desc* tensors, 
  * layer's epilogue then stores the cut tensor straight over NVLink. */
 int adapt_stage_bind_io(adapt_stage_t* stage, int slot, void* in_ptr, void* out_ptr);
 
+/* Optional warm-up, part of (re)configuration: build the launch records of (`slot`, `batch`) and
+ * capture them into a CUDA graph.  May synchronise the device; call it before streaming starts.
+ * A batch size that was never prepared still works through enqueue(), as plain launches.
+ * (Reference counterpart: Keras builds its predict function on the first `predict` call.) */
+int adapt_stage_prepare(adapt_stage_t* stage, int slot, int batch);
+
 /* Replaces: `model.predict(inpt)` (reference src/node.py:177).  Asynchronously runs the stage
  * program on `batch` images from slot's input buffer into slot's output buffer on `stream`. */
 int adapt_stage_enqueue(adapt_stage_t* stage, int slot, int batch, void* stream);
@@ -163,6 +169,25 @@ int adapt_memcpy_d2h(int device, void* dst, const void* src, size_t bytes, void*
 int adapt_memcpy_d2d(int device, void* dst, const void* src, size_t bytes, void* stream);
 int adapt_memset(int device, void* dst, int value, size_t bytes, void* stream);
 int adapt_stream_sync(int device, void* stream);
+/* Non-blocking: *busy_out = 0 when all work queued on `stream` has completed, 1 otherwise. */
+int adapt_stream_query(int device, void* stream, int* busy_out);
+/* Liveness beacon: a native thread stores CLOCK_MONOTONIC nanoseconds into *word every
+ * `interval_us` (immune to the Python GIL).  Replaces the worker's etcd lease/heartbeat
+ * (reference src/node_state.py:18-23).  Needs no GPU. */
+int adapt_heartbeat_start(volatile int64_t* word, int interval_us, void** handle_out);
+int adapt_heartbeat_stop(void* handle);
+/* Pin + map an existing host range (e.g. a shared-memory segment) so that async copies and
+ * stream-ordered flag writes can target it; *dev_ptr_out is the device-side alias. */
+int adapt_host_register(int device, void* host_ptr, size_t bytes, void** dev_ptr_out);
+int adapt_host_unregister(int device, void* host_ptr);
+/* Streams and timing events owned by the library (a worker uses one compute and one copy stream). */
+int adapt_stream_create(int device, void** stream_out);
+int adapt_stream_destroy(int device, void* stream);
+int adapt_event_create(int device, void** event_out);
+int adapt_event_record(int device, void* event, void* stream);
+int adapt_event_sync(int device, void* event);
+int adapt_event_elapsed_ms(int device, void* start, void* stop, float* ms_out);
+int adapt_event_destroy(int device, void* event);
 
 #ifdef __cplusplus
 }

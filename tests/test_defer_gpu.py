@@ -1,0 +1,131 @@
+"""GPU: the reference-facing API (DEFER / part_at / queues) end to end on real B200s, checked
+against the oracle.  Stages may share one GPU (computeNodes naming the same device): the
+hand-off protocol is identical, the peer pointer just happens to be local."""
+import os
+import queue
+import threading
+import time
+
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")  # several stages' streams on one GPU must not alias
+
+import numpy as np  # noqa: E402
+import pytest  # noqa: E402
+
+from _util import KO, oracle_for  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+PROB_TOL_BF16 = 1e-2
+
+
+def _ngpu():
+    from adapt_b200 import _native
+
+    return _native.device_count()
+
+
+def _run(defer, model, part_at, inputs, kill_after=None, kill_stage=None, timeout=40):
+    in_q, out_q = queue.Queue(10), queue.Queue()
+    t = threading.Thread(target=defer.run_defer, args=(model, part_at, in_q, out_q), daemon=True)
+    t.start()
+    defer.wait_ready(120)
+    outs = []
+    threading.Thread(target=lambda: [in_q.put(x) for x in inputs], daemon=True).start()
+    t0, killed = time.time(), False
+    while len(outs) < len(inputs):
+        try:
+            outs.append(out_q.get(timeout=0.2))
+        except queue.Empty:
+            assert defer.error is None, defer.error
+            assert time.time() - t0 < timeout, f"timed out with {len(outs)}/{len(inputs)} results: {defer.debug_state()}"
+        if kill_after is not None and not killed and len(outs) >= kill_after:
+            defer.inject_kill(kill_stage)
+            killed = True
+    time.sleep(0.05)
+    assert out_q.empty(), "duplicate delivery"
+    stats = dict(defer.stats)
+    launches = defer.gpu_launches
+    defer.shutdown()
+    t.join(30)
+    return outs, stats, launches
+
+
+def _check(model, inputs, outs, tol=PROB_TOL_BF16):
+    o = oracle_for(model)
+    for x, y in zip(inputs, outs):
+        ref = o.predict(np.asarray(x))[0]
+        assert y.shape == ref.shape and y.dtype == np.float32
+        assert np.abs(y - ref).max() <= tol
+        assert y.argmax(-1).tolist() == ref.argmax(-1).tolist()
+
+
+def test_reference_driver_shape(pkg, model50):
+    """The reference's own driver (test/test.py:10-50), restated: 10 x batch-1 through part_at=[]."""
+    from src.dispatcher import DEFER
+
+    defer = DEFER(["0.0.0.0"], max_batch=1)
+    x = KO.synthetic_images(1, seed=7, kind="caffe")
+    outs, stats, launches = _run(defer, model50, [], [x] * 10)
+    assert len(outs) == 10 and all(o.shape == (1, 1000) for o in outs)
+    _check(model50, [x], outs[:1])
+    for o in outs[1:]:
+        np.testing.assert_array_equal(o, outs[0])
+    assert launches >= 10 * 58
+
+
+@pytest.mark.parametrize("part_at", [["conv3_block4_out"], ["conv2_block3_out", "conv3_block4_out", "conv4_block6_out"]])
+def test_pipeline_stages_sharing_one_gpu(pkg, model50, part_at):
+    from adapt_b200.dispatcher import DEFER
+
+    n = len(part_at) + 1
+    inputs = [KO.synthetic_images(b, seed=300 + i, kind="normal") for i, b in enumerate([4, 3, 4, 1, 2, 4, 4, 4])]
+    defer = DEFER(["cuda:0"] * n, max_batch=4)
+    outs, stats, _ = _run(defer, model50, part_at, inputs)
+    assert stats["delivered"] == len(inputs) and stats["failovers"] == 0
+    _check(model50, inputs, outs)
+
+
+def test_pipeline_across_gpus(pkg, model50):
+    if _ngpu() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    from adapt_b200.dispatcher import DEFER, balanced_part_at
+
+    n = min(_ngpu(), 4)
+    part_at = balanced_part_at(model50, n)
+    inputs = [KO.synthetic_images(4, seed=400 + i, kind="normal") for i in range(12)]
+    defer = DEFER([f"cuda:{i}" for i in range(n)], max_batch=4)
+    outs, stats, _ = _run(defer, model50, part_at, inputs)
+    assert stats["delivered"] == 12
+    _check(model50, inputs, outs)
+
+
+def test_pinned_torch_inputs(pkg, model50):
+    torch = pytest.importorskip("torch")
+    from adapt_b200.dispatcher import DEFER
+
+    xs = [KO.synthetic_images(2, seed=500 + i, kind="normal") for i in range(4)]
+    pinned = [torch.from_numpy(x).pin_memory() for x in xs]
+    defer = DEFER(["cuda:0"], max_batch=2)
+    outs, _, _ = _run(defer, model50, [], pinned)
+    _check(model50, xs, outs)
+
+
+def test_failover_resliced_and_replayed(pkg, model50):
+    from adapt_b200.dispatcher import DEFER
+
+    devs = [f"cuda:{i % max(1, _ngpu())}" for i in range(3)]
+    inputs = [KO.synthetic_images(2, seed=600 + i, kind="normal") for i in range(40)]
+    defer = DEFER(devs, max_batch=2, heartbeat_timeout=0.05)
+    outs, stats, _ = _run(defer, model50, ["conv2_block3_out", "conv4_block1_out"], inputs, kill_after=10, kill_stage=1)
+    assert stats["failovers"] == 1 and stats["delivered"] == 40
+    assert len(defer.part_at) == 1
+    _check(model50, inputs, outs)                       # FIFO, nothing lost, nothing duplicated
+    assert stats["failover_ms"] and stats["failover_ms"][0] < 1000.0   # sub-second recovery (north_star)
+
+
+def test_fp32_check_mode_through_defer(pkg, model50):
+    from adapt_b200.dispatcher import DEFER
+
+    inputs = [KO.synthetic_images(1, seed=700 + i, kind="caffe") for i in range(2)]
+    defer = DEFER(["cuda:0", "cuda:0"], mode="fp32", max_batch=1)
+    outs, _, _ = _run(defer, model50, ["conv3_block4_out"], inputs)
+    _check(model50, inputs, outs, tol=1e-4)

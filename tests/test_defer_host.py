@@ -1,0 +1,143 @@
+"""CPU: host logic of the dispatcher / worker protocol with a synchronous test backend whose
+stage compute is the oracle (tests/_host_backend.py).  No CUDA involved; the GPU versions of the
+same scenarios are in tests/test_defer_gpu.py."""
+import queue
+import threading
+import time
+
+import numpy as np
+import pytest
+
+from _host_backend import HostBackend
+from _util import KO, oracle_for
+
+
+def _run(defer, model, part_at, inputs, kill_after=None, kill_stage=None, timeout=120):
+    in_q, out_q = queue.Queue(10), queue.Queue()
+    t = threading.Thread(target=defer.run_defer, args=(model, part_at, in_q, out_q), daemon=True)
+    t.start()
+    defer.wait_ready(60)
+    outs = []
+
+    def feed():
+        for x in inputs:
+            in_q.put(x)
+
+    f = threading.Thread(target=feed, daemon=True)
+    f.start()
+    t0 = time.time()
+    killed = False
+    while len(outs) < len(inputs):
+        try:
+            outs.append(out_q.get(timeout=0.2))
+        except queue.Empty:
+            assert defer.error is None, defer.error
+            assert time.time() - t0 < timeout, f"timed out with {len(outs)}/{len(inputs)} results"
+        if kill_after is not None and not killed and len(outs) >= kill_after:
+            defer.inject_kill(kill_stage)
+            killed = True
+    time.sleep(0.05)
+    assert out_q.empty(), "more results than inputs (duplicate delivery)"
+    stats = dict(defer.stats)
+    defer.shutdown()
+    t.join(20)
+    return outs, stats
+
+
+def test_partition_names_and_errors(pkg, model50):
+    from adapt_b200.dispatcher import DEFER
+
+    d = DEFER(["127.0.0.1"], backend_factory=HostBackend)
+    assert d.computeNodes == ["127.0.0.1"] and d.chunk_size == 512 * 1000 and isinstance(d.dispatchIP, str)
+    parts = d._partition(model50, ["conv2_block3_out", "conv3_block4_out", "conv4_block6_out"])
+    assert [p.name for p in parts] == ["part1", "part2", "part3", "part4"]
+    assert parts[0].start == "input_1" and parts[0].end == "conv2_block3_out"
+    assert parts[1].layer_names[0] == "conv3_block1_1_conv" and parts[1].layer_names[-1] == "conv3_block4_out"
+    assert parts[3].end == "predictions"
+    assert sum(p.macs() for p in parts) == 3_857_973_248
+    assert [round(p.macs() / 1e9, 3) for p in parts] == [0.786, 0.951, 1.387, 0.734]   # SURVEY 8d, config 3 (rounded there)
+    with pytest.raises(RuntimeError):
+        d._partition(model50, ["conv3_block1_2_relu"])
+    with pytest.raises(ValueError):
+        d._partition(model50, ["not_a_layer"])
+    assert len(d._partition(model50, [])) == 1
+
+
+def test_balanced_part_at(pkg, model50):
+    from adapt_b200.dag_util import valid_cut_points
+    from adapt_b200.dispatcher import DEFER, balanced_part_at
+
+    valid = set(valid_cut_points(model50))
+    d = DEFER([0], backend_factory=HostBackend)
+    for n, eff_floor in ((2, 0.90), (4, 0.85), (7, 0.80), (8, 0.80)):
+        cuts = balanced_part_at(model50, n)
+        assert len(cuts) == n - 1 and set(cuts) <= valid
+        macs = [p.macs() for p in d._partition(model50, cuts)]
+        assert sum(macs) / (n * max(macs)) >= eff_floor, (n, cuts, macs)
+    assert balanced_part_at(model50, 1) == []
+
+
+def test_control_ring_and_health_table(pkg):
+    from adapt_b200.fabric import ControlRing, HealthTable, ResultRing, ShmRegion
+
+    reg = ShmRegion(create=True, size=HealthTable.BYTES + ControlRing.BYTES + ResultRing.bytes_needed(4000) + 4096)
+    try:
+        ring = ControlRing(reg, HealthTable.BYTES)
+        assert ring.pop(timeout=0.001) is None
+        for i in range(300):                      # wraps the 256-entry ring
+            assert ring.push((1, 0, i, i, 2, 0))
+            assert ring.pop() == (1, 0, i, i, 2, 0)
+        for i in range(ControlRing.CAP):
+            assert ring.push((1, 0, i, i, 1, 0))
+        assert not ring.push((1, 0, 0, 0, 1, 0), timeout=0.01)     # full -> back-pressure
+        ring.clear()
+        assert ring.pop(timeout=0.001) is None
+        h = HealthTable(reg, 0)
+        h.write_table({"epoch": 3, "order": [0, 2], "part_at": ["conv3_block4_out"]})
+        assert h.read_table()["order"] == [0, 2]
+        h.beat(1)
+        assert h.age_ms(1) < 50
+        other = ShmRegion(reg.name)               # second mapping sees the same bytes
+        assert HealthTable(other, 0).read_table()["epoch"] == 3
+        other.close()
+    finally:
+        reg.close()
+
+
+@pytest.mark.parametrize("part_at", [[], ["conv3_block4_out"], ["pool1_pool", "conv3_block1_out", "conv5_block1_add"]])
+def test_pipeline_fifo_and_values(pkg, model50, part_at):
+    from adapt_b200.dispatcher import DEFER
+
+    o = oracle_for(model50)
+    inputs = [KO.synthetic_images(b, seed=100 + i, kind="normal") for i, b in enumerate([1, 2, 1, 1])]   # ragged batches
+    d = DEFER([f"10.0.0.{i}" for i in range(len(part_at) + 1)], mode="fp32", max_batch=2, backend_factory=HostBackend,
+              heartbeat_timeout=5.0)
+    outs, stats = _run(d, model50, part_at, inputs)
+    assert stats["delivered"] == len(inputs) and stats["failovers"] == 0
+    for x, y in zip(inputs, outs):
+        assert y.shape == (x.shape[0], 1000) and y.dtype == np.float32
+        np.testing.assert_allclose(y, o.predict(x)[0], rtol=1e-5, atol=1e-7)
+
+
+def test_failover_replays_exactly_once_in_order(pkg, model50):
+    from adapt_b200.dispatcher import DEFER
+
+    o = oracle_for(model50)
+    inputs = [KO.synthetic_images(1, seed=200 + i, kind="normal") for i in range(7)]
+    d = DEFER([0, 1, 2], mode="fp32", max_batch=1, backend_factory=lambda dev: HostBackend(dev, delay=0.02),
+              heartbeat_timeout=0.25)
+    outs, stats = _run(d, model50, ["conv2_block3_out", "conv4_block1_out"], inputs, kill_after=2, kill_stage=1)
+    assert stats["failovers"] == 1 and stats["delivered"] == 7
+    assert stats["replayed"] >= 1                     # something was in flight when the stage died
+    assert d.part_at and len(d.part_at) == 1          # re-sliced onto the two survivors
+    for x, y in zip(inputs, outs):                    # order preserved, nothing lost, nothing duplicated
+        np.testing.assert_allclose(y, o.predict(x)[0], rtol=1e-5, atol=1e-7)
+    assert len(stats["failover_ms"]) == 1 and stats["failover_ms"][0] > 0
+
+
+def test_too_few_compute_nodes(pkg, model50):
+    from adapt_b200.dispatcher import DEFER
+
+    d = DEFER([0], backend_factory=HostBackend)
+    with pytest.raises(ValueError):
+        d.run_defer(model50, ["conv3_block4_out"], queue.Queue(), queue.Queue())
