@@ -758,6 +758,40 @@ int adapt_stage_read_tensor(adapt_stage_t* st, int tensor, void* host_dst, size_
     return ADAPT_OK;
 }
 
+int adapt_stage_profile(adapt_stage_t* st, int slot, int batch, void* stream_v, int reps, float* ms_per_op, int n_ops) {
+    Plan* plan = nullptr;
+    int rc = get_plan(st, slot, batch, &plan);
+    if (rc) return rc;
+    const std::vector<Step>& steps = plan->steps[slot];
+    if (!ms_per_op || n_ops != (int)steps.size() || reps <= 0)
+        return fail(ADAPT_EINVAL, "profile: need reps > 0 and n_ops == %d", (int)steps.size());
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
+    const size_t n = steps.size();
+    std::vector<cudaEvent_t> ev((n + 1) * (size_t)reps);
+    for (auto& e : ev) CUDA_TRY(cudaEventCreate(&e));
+    for (int r = 0; r < reps; ++r) {
+        CUDA_TRY(cudaEventRecord(ev[(size_t)r * (n + 1)], stream));
+        for (size_t i = 0; i < n; ++i) {
+            std::vector<Step> one(1, steps[i]);
+            rc = run_steps(st, one, stream);
+            if (rc) return rc;
+            CUDA_TRY(cudaEventRecord(ev[(size_t)r * (n + 1) + i + 1], stream));
+        }
+    }
+    CUDA_TRY(cudaStreamSynchronize(stream));
+    for (size_t i = 0; i < n; ++i) {
+        float acc = 0.f;
+        for (int r = 0; r < reps; ++r) {
+            float ms = 0.f;
+            CUDA_TRY(cudaEventElapsedTime(&ms, ev[(size_t)r * (n + 1) + i], ev[(size_t)r * (n + 1) + i + 1]));
+            acc += ms;
+        }
+        ms_per_op[i] = acc / (float)reps;
+    }
+    for (auto& e : ev) cudaEventDestroy(e);
+    return ADAPT_OK;
+}
+
 int adapt_stage_num_launches(adapt_stage_t* st, int batch) {
     if (!st) return fail(ADAPT_EINVAL, "stage is null");
     (void)batch;

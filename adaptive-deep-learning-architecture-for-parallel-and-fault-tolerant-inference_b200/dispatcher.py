@@ -29,7 +29,8 @@ import numpy as np
 
 from . import _native as N
 from .dag_util import PartModel, construct_model, layer_macs
-from .fabric import (G_EPOCH, G_NWORKERS, G_PHASE, KIND_DATA, KIND_PINNED, KIND_STOP, MAX_WORKERS, PHASE_CONFIGURE, PHASE_INIT,
+from .fabric import (G_EPOCH, G_NWORKERS, G_PHASE, G_T0, G_T1, G_TIMING_REQ, KIND_DATA, KIND_PINNED, KIND_RESIDENT, KIND_STOP,
+                     W_ELAPSED_US, W_TIMING_ACK, MAX_WORKERS, PHASE_CONFIGURE, PHASE_INIT,
                      PHASE_QUIESCE, PHASE_RUN, PHASE_SHUTDOWN, POISON, W_ACK_QUIESCE, W_ACK_READY, W_KILL, W_STATE,
                      ControlRing, CudaBackend, HealthTable, ResultRing, ShmRegion, StateEnum)
 from .node import IMAGE_BYTES, OUT_ROW_BYTES, StageWorker, arena_slot_bytes
@@ -100,6 +101,15 @@ def balanced_part_at(model, n_stages: int, cut_bytes_weight: float = 0.0) -> Lis
         j = arg[s][j]
         s -= 1
     return cuts[::-1]
+
+
+class ResidentBatch:
+    """Queue item for the device-resident measurement leg (bench.py `value`): "run one micro-batch
+    of `batch` images on the input that `DEFER.preload_input` already placed in the first stage's
+    input slots".  No host-to-device copy happens for such an item."""
+
+    def __init__(self, batch: int):
+        self.batch = int(batch)
 
 
 class DEFER:
@@ -254,7 +264,7 @@ class DEFER:
                 continue
             if model_input is None:  # convenience: None ends the stream
                 break
-            arr = self._as_host_array(model_input)
+            arr = model_input if isinstance(model_input, ResidentBatch) else self._as_host_array(model_input)
             while not self.concurrency_sem.acquire(timeout=0.05):
                 if self._shutdown_event.is_set():
                     return
@@ -282,6 +292,8 @@ class DEFER:
     @staticmethod
     def _addr_batch(arr):
         """(host address, batch, pinned?) of a queue item."""
+        if isinstance(arr, ResidentBatch):
+            return 0, int(arr.batch), False
         if isinstance(arr, np.ndarray):
             return arr.ctypes.data, int(arr.shape[0]), False
         return int(arr.data_ptr()), int(arr.shape[0]), bool(arr.is_pinned())
@@ -292,7 +304,8 @@ class DEFER:
             raise ValueError(f"queue item holds {batch} images; max_batch is {self.max_batch}")
         k = self._k_feed
         self._k_feed += 1
-        if not self.rings[self.order[0]].push((KIND_DATA | (KIND_PINNED if pinned else 0), self.health.epoch, k, seq, batch, addr)):
+        kind = KIND_DATA | (KIND_PINNED if pinned else 0) | (KIND_RESIDENT if isinstance(arr, ResidentBatch) else 0)
+        if not self.rings[self.order[0]].push((kind, self.health.epoch, k, seq, batch, addr)):
             raise RuntimeError("first stage does not drain its control ring")
 
     def _result_server(self, output: queue.Queue):
@@ -378,6 +391,36 @@ class DEFER:
                 self.stats["replayed"] += 1
         self.stats["failovers"] += 1
         self.stats.setdefault("reconfig_ms", []).append((time.perf_counter() - t0) * 1e3)
+
+    # ------------------------------------------------------------------ measurement aids
+    def preload_input(self, x) -> None:
+        """Copy `x` (host, fp32 NHWC) into both input slots of the (dispatcher-local) first stage."""
+        arr = np.ascontiguousarray(x, dtype=np.float32)
+        wk = next(w for w in self.workers if w.wid == self.order[0])
+        for s in (0, 1):
+            wk.backend.h2d(wk.in_buf(wk.wid, s), arr.ctypes.data, arr.nbytes, wk.copy_stream)
+        wk.backend.sync(wk.copy_stream)
+
+    def set_timing_window(self, k0: int, k1: int) -> None:
+        """Every stage records CUDA events on its stream around micro-batches [k0, k1) of this epoch."""
+        self.health.g[G_T0], self.health.g[G_T1] = k0, k1
+
+    def collect_timing(self, timeout: float = 30.0) -> List[float]:
+        """Per-stage device milliseconds for the timing window (call after its results arrived)."""
+        token = int(time.monotonic_ns() & 0x7FFFFFFF) | 1
+        self.health.g[G_TIMING_REQ] = token
+        t0 = time.monotonic()
+        while any(int(self.health.w[w, W_TIMING_ACK]) != token for w in self.order):
+            if time.monotonic() - t0 > timeout:
+                raise TimeoutError("stages did not report their timing")
+            time.sleep(1e-3)
+        self.health.g[G_TIMING_REQ] = 0
+        return [int(self.health.w[w, W_ELAPSED_US]) / 1000.0 for w in self.order]
+
+    @property
+    def feed_index(self) -> int:
+        """Dense index (within the current epoch) the next fed micro-batch will get."""
+        return self._k_feed
 
     def inject_kill(self, stage_index: int) -> int:
         """Fault injection: mark the worker currently running stage `stage_index` dead."""

@@ -78,6 +78,20 @@ class StageExecutor:
     def enqueue(self, slot: int, batch: int, stream: int = 0) -> None:
         N.check(self.lib.adapt_stage_enqueue(self.handle, slot, batch, stream))
 
+    def profile(self, slot: int, batch: int, stream: int = 0, reps: int = 5) -> List[dict]:
+        """Per-op mean device time (CUDA events around each launch) with the op's algorithmic work."""
+        n = len(self.program.ops)
+        ms = (C.c_float * n)()
+        N.check(self.lib.adapt_stage_profile(self.handle, slot, batch, stream, reps, ms, n))
+        out = []
+        for op, t in zip(self.program.ops, ms):
+            # algorithmic work uses the layer's true input channels (the stem stores 3 as 8)
+            cin = self.entries[op.weight].geom[2] if op.kind == N.OP_CONV else 0
+            macs = batch * op.Ho * op.Wo * op.Cout * op.kh * op.kw * cin
+            out.append({"layers": op.layers, "kind": op.kind, "ms": float(t), "macs": int(macs),
+                        "shape": [op.H, op.W, op.Cin, op.Cout, op.kh, op.stride]})
+        return out
+
     def read_logits(self, batch: int, stream: int = 0) -> np.ndarray:
         if "logits" not in self.program.taps:
             raise KeyError("this stage does not contain the `predictions` layer")

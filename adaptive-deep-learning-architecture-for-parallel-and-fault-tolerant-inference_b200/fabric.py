@@ -75,6 +75,7 @@ class ShmRegion:
 REC_WORDS = 6  # kind, epoch, k (dense index within the epoch), seq (global id), batch, aux
 KIND_DATA, KIND_STOP = 1, 2
 KIND_PINNED = 0x100  # header flag: `aux` points at pinned host memory (DMA straight from it)
+KIND_RESIDENT = 0x200  # header flag: the first stage's input slots were preloaded (device-resident bench leg)
 
 
 class ControlRing:
@@ -135,9 +136,10 @@ _W_WORDS = 16          # per worker
 _TABLE_BYTES = 8192    # JSON partition table
 
 # global words
-G_EPOCH, G_PHASE, G_NWORKERS, G_TABLE_LEN = 0, 1, 2, 3
+G_EPOCH, G_PHASE, G_NWORKERS, G_TABLE_LEN, G_T0, G_T1, G_TIMING_REQ = 0, 1, 2, 3, 4, 5, 6
 # per-worker words
-W_HEARTBEAT, W_STATE, W_KILL, W_ACK_QUIESCE, W_ACK_READY, W_LAST_K, W_PID, W_DEVICE, W_ERRORS = range(9)
+(W_HEARTBEAT, W_STATE, W_KILL, W_ACK_QUIESCE, W_ACK_READY, W_LAST_K, W_PID, W_DEVICE, W_ERRORS, W_ELAPSED_US,
+ W_TIMING_ACK) = range(11)
 
 
 class HealthTable:
@@ -288,6 +290,23 @@ class CudaBackend:
 
     def memset(self, dst: int, value: int, nbytes: int, stream: int) -> None:
         N.check(self.lib.adapt_memset(self.device, dst, value, int(nbytes), stream))
+
+    # timing events
+    def event_create(self) -> int:
+        p = C.c_void_p()
+        N.check(self.lib.adapt_event_create(self.device, C.byref(p)))
+        return int(p.value)
+
+    def event_record(self, event: int, stream: int) -> None:
+        N.check(self.lib.adapt_event_record(self.device, event, stream))
+
+    def event_sync(self, event: int) -> None:
+        N.check(self.lib.adapt_event_sync(self.device, event))
+
+    def event_elapsed_ms(self, start: int, stop: int) -> float:
+        v = C.c_float(0)
+        N.check(self.lib.adapt_event_elapsed_ms(self.device, start, stop, C.byref(v)))
+        return float(v.value)
 
     # liveness
     def start_heartbeat(self, word_addr: int, interval_s: float) -> int:

@@ -26,8 +26,9 @@ import numpy as np
 
 from . import _native as N
 from .dag_util import construct_model
-from .fabric import (G_EPOCH, G_PHASE, KIND_DATA, KIND_PINNED, KIND_STOP, PHASE_CONFIGURE, PHASE_QUIESCE, PHASE_RUN,
-                     PHASE_SHUTDOWN, POISON, W_ACK_QUIESCE, W_ACK_READY, W_DEVICE, W_ERRORS, W_HEARTBEAT, W_KILL, W_LAST_K, W_PID,
+from .fabric import (G_EPOCH, G_PHASE, G_T0, G_T1, G_TIMING_REQ, KIND_DATA, KIND_PINNED, KIND_RESIDENT, KIND_STOP, PHASE_CONFIGURE, PHASE_QUIESCE, PHASE_RUN,
+                     PHASE_SHUTDOWN, POISON, W_ACK_QUIESCE, W_ACK_READY, W_DEVICE, W_ERRORS, W_ELAPSED_US, W_HEARTBEAT, W_KILL, W_LAST_K, W_PID,
+                     W_TIMING_ACK,
                      ControlRing, CudaBackend, HealthTable, ResultRing, ShmRegion, StateEnum)
 
 # uint32 word indices inside a worker's flag block.  Flags live in the pinned, device-mapped
@@ -109,6 +110,8 @@ class StageWorker:
         self._stop = threading.Event()
         self._hb_thread: Optional[threading.Thread] = None
         self.launches = 0
+        self._timing_events = None
+        self._timing_armed = False
         self.on_kill: Optional[Callable[[], None]] = None
         if hasattr(self.backend, "abort_check"):  # synchronous test backends must be able to give up a wait
             self.backend.abort_check = lambda: (self.health.phase != PHASE_RUN or bool(self.health.w[self.wid, W_KILL])
@@ -129,6 +132,8 @@ class StageWorker:
         base = (self._stage_np.ctypes.data + 4095) // 4096 * 4096
         b.register_host(base, 2 * stage_bytes)
         self.stage_addr = [base, base + stage_bytes]
+        if hasattr(b, "event_create"):
+            self._timing_events = (b.event_create(), b.event_create())
         # the whole control segment (flags + result ring) is pinned and mapped into this device
         self.ctl_dev = b.register_host(self.region.addr, self.region.size)
         self.results_dev = self.ctl_dev + self.session["result_off"]
@@ -225,7 +230,11 @@ class StageWorker:
         s = k & 1
         first = self.stage_index == 0
         last = self.stage_index == self.n_stages - 1
-        if first:
+        if first and (kind & KIND_RESIDENT):
+            # measurement mode: the input batch was preloaded into both input slots (no copy); keep the
+            # copy-side flag current so that copied micro-batches can follow resident ones
+            b.write_flag(self.stream, self.flag(self.wid, F_H2D_DONE + s), k + 1)
+        elif first:
             # host -> device copy of the input on the copy stream, double buffered against compute
             nbytes = batch * self.session["in_row_bytes"]
             src = aux
@@ -262,9 +271,12 @@ class StageWorker:
                 if time.monotonic() - t0 > 30:
                     raise TimeoutError("result slot never freed")
                 time.sleep(20e-6)
+        timed = self._timing_events is not None
+        if timed and k == int(self.health.g[G_T0]):
+            b.event_record(self._timing_events[0], self.stream)
         ex.enqueue(s, batch, self.stream)
         self.launches += ex.num_launches
-        if first:
+        if first:  # (also for resident micro-batches, so that a later copied one finds the flag current)
             b.write_flag(self.stream, self.flag(self.wid, F_IN_CONSUMED + s), k + 1)
         else:
             b.write_flag(self.stream, self.flag(self.prev_wid, F_OUT_FREE + s), k + 1)
@@ -276,7 +288,21 @@ class StageWorker:
         else:
             b.write_flag(self.stream, self.flag(self.next_wid, F_IN_READY + s), k + 1)
             self.rings[self.next_wid].push((kind, epoch, k, seq, batch, 0))
+        if timed and k == int(self.health.g[G_T1]) - 1:
+            b.event_record(self._timing_events[1], self.stream)
+            self._timing_armed = True
         self.health.w[self.wid, W_LAST_K] = k
+
+    def _report_timing(self) -> None:
+        """Device time this stage spent on the micro-batches [G_T0, G_T1) (CUDA events on its stream)."""
+        token = int(self.health.g[G_TIMING_REQ])
+        if not token or int(self.health.w[self.wid, W_TIMING_ACK]) == token or not self._timing_armed:
+            return
+        self.backend.event_sync(self._timing_events[1])
+        ms = self.backend.event_elapsed_ms(self._timing_events[0], self._timing_events[1])
+        self.health.w[self.wid, W_ELAPSED_US] = int(ms * 1000.0)
+        self._timing_armed = False
+        self.health.w[self.wid, W_TIMING_ACK] = token
 
     def _heartbeat_loop(self) -> None:
         while not self._stop.is_set() and not self.dead:
@@ -340,6 +366,7 @@ class StageWorker:
                 rec = self.ring.pop(timeout=0.002)
                 if rec is None:
                     self.state.state = StateEnum.IDLE
+                    self._report_timing()
                     continue
                 if (rec[0] & 0xFF) == KIND_STOP:
                     if self.next_wid >= 0:

@@ -1,0 +1,346 @@
+#!/usr/bin/env python
+"""Headline benchmark: pipelined ResNet-50 inference through the DEFER API on N B200s.
+
+    python bench.py --gpus 1 --steps 30 --warmup 5
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference --gpus N --steps K --warmup W      # restated CPU pipeline
+
+One "step" = one micro-batch (default 128 images, BASELINE config 4's micro-batch) through the
+whole pipeline.  Rank 0 prints ONE JSON line:
+  value     images/s with the input batch already resident in the first stage's HBM slots, timed
+            with CUDA events on every stage's stream, max over stages/ranks;
+  e2e       images/s through the public API (input_q -> DEFER -> output_q) with pinned host
+            inputs: host->device copy of every step's inputs and device->host read of every
+            step's (B, 1000) result inside the timed region (wall clock);
+  roofline  the dominant kernel (conv_gemm_kernel: every Conv2D/Dense of the stage on rank 0)
+            from a per-launch CUDA-event pass, against the measured bf16 tensor peak;
+  cpu_baseline  the restated reference CPU pipeline (oracle/cpu_pipeline.py) on a bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import queue
+import statistics
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
+FLOP_PER_IMAGE = 2 * 3_857_973_248  # Keras ResNet-50 v1, SURVEY 8(d)
+CONFIG_PART_AT = {
+    1: [],
+    2: ["conv3_block4_out"],                                                 # BASELINE config 2
+    4: ["conv2_block3_out", "conv3_block4_out", "conv4_block6_out"],         # BASELINE config 3
+}
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        p = json.load(open(path))
+        return {"bf16_sustained": p.get("bf16_tflops_sustained", 1388.0), "bf16_burst": p.get("bf16_tflops", 1653.4),
+                "hbm": p.get("hbm_gbs", 6548.5), "source": "measured"}
+    return {"bf16_sustained": 1400.0, "bf16_burst": 1590.0, "hbm": 6650.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self):
+        self.path = tempfile.mktemp(prefix="adapt_clocks_", suffix=".csv")
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except OSError:
+            self.proc = None
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in open(self.path):
+            f = [c.strip() for c in line.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        try:
+            os.unlink(self.path)
+        except OSError:
+            pass
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        busy = sorted(sm)[len(sm) // 2:]  # upper half = samples under load
+        return {"sm_mhz": statistics.median(busy), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def part_at_for(model, n: int):
+    from adapt_b200.dispatcher import balanced_part_at
+
+    return CONFIG_PART_AT.get(n) if n in CONFIG_PART_AT else balanced_part_at(model, n)
+
+
+# ---------------------------------------------------------------------------------------------
+def run_reference(args) -> int:
+    """Reference arm: the restated reference CPU pipeline on the box's host cores (rank 0 only)."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return 0
+    import adapt_b200
+    from oracle.cpu_pipeline import time_cpu_pipeline
+
+    model = adapt_b200.ResNet50(weights=None)
+    weights = {l.name: l.get_weights() for l in model.layers if l.get_weights()}
+    part_at = part_at_for(model, args.gpus)
+    sample = args.ref_batch
+    r = time_cpu_pipeline(weights, part_at, sample, args.steps, args.warmup)
+    line = {
+        "impl": "reference", "metric": "images_per_sec", "value": r["value"], "unit": "img/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["seconds"] / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(args.gpus, args.batch, part_at), "part_at": part_at, "micro_batch": args.batch,
+                   "sample_micro_batch": sample},
+        "cpu_baseline": {"value": r["value"], "unit": "img/s", "cores": r["cores"], "kind": "port",
+                         "sample": f"{args.steps} micro-batches of {sample} images (a {sample}/{args.batch} sample of the "
+                                   f"{args.batch}-image step) through {r['stages']} localhost worker process(es), "
+                                   f"{r['threads_per_stage']} torch threads each; restated reference CPU pipeline, "
+                                   f"TensorFlow unavailable, lossless zfp+lz4 codec omitted"},
+        "e2e": {"value": r["value"], "unit": "img/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def workload_name(n: int, batch: int, part_at) -> str:
+    return (f"ResNet-50 (Keras v1, random init) {n}-stage pipeline, micro-batch {batch}, bf16 activations / fp32 accumulate, "
+            f"part_at={part_at if part_at else '[] (single chunk)'}")
+
+
+# ---------------------------------------------------------------------------------------------
+def drive(defer, in_q, out_q, items, timeout=60.0):
+    """Feed `items` and collect as many results; returns (results, wall seconds)."""
+    t = threading.Thread(target=lambda: [in_q.put(x) for x in items], daemon=True)
+    t0 = time.perf_counter()
+    t.start()
+    outs = []
+    while len(outs) < len(items):
+        try:
+            outs.append(out_q.get(timeout=0.5))
+        except queue.Empty:
+            if defer.error:
+                raise RuntimeError(defer.error)
+            if time.perf_counter() - t0 > timeout:
+                raise TimeoutError(f"bench: {len(outs)}/{len(items)} results; {defer.debug_state()}")
+    dt = time.perf_counter() - t0
+    t.join()
+    return outs, dt
+
+
+def run_ours(args) -> int:
+    import numpy as np
+    import torch
+
+    import adapt_b200
+    from adapt_b200 import _native as N
+    from adapt_b200.dispatcher import DEFER, ResidentBatch
+    from adapt_b200.node import Node
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    N.require_gpu()  # no CPU fallback: fail loudly
+    if world > 1:
+        import torch.distributed as dist
+
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group(backend="cpu:gloo,cuda:nccl", init_method="env://")
+        if world != args.gpus:
+            raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    n = args.gpus
+    B = args.batch
+    model = adapt_b200.ResNet50(weights=None)
+    part_at = part_at_for(model, n)
+
+    if world > 1 and rank > 0:
+        Node(model, device=local_rank).run()      # worker role: blocks until the dispatcher shuts down
+        dist.barrier()
+        dist.destroy_process_group()
+        return 0
+
+    devices = [f"cuda:{i}" for i in range(n)]
+    defer = DEFER(devices, mode="bf16", max_batch=B, warm_batches=[B], heartbeat_timeout=0.05,
+                  max_inflight=max(2 * n + 4, 12))
+    in_q, out_q = queue.Queue(2 * n + 8), queue.Queue()
+    th = threading.Thread(target=defer.run_defer, args=(model, part_at, in_q, out_q), daemon=True)
+    th.start()
+    defer.wait_ready(600)
+
+    rng = np.random.default_rng(0)
+    x = rng.uniform(0, 255, (B, 224, 224, 3)).astype(np.float32)
+    x = np.ascontiguousarray(x[..., ::-1] - np.array([103.939, 116.779, 123.68], dtype=np.float32))
+    K, W = args.steps, args.warmup
+    clocks = ClockSampler()
+
+    # ---------------- leg 1: device-resident inputs, CUDA-event timing on every stage ----------------
+    defer.preload_input(x)
+    drive(defer, in_q, out_q, [ResidentBatch(B)] * W)
+    torch.cuda.synchronize()
+    launches0 = defer.gpu_launches
+    clocks.start()
+    k0 = defer.feed_index
+    defer.set_timing_window(k0, k0 + K)
+    outs, wall_resident = drive(defer, in_q, out_q, [ResidentBatch(B)] * K)
+    stage_ms = defer.collect_timing()
+    torch.cuda.synchronize()
+    clock_info = clocks.stop()
+    local_launches = defer.gpu_launches - launches0
+    ms_total = max(stage_ms)
+    value = K * B / (ms_total / 1e3)
+    probs_sum = float(np.float64(outs[-1]).sum())
+
+    # ---------------- leg 2: end to end through the public API, pinned host inputs ----------------
+    pinned = [torch.from_numpy(x).pin_memory() for _ in range(3)]
+    drive(defer, in_q, out_q, [pinned[i % 3] for i in range(W)])
+    defer.latencies_ms.clear()
+    e2e_outs, e2e_wall = drive(defer, in_q, out_q, [pinned[i % 3] for i in range(K)])
+    e2e_value = K * B / e2e_wall
+    lat = sorted(defer.latencies_ms)
+    p50 = lat[len(lat) // 2] if lat else None
+    p99 = lat[min(len(lat) - 1, int(len(lat) * 0.99))] if lat else None
+
+    # ---------------- per-launch pass on rank 0's stage: roofline of the dominant kernel ----------------
+    wk = defer.workers[0]
+    prof = wk.executor.profile(0, B, wk.stream, reps=5)
+    conv = [p for p in prof if p["kind"] == N.OP_CONV]
+    conv_ms = sum(p["ms"] for p in conv)
+    conv_flop = 2.0 * sum(p["macs"] for p in conv)
+    all_ms = sum(p["ms"] for p in prof)
+    peaks = measured_peaks()
+    achieved_tf = conv_flop / (conv_ms / 1e3) / 1e12
+    roofline = {
+        "bound": "tensor", "kernel": "conv_gemm_kernel", "achieved": round(achieved_tf, 2), "peak": peaks["bf16_sustained"],
+        "unit": "TFLOP/s", "frac": round(achieved_tf / peaks["bf16_sustained"], 4), "traffic": None,
+        "peak_source": f"{peaks['source']} bf16 sustained (kernel timed inside a long step)",
+        "launches_per_step": len(conv), "avg_launch_ms": round(conv_ms / max(1, len(conv)), 5),
+        "kernel_share_of_step": round(conv_ms / all_ms, 4),
+        "algorithmic_flop_per_launch_avg": conv_flop / max(1, len(conv)),
+        "whole_pipeline_frac": round(value * FLOP_PER_IMAGE / 1e12 / (n * peaks["bf16_sustained"]), 4),
+        "whole_pipeline_frac_4p1gflop": round(value * 4.1e9 / 1e12 / (n * peaks["bf16_sustained"]), 4),
+    }
+    if args.dump_ops:
+        os.makedirs(os.path.dirname(os.path.abspath(args.dump_ops)), exist_ok=True)
+        json.dump({"batch": B, "stage": 0, "ops": prof}, open(args.dump_ops, "w"), indent=1)
+
+    # ---------------- fail-over leg (needs a stage to lose) ----------------
+    failover = None
+    if n >= 2 and not args.no_failover:
+        pre = [pinned[i % 3] for i in range(3 * n)]
+        t = threading.Thread(target=lambda: [in_q.put(p) for p in pre + pre], daemon=True)
+        t.start()
+        got = 0
+        t_kill = None
+        while got < 2 * len(pre):
+            out_q.get(timeout=120)
+            got += 1
+            if got == len(pre) // 2 and t_kill is None:
+                defer.inject_kill(n // 2)
+                t_kill = time.perf_counter()
+        t.join()
+        failover = {"failover_ms": defer.stats["failover_ms"][-1] if defer.stats["failover_ms"] else None,
+                    "reconfig_ms": defer.stats.get("reconfig_ms", [None])[-1], "replayed": defer.stats["replayed"],
+                    "delivered_exactly_once": got == 2 * len(pre) and out_q.empty(), "stages_after": len(defer.order)}
+
+    from adapt_b200.dag_util import build_weight_table, compile_part
+
+    _, windex = build_weight_table(model)
+    launches_per_step = sum(len(compile_part(p, windex).ops) for p in defer._partition(model, part_at))
+    assert world > 1 or local_launches == launches_per_step * K, (local_launches, launches_per_step, K)
+    defer.shutdown()
+    th.join(60)
+
+    # ---------------- CPU baseline on a bounded sample (N=1 only) ----------------
+    cpu = None
+    if n == 1 and not args.no_cpu_baseline:
+        from oracle.cpu_pipeline import time_cpu_pipeline
+
+        weights = {l.name: l.get_weights() for l in model.layers if l.get_weights()}
+        r = time_cpu_pipeline(weights, [], args.ref_batch, args.cpu_steps, 1)
+        cpu = {"value": round(r["value"], 2), "unit": "img/s", "cores": r["cores"], "kind": "port",
+               "sample": f"{args.cpu_steps} micro-batches of {args.ref_batch} images through the restated reference CPU "
+                         f"pipeline (1 localhost worker, torch CPU fp32, {r['threads_per_stage']} threads), {r['seconds']:.1f} s"}
+
+    line = {
+        "metric": "images_per_sec", "value": round(value, 1), "unit": "img/s", "n_gpus": n, "steps": K, "warmup": W,
+        "ms_per_step": round(ms_total / K, 4), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": workload_name(n, B, part_at), "part_at": part_at, "micro_batch": B,
+                   "l2": "per-step working set (activations of 53 convolutions x micro-batch, > 5 GB at B=128) far exceeds the "
+                         "126 MB L2; input slots alternate", "handoff": "peer stores over NVLink + stream memory ops",
+                   "stage_ms_per_step": [round(m / K, 4) for m in stage_ms], "timing": "CUDA events per stage stream, max over stages"},
+        "clocks": clock_info,
+        "e2e": {"value": round(e2e_value, 1), "unit": "img/s", "h2d_bytes_per_step": int(x.nbytes),
+                "d2h_bytes_per_step": B * 1000 * 4, "p50_latency_ms": p50, "p99_latency_ms": p99,
+                "timing": "wall clock around K queue items"},
+        "gpu_launches": int(launches_per_step * K),
+        "roofline": roofline,
+        "cpu_baseline": cpu,
+        "failover": failover,
+        "checks": {"probs_row_sum": probs_sum / B, "wall_resident_img_s": round(K * B / wall_resident, 1)},
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main() -> int:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=128, help="micro-batch (images per step)")
+    ap.add_argument("--ref-batch", type=int, default=16, help="micro-batch of the CPU reference sample")
+    ap.add_argument("--cpu-steps", type=int, default=12)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-failover", action="store_true")
+    ap.add_argument("--dump-ops", default=None, help="write the per-launch timing table (JSON) here")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3  # timing rule: at least 3 warm-up steps
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -130,6 +130,11 @@ int adapt_stage_enqueue(adapt_stage_t* stage, int slot, int batch, void* stream)
  * synchronising `stream`.  No reference counterpart (the reference never inspects activations). */
 int adapt_stage_read_tensor(adapt_stage_t* stage, int tensor, void* host_dst, size_t bytes, void* stream);
 
+/* Measurement aid: run the ops of (`slot`, `batch`) one by one `reps` times on `stream`, each bracketed
+ * by CUDA events, and return the mean duration of every op (ms) in ms_per_op[n_ops].  Synchronises. */
+int adapt_stage_profile(adapt_stage_t* stage, int slot, int batch, void* stream, int reps, float* ms_per_op,
+                        int n_ops);
+
 /* Number of kernel launches one enqueue() of `batch` images performs (for bench accounting). */
 int adapt_stage_num_launches(adapt_stage_t* stage, int batch);
 
