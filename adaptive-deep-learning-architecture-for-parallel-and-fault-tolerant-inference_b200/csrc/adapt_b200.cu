@@ -164,6 +164,8 @@ struct ConvGeom {
 struct ConvLaunch {
     CUtensorMap tmap_a;
     CUtensorMap tmap_b;
+    CUtensorMap tmap_out;  // [M, N] bf16 output, 64-column x 32-row boxes (staged epilogue)
+    CUtensorMap tmap_res;  // [M, N] bf16 residual, same boxes
     adapt::ConvGemmParams p;
     int block_n = 0;
     int a_mode = 0;
@@ -281,6 +283,20 @@ int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const vo
     } else {
         L->tmap_a = L->tmap_b;  // unused by the gather kernel
     }
+    // staged epilogue: bf16 output whose width the tile divides; the direct epilogue remains for fp32
+    // logits (Dense) and as a switchable fall-back (ADAPT_EPI_DIRECT=1)
+    const int epi_mode = env_int("ADAPT_EPI_MODE", 1);  // 0 direct, 1 staged + TMA store, 2 staged + coalesced st.global
+    L->tmap_out = L->tmap_b;
+    L->tmap_res = L->tmap_b;
+    p.epi_tma = (!out_f32 && g.Cout % bn == 0) ? epi_mode : 0;
+    if (p.epi_tma) {
+        rc = encode_tiled_2d_bf16(&L->tmap_out, out, (uint64_t)g.Cout, (uint64_t)M, adapt::kEpiCols, 32);
+        if (rc) return rc;
+        if (residual) {
+            rc = encode_tiled_2d_bf16(&L->tmap_res, residual, (uint64_t)g.Cout, (uint64_t)M, adapt::kEpiCols, 32);
+            if (rc) return rc;
+        }
+    }
     return ADAPT_OK;
 }
 
@@ -289,13 +305,13 @@ void launch_conv_bn(const ConvLaunch& L, cudaStream_t s) {
     using Cfg = adapt::ConvGemmCfg<BN>;
     switch (L.a_mode) {
         case adapt::A_TILED:
-            adapt::conv_gemm_kernel<BN, adapt::A_TILED><<<L.grid, 192, Cfg::kSmemBytes, s>>>(L.tmap_a, L.tmap_b, L.p);
+            adapt::conv_gemm_kernel<BN, adapt::A_TILED><<<L.grid, 192, Cfg::kSmemBytes, s>>>(L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
             break;
         case adapt::A_IM2COL:
-            adapt::conv_gemm_kernel<BN, adapt::A_IM2COL><<<L.grid, 192, Cfg::kSmemBytes, s>>>(L.tmap_a, L.tmap_b, L.p);
+            adapt::conv_gemm_kernel<BN, adapt::A_IM2COL><<<L.grid, 192, Cfg::kSmemBytes, s>>>(L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
             break;
         default:
-            adapt::conv_gemm_kernel<BN, adapt::A_GATHER><<<L.grid, 320, Cfg::kSmemBytes, s>>>(L.tmap_a, L.tmap_b, L.p);
+            adapt::conv_gemm_kernel<BN, adapt::A_GATHER><<<L.grid, 320, Cfg::kSmemBytes, s>>>(L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
             break;
     }
 }

@@ -46,6 +46,7 @@ struct ConvGemmParams {
     __nv_bfloat16* out_bf16;        // [M, N] or nullptr
     float* out_f32;                 // [M, N] or nullptr (Dense logits)
     int relu;
+    int epi_tma;  // 1: staged epilogue (TMA residual load + TMA store); 0: direct per-thread global accesses
     // A_GATHER source
     const __nv_bfloat16* in;
 };
@@ -55,15 +56,24 @@ constexpr int kBlockK = 64;  // 64 bf16 = one 128-byte swizzle row
 constexpr int kUmmaK = 16;
 constexpr int kABytes = kBlockM * kBlockK * 2;
 
+// Epilogue staging (per epilogue warp): the warp's 32-row x 64-column slab travels through shared
+// memory in the 128-byte-swizzled layout so that both the residual read and the output write are
+// full-line TMA transfers instead of per-thread row-strided accesses.
+constexpr int kEpiCols = 64;                        // columns per staged chunk (64 bf16 = 128 B per row)
+constexpr int kEpiSlabBytes = 32 * kEpiCols * 2;    // 4 KiB: 32 rows x 128 B
+constexpr int kEpiWarpBytes = 4 * kEpiSlabBytes;    // residual[2] + out[2]
+
 template <int BLOCK_N>
 struct ConvGemmCfg {
     static constexpr int kBBytes = BLOCK_N * kBlockK * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
-    static constexpr int kStagesRaw = (196 * 1024) / kStageBytes;
+    static constexpr int kEpiBytes = 4 * kEpiWarpBytes + 4 * 2 * BLOCK_N * 4;  // staging + per-warp scale/bias
+    static constexpr int kBarrierBytes = 256;
+    static constexpr int kBudget = 227 * 1024 - 1024 - kBarrierBytes - kEpiBytes;
+    static constexpr int kStagesRaw = kBudget / kStageBytes;
     static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
     static constexpr int kTmemCols = 2 * BLOCK_N;  // double-buffered accumulator (power of 2 >= 32)
-    static constexpr int kBarrierBytes = 256;
-    static constexpr int kSmemBytes = kStages * kStageBytes + kBarrierBytes + 1024;  // +1024 alignment slack
+    static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + kBarrierBytes + 1024;  // +1024 alignment slack
 };
 
 template <int A_MODE>
@@ -74,21 +84,26 @@ constexpr int conv_gemm_threads() {
 template <int BLOCK_N, int A_MODE>
 __global__ void __launch_bounds__(conv_gemm_threads<A_MODE>(), 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                 const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
                  const ConvGemmParams p) {
     using Cfg = ConvGemmCfg<BLOCK_N>;
     constexpr int kStages = Cfg::kStages;
-    static_assert(BLOCK_N % 32 == 0 && BLOCK_N >= 64 && BLOCK_N <= 256, "BLOCK_N");
+    static_assert(BLOCK_N % 64 == 0 && BLOCK_N >= 64 && BLOCK_N <= 256, "BLOCK_N");
+    static_assert(kStages >= 2, "pipeline too shallow");
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* smem_a = smem;
     uint8_t* smem_b = smem + kStages * kABytes;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+    uint8_t* smem_epi = smem + kStages * Cfg::kStageBytes;                   // 4 x kEpiWarpBytes, 1024-aligned
+    float* smem_sb = reinterpret_cast<float*>(smem_epi + 4 * kEpiWarpBytes);  // 4 x [scale BLOCK_N | bias BLOCK_N]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes + Cfg::kEpiBytes);
     uint64_t* full_bar = bars;
     uint64_t* empty_bar = bars + kStages;
     uint64_t* tmem_full_bar = bars + 2 * kStages;
     uint64_t* tmem_empty_bar = bars + 2 * kStages + 2;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+    uint64_t* res_bar = bars + 2 * kStages + 4;  // [4 warps][2 buffers]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 12);
 
     const int warp_idx = __shfl_sync(0xffffffff, threadIdx.x / 32, 0);
     const int lane = threadIdx.x % 32;
@@ -105,6 +120,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         for (int i = 0; i < 2; ++i) {
             ptx::mbar_init(&tmem_full_bar[i], 1);
             ptx::mbar_init(&tmem_empty_bar[i], 4);  // one arrive per epilogue warp
+        }
+        for (int i = 0; i < 8; ++i) ptx::mbar_init(&res_bar[i], 1);
+        if (p.epi_tma) {
+            ptx::prefetch_tmap(&tmap_out);
+            if (p.residual != nullptr) ptx::prefetch_tmap(&tmap_res);
         }
         ptx::fence_mbar_init();
     }
@@ -194,16 +214,126 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         // ===================== epilogue =====================
         const int lane_group = warp_idx & 3;  // TMEM lanes this warp may touch: [32*lane_group, +32)
         int tile_iter = 0;
+        uint32_t res_uses = 0;  // bit b: parity the next wait on residual buffer b expects
+        uint32_t out_it = 0;    // running count of staged output chunks (selects the out buffer)
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tile_iter) {
             const int m_blk = tile / p.n_tiles;
             const int n_blk = tile % p.n_tiles;
             const int acc_stage = tile_iter & 1;
             const uint32_t acc_phase = (tile_iter >> 1) & 1;
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lane_group * 32) << 16) + acc_stage * BLOCK_N;
+            if (p.epi_tma) {
+                // ---------- staged epilogue: TMEM -> regs -> swizzled smem slab -> TMA store ----------
+                constexpr int kChunks = BLOCK_N / kEpiCols;
+                uint8_t* my_epi = smem_epi + lane_group * kEpiWarpBytes;  // res[0] res[1] out[0] out[1]
+                float* my_scale = smem_sb + lane_group * 2 * BLOCK_N;
+                float* my_bias = my_scale + BLOCK_N;
+                uint64_t* my_res_bar = res_bar + lane_group * 2;
+                const int m_row0 = m_blk * kBlockM + lane_group * 32;
+                const int n_tile0 = n_blk * BLOCK_N;
+                const bool slab_ok = m_row0 < p.M;
+                const bool has_res = p.residual != nullptr;
+                // this tile's scale / bias -> per-warp smem (read back as broadcasts)
+                for (int i = lane; i < BLOCK_N / 4; i += 32) {
+                    reinterpret_cast<float4*>(my_scale)[i] = __ldg(reinterpret_cast<const float4*>(p.scale + n_tile0) + i);
+                    reinterpret_cast<float4*>(my_bias)[i] = __ldg(reinterpret_cast<const float4*>(p.bias + n_tile0) + i);
+                }
+                if (has_res && slab_ok && lane == 0) {
+#pragma unroll
+                    for (int c = 0; c < (kChunks < 2 ? kChunks : 2); ++c) {
+                        ptx::mbar_expect_tx(&my_res_bar[c], kEpiSlabBytes);
+                        ptx::tma_load_2d(my_epi + c * kEpiSlabBytes, &tmap_res, &my_res_bar[c], n_tile0 + c * kEpiCols,
+                                         m_row0);
+                    }
+                }
+                __syncwarp();
+                ptx::mbar_wait(&tmem_full_bar[acc_stage], acc_phase);
+                ptx::tc_fence_after();
+#pragma unroll 1
+                for (int c = 0; c < kChunks; ++c) {
+                    uint32_t v0[32], v1[32];
+                    ptx::tmem_ld_32x32b_x32(taddr + c * kEpiCols, v0);
+                    ptx::tmem_ld_32x32b_x32(taddr + c * kEpiCols + 32, v1);
+                    ptx::tmem_ld_wait();
+                    if (c == kChunks - 1) {
+                        ptx::tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) ptx::mbar_arrive(&tmem_empty_bar[acc_stage]);
+                    }
+                    if (!slab_ok) continue;
+                    const int buf = c & 1;
+                    uint8_t* res_slab = my_epi + buf * kEpiSlabBytes;
+                    uint8_t* out_slab = my_epi + (2 + (out_it & 1)) * kEpiSlabBytes;
+                    ++out_it;
+                    if (has_res) {
+                        ptx::mbar_wait(&my_res_bar[buf], (res_uses >> buf) & 1);
+                        res_uses ^= (1u << buf);
+                    }
+                    // the TMA store issued from this out buffer two chunks ago must have read it
+                    if (p.epi_tma == 1 && lane == 0) ptx::tma_store_wait_read<1>();
+                    __syncwarp();
+                    const float* sc = my_scale + c * kEpiCols;
+                    const float* bi = my_bias + c * kEpiCols;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {  // 8 columns = one 16-byte unit of this thread's row
+                        const uint32_t* vv = (j < 4) ? &v0[j * 8] : &v1[(j - 4) * 8];
+                        float y[8];
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) y[e] = fmaf(__uint_as_float(vv[e]), sc[j * 8 + e], bi[j * 8 + e]);
+                        const int sw = ((j ^ (lane & 7)) << 4) + lane * 128;
+                        if (has_res) {
+                            const uint4 rv = *reinterpret_cast<const uint4*>(res_slab + sw);
+                            const __nv_bfloat162* r2 = reinterpret_cast<const __nv_bfloat162*>(&rv);
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                const float2 f = __bfloat1622float2(r2[e]);
+                                y[2 * e] += f.x;
+                                y[2 * e + 1] += f.y;
+                            }
+                        }
+                        if (p.relu) {
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) y[e] = fmaxf(y[e], 0.0f);
+                        }
+                        uint4 ov;
+                        __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&ov);
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(y[2 * e], y[2 * e + 1]);
+                        *reinterpret_cast<uint4*>(out_slab + sw) = ov;
+                    }
+                    if (p.epi_tma == 1) ptx::fence_proxy_async_smem();  // slab writes -> visible to the TMA store
+                    __syncwarp();
+                    if (lane == 0) {
+                        if (has_res && c + 2 < kChunks) {  // residual buffer fully consumed: prefetch chunk c+2
+                            ptx::mbar_expect_tx(&my_res_bar[buf], kEpiSlabBytes);
+                            ptx::tma_load_2d(res_slab, &tmap_res, &my_res_bar[buf], n_tile0 + (c + 2) * kEpiCols, m_row0);
+                        }
+                        if (p.epi_tma == 1) {
+                            ptx::tma_store_2d(&tmap_out, out_slab, n_tile0 + c * kEpiCols, m_row0);
+                            ptx::tma_store_commit();
+                        }
+                    }
+                    if (p.epi_tma == 2) {
+                        // coalesced write-out: 8 lanes cover one 128-byte row segment, 4 rows per instruction;
+                        // plain stores (also valid for a peer-mapped destination on the next stage's GPU)
+                        __nv_bfloat16* gout = p.out_bf16 + static_cast<size_t>(m_row0) * p.N + n_tile0 + c * kEpiCols;
+                        const int ch = lane & 7;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int row = i * 4 + (lane >> 3);
+                            const uint4 val = *reinterpret_cast<const uint4*>(out_slab + row * 128 + ((ch ^ (row & 7)) << 4));
+                            if (m_row0 + row < p.M)
+                                *reinterpret_cast<uint4*>(gout + static_cast<size_t>(row) * p.N + ch * 8) = val;
+                        }
+                        // (the slab is re-used two chunks later, after at least one __syncwarp)
+                    }
+                }
+                continue;
+            }
             ptx::mbar_wait(&tmem_full_bar[acc_stage], acc_phase);
             ptx::tc_fence_after();
             const int m = m_blk * kBlockM + lane_group * 32 + lane;
             const bool row_ok = m < p.M;
-            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lane_group * 32) << 16) + acc_stage * BLOCK_N;
 #pragma unroll 1
             for (int chunk = 0; chunk < BLOCK_N / 32; ++chunk) {
                 uint32_t v[32];
@@ -265,6 +395,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 }
             }
         }
+        // all of this warp's bulk stores must have landed before the CTA may exit
+        if (p.epi_tma && lane == 0) ptx::tma_store_wait<0>();
     } else {
         // ===================== software im2col producers (A_GATHER) =====================
         if (A_MODE == A_GATHER) {

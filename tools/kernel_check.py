@@ -139,9 +139,15 @@ def run_perf() -> int:
         ("conv5_1x1_512_2048", 7, 7, 512, 2048, 1, 1, 0),
         ("conv3_s2_256_128", 56, 56, 256, 128, 1, 2, 0),
         ("stem_gather", 224, 224, 8, 64, 7, 2, 3),
+        ("conv2_3_res", 56, 56, 64, 256, 1, 1, 0, 1),
+        ("conv3_3_res", 28, 28, 128, 512, 1, 1, 0, 1),
+        ("conv4_3_res", 14, 14, 256, 1024, 1, 1, 0, 1),
+        ("conv5_3_res", 7, 7, 512, 2048, 1, 1, 0, 1),
     ]
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
-    for (name, H, W, Cin, Cout, k, stride, pad) in layers:
+    for lay in layers:
+        (name, H, W, Cin, Cout, k, stride, pad) = lay[:8]
+        use_res = len(lay) > 8 and lay[8]
         x = torch.randn(B, H, W, Cin, device=dev).to(torch.bfloat16)
         w = (torch.randn(Cout, k, k, Cin, device=dev) / (k * k * Cin) ** 0.5).to(torch.bfloat16)
         scale = torch.ones(Cout, device=dev)
@@ -149,6 +155,7 @@ def run_perf() -> int:
         Ho = (H + 2 * pad - k) // stride + 1
         Wo = (W + 2 * pad - k) // stride + 1
         out = torch.empty(B, Ho, Wo, Cout, device=dev, dtype=torch.bfloat16)
+        res = torch.randn(B, Ho, Wo, Cout, device=dev).to(torch.bfloat16) if use_res else None
         for bn in (64, 128, 256):
             if bn > 64 and Cout < bn:
                 continue
@@ -158,7 +165,8 @@ def run_perf() -> int:
                 e0 = torch.cuda.Event(enable_timing=True)
                 e1 = torch.cuda.Event(enable_timing=True)
                 e0.record()
-                rc = lib.adapt_conv2d_bf16(0, x.data_ptr(), w.data_ptr(), scale.data_ptr(), bias.data_ptr(), None,
+                rc = lib.adapt_conv2d_bf16(0, x.data_ptr(), w.data_ptr(), scale.data_ptr(), bias.data_ptr(),
+                                           res.data_ptr() if use_res else None,
                                            out.data_ptr(), 0, B, H, W, Cin, Cout, k, k, stride, pad, 1, -1, bn,
                                            torch.cuda.current_stream().cuda_stream)
                 e1.record()
@@ -173,7 +181,8 @@ def run_perf() -> int:
             ms = sum(times) / len(times)
             M = B * Ho * Wo
             flops = 2.0 * M * Cout * k * k * Cin
-            bytes_ = 2.0 * (B * H * W * Cin + M * Cout + Cout * k * k * Cin)
+            bytes_ = 2.0 * (M * (stride * stride if k == 1 else 1) * Cin / (stride * stride) + M * Cout * (2 if use_res else 1)
+                            + Cout * k * k * Cin)
             print(json.dumps({"layer": name, "bn": bn, "ms": round(ms, 4), "tflops": round(flops / ms / 1e9, 1),
                               "gbs": round(bytes_ / ms / 1e6, 1)}), flush=True)
     return 0
