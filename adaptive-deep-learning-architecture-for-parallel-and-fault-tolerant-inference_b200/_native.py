@@ -19,6 +19,7 @@ MODE_BF16, MODE_FP32_CHECK = 0, 1
 OP_INGEST, OP_CONV, OP_MAXPOOL, OP_GAP, OP_SOFTMAX, OP_AFFINE, OP_ZEROPAD = 0, 1, 2, 3, 4, 5, 6
 T_INTERNAL, T_INPUT, T_OUTPUT = 0, 1, 2
 DT_WORK, DT_F32 = 0, 1
+NOALLOC_MAX_LOGITS = 256 * 1024  # ADAPT_NOALLOC_MAX_LOGITS
 
 
 class WeightDesc(C.Structure):
@@ -78,6 +79,7 @@ SYMBOLS = {
     "adapt_stage_destroy": (None, [_VP]),
     "adapt_conv2d_bf16": (_I, [_I, _VP, _VP, _VP, _VP, _VP, _VP, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I,
                                _VP]),
+    "adapt_dense_softmax_noalloc": (_I, [_I, _VP, _VP, _VP, _VP, _VP, _I, _I, _I, _VP]),
     "adapt_device_alloc": (_I, [_I, _SZ, C.POINTER(_VP)]),
     "adapt_device_free": (_I, [_I, _VP]),
     "adapt_peer_enable": (_I, [_I, _I]),

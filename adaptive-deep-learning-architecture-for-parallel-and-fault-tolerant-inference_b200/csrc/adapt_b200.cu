@@ -856,6 +856,77 @@ int adapt_conv2d_bf16(int device, const void* in, const void* w, const float* sc
     return run_conv_launch(L, reinterpret_cast<cudaStream_t>(stream));
 }
 
+// ---------------------------------------------------------------- classifier head without allocations
+}  // extern "C"  (the scratch array below needs C++ linkage-free file scope)
+
+// Fixed scratch for adapt_dense_softmax_noalloc: the fp32 logits that sit between the Dense
+// GEMM and the row softmax.  ADAPT_NOALLOC_MAX_LOGITS floats = 1 MiB, reserved on every GPU
+// that loads this library for as long as the process lives.
+static __device__ __align__(256) float g_noalloc_logits[ADAPT_NOALLOC_MAX_LOGITS];
+
+namespace {
+// Device address of g_noalloc_logits per device.  In host code the array's name is only a
+// stand-in symbol, never an address a kernel could use, so the real address is looked up once
+// per device (with that device current) and cached.
+float* g_noalloc_logits_addr[64] = {nullptr};
+
+int noalloc_scratch(int device, float** out) {
+    if (device < 0 || device >= 64) return fail(ADAPT_EINVAL, "noalloc: device %d unsupported", device);
+    if (g_noalloc_logits_addr[device] == nullptr) {
+        float* ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_noalloc_logits);
+        if (e != cudaSuccess || ptr == nullptr)
+            return fail(ADAPT_ECUDA, "cudaGetSymbolAddress(g_noalloc_logits) on device %d: %s", device,
+                        cudaGetErrorString(e));
+        g_noalloc_logits_addr[device] = ptr;
+    }
+    *out = g_noalloc_logits_addr[device];
+    return ADAPT_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int adapt_dense_softmax_noalloc(int device, const void* in, const void* w, const float* scale, const float* bias,
+                                float* probs, int batch, int cin, int cout, void* stream_v) {
+    if (!in || !w || !scale || !bias || !probs) return fail(ADAPT_EINVAL, "dense_softmax_noalloc: null pointer");
+    if (batch <= 0 || cin <= 0 || cout <= 0 || cin % 8 != 0 || cout % 8 != 0)
+        return fail(ADAPT_EINVAL, "dense_softmax_noalloc: need batch > 0 and cin, cout positive multiples of 8");
+    if ((long long)batch * cout > (long long)ADAPT_NOALLOC_MAX_LOGITS)
+        return fail(ADAPT_EINVAL,
+                    "dense_softmax_noalloc: batch %d x cout %d = %lld logits exceeds the fixed scratch of %d floats "
+                    "(ADAPT_NOALLOC_MAX_LOGITS); split the batch or use the stage API",
+                    batch, cout, (long long)batch * cout, (int)ADAPT_NOALLOC_MAX_LOGITS);
+    int rc = require_device(device);
+    if (rc) return rc;
+    static bool attr_done[64] = {false};
+    if (device < 64 && !attr_done[device]) {  // first call on this device: one-time set-up, no allocation
+        rc = init_conv_kernels_for_device();
+        if (rc) return rc;
+        attr_done[device] = true;
+    }
+    float* logits = nullptr;
+    rc = noalloc_scratch(device, &logits);
+    if (rc) return rc;
+    int num_sms = 0;
+    CUDA_TRY(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, device));
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
+    // Dense as a 1x1 convolution over M = batch rows, fp32 logits into the fixed scratch (every
+    // element of logits[0 : batch*cout) is overwritten, so nothing has to be cleared first) ...
+    ConvGeom g{batch, 1, 1, cin, 1, 1, cout, 1, 1, 1, 0};
+    ConvLaunch L;
+    rc = build_conv_launch(&L, g, in, w, scale, bias, nullptr, logits, /*out_f32=*/true, /*relu=*/0, -1, 0, num_sms);
+    if (rc) return rc;
+    rc = run_conv_launch(L, stream);
+    if (rc) return rc;
+    // ... then the row softmax from the scratch into the caller's output.
+    const int warps_per_block = 4;
+    const unsigned blocks = (unsigned)((batch + warps_per_block - 1) / warps_per_block);
+    adapt::softmax_rows_kernel<<<blocks, warps_per_block * 32, 0, stream>>>(logits, probs, batch, cout);
+    CUDA_TRY(cudaGetLastError());
+    return ADAPT_OK;
+}
+
 // ---------------------------------------------------------------- hand-off plumbing
 int adapt_device_alloc(int device, size_t bytes, void** out) {
     if (!out || bytes == 0) return fail(ADAPT_EINVAL, "device_alloc: bad argument");

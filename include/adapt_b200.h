@@ -152,6 +152,29 @@ int adapt_conv2d_bf16(int device, const void* in, const void* w, const float* sc
                       const void* residual, void* out, int out_is_f32, int batch, int H, int W, int Cin, int Cout,
                       int kh, int kw, int stride, int pad, int relu, int a_mode, int block_n, void* stream);
 
+/* Classifier head (Dense + softmax) for callers that must not allocate device memory.
+ * This entry point has NO counterpart in the reference; it exists for users of this library whose
+ * process cannot call cudaMalloc when it needs a prediction: a serving process that handed all of
+ * its HBM to its own arenas at start-up (any later allocation would fail), a latency-critical loop
+ * that cannot afford the device-wide synchronisation and unbounded duration of an allocation, or a
+ * liveness probe of the fail-over logic that has to keep working on a GPU that is out of memory.
+ *
+ *   probs[b, :] = softmax(in[b, :] @ w^T * scale + bias)      in: bf16 [batch][cin], w: bf16 [cout][cin],
+ *                                                              scale/bias: fp32 [cout], probs: fp32 [batch][cout]
+ * All pointers are device pointers owned by the caller; cin and cout must be multiples of 8.
+ * The only intermediate, the fp32 logits, lives in a fixed array inside the library
+ * (ADAPT_NOALLOC_MAX_LOGITS floats = 1 MiB per GPU, held from library load to process exit), so the
+ * call performs no cudaMalloc / cudaFree and calls no allocating library routine.
+ *   - LIMIT: batch * cout <= ADAPT_NOALLOC_MAX_LOGITS, otherwise ADAPT_EINVAL with a message.
+ *   - The first call on each device looks up the array's device address and sets kernel attributes
+ *     (no allocation); make that first call before starting any stream capture.
+ *   - Every call uses the same array and leaves its logits there.  Nothing needs clearing (each call
+ *     overwrites all batch * cout entries it reads), but two calls whose GPU work overlaps -- different
+ *     streams, or different threads -- race on it: serialise them on one stream. */
+#define ADAPT_NOALLOC_MAX_LOGITS (256 * 1024)
+int adapt_dense_softmax_noalloc(int device, const void* in, const void* w, const float* scale, const float* bias,
+                                float* probs, int batch, int cin, int cout, void* stream);
+
 /* ---- stage-to-stage hand-off plumbing (replaces the TCP framing of reference
  *      src/node_state.py:39-161 and the routing of src/dispatcher.py:176-220) ---- */
 
