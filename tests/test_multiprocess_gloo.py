@@ -1,0 +1,85 @@
+"""CPU: the one-process-per-stage path (what torchrun launches on the GPU box) with world_size 2 over
+gloo: rank 0 = dispatcher + stage 0, rank 1 = `Node().run()` worker.  Device memory is stood in for by
+named shared memory and the stage compute by the oracle (tests/_host_backend.py)."""
+import os
+import queue
+import sys
+import threading
+import time
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
+    import torch
+    import torch.distributed as dist
+
+    torch.set_num_threads(2)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import adapt_b200
+    from _host_backend import SharedHostBackend
+    from _util import KO, oracle_for
+    from adapt_b200.dispatcher import DEFER, join_session_as_worker
+
+    model = adapt_b200.ResNet50(weights=None)
+    try:
+        if rank > 0:
+            join_session_as_worker(model, device=rank, backend_factory=SharedHostBackend)
+            q.put((rank, "ok", None))
+            return
+        inputs = [KO.synthetic_images(1, seed=900 + i, kind="normal") for i in range(4)]
+        defer = DEFER(["10.0.0.1", "10.0.0.2"], mode="fp32", max_batch=1, backend_factory=SharedHostBackend, heartbeat_timeout=5.0)
+        in_q, out_q = queue.Queue(), queue.Queue()
+        t = threading.Thread(target=defer.run_defer, args=(model, ["conv3_block4_out"], in_q, out_q), daemon=True)
+        t.start()
+        defer.wait_ready(120)
+        for x in inputs:
+            in_q.put(x)
+        outs = [out_q.get(timeout=120) for _ in inputs]
+        defer.shutdown()
+        t.join(30)
+        o = oracle_for(model)
+        err = max(float(np.abs(y - o.predict(x)[0]).max()) for x, y in zip(inputs, outs))
+        q.put((0, "ok", err))
+    except Exception as e:  # noqa: BLE001
+        import traceback
+
+        q.put((rank, "fail", f"{e}\n{traceback.format_exc()}"))
+    finally:
+        try:
+            dist.destroy_process_group()
+        except Exception:
+            pass
+
+
+def test_two_rank_pipeline_over_gloo():
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    results = {}
+    t0 = time.time()
+    while len(results) < 2 and time.time() - t0 < 240:
+        try:
+            r, status, info = q.get(timeout=5)
+            results[r] = (status, info)
+        except Exception:
+            if not any(p.is_alive() for p in procs):
+                break
+    for p in procs:
+        p.join(20)
+        if p.is_alive():
+            p.kill()
+    assert results.get(0, ("missing", None))[0] == "ok", results
+    assert results.get(1, ("missing", None))[0] == "ok", results
+    assert results[0][1] < 1e-5
