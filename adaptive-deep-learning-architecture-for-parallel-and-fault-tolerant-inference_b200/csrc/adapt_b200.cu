@@ -166,6 +166,7 @@ struct ConvLaunch {
     CUtensorMap tmap_b;
     CUtensorMap tmap_out;  // [M, N] bf16 output, 64-column x 32-row boxes (staged epilogue)
     CUtensorMap tmap_res;  // [M, N] bf16 residual, same boxes
+    int smem = 0;          // dynamic shared memory of this launch (operand stages + epilogue staging)
     adapt::ConvGemmParams p;
     int block_n = 0;
     int a_mode = 0;
@@ -205,7 +206,7 @@ int pick_block_n(int m_tiles, int N, int num_sms) {
 template <int BN, int MODE>
 int set_smem_attr() {
     CUDA_TRY(cudaFuncSetAttribute(adapt::conv_gemm_kernel<BN, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  adapt::ConvGemmCfg<BN>::kSmemBytes));
+                                  adapt::kMaxSmemBytes));
     return ADAPT_OK;
 }
 
@@ -252,8 +253,14 @@ int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const vo
     p.N = g.Cout;
     p.num_k_blocks = (K + adapt::kBlockK - 1) / adapt::kBlockK;
     p.m_tiles = (int)((M + adapt::kBlockM - 1) / adapt::kBlockM);
+    // Roofline class of the layer: FLOP per byte of unavoidable HBM traffic (input read once, output
+    // written once, residual read once, weights once).  Below the machine balance (~210-250 FLOP/B) the
+    // layer is HBM-bound and the launch is configured for bytes in flight, not for MMA efficiency.
+    const double hbm_bytes = 2.0 * ((double)g.batch * g.H * g.W * g.Cin / (g.kh == 1 ? g.stride * g.stride : 1) +
+                                    (double)M * g.Cout * (residual ? 2 : 1) + (double)g.Cout * K);
+    const bool memory_bound = (2.0 * (double)M * g.Cout * K) / hbm_bytes < 300.0;
     int bn = block_n_req > 0 ? block_n_req : (g_force_block_n > 0 ? g_force_block_n : 0);
-    if (bn == 0) bn = pick_block_n(p.m_tiles, g.Cout, num_sms);
+    if (bn == 0) bn = memory_bound ? (g.Cout >= 128 ? 128 : 64) : pick_block_n(p.m_tiles, g.Cout, num_sms);
     if (bn != 64 && bn != 128 && bn != 256) return fail(ADAPT_EINVAL, "conv: block_n=%d unsupported", bn);
     p.n_tiles = (g.Cout + bn - 1) / bn;
     p.H = g.H; p.W = g.W; p.Cin = g.Cin; p.Ho = g.Ho; p.Wo = g.Wo;
@@ -282,6 +289,34 @@ int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const vo
         if (rc) return rc;
     } else {
         L->tmap_a = L->tmap_b;  // unused by the gather kernel
+        // "Wide pixel" view for thin-channel stride-1 VALID convolutions whose filter row is exactly one
+        // 64-element k-block (the space-to-depth stem: 4 taps x 16 channels): kw horizontally adjacent
+        // pixels are contiguous in NHWC, so the tensor is described to the TMA as (C'=kw*Cin, W'=Wo, H, N)
+        // with a W stride of ONE pixel (overlapping windows) and the layer runs on the im2col path as a
+        // kh x 1 convolution over 64 channels.  Falls back to the software gather if the driver refuses.
+        static int wide_ok = env_int("ADAPT_WIDE_PIXEL", 1);
+        if (wide_ok && a_mode_req < 0 && g.Cin * g.kw == adapt::kBlockK && g.stride == 1 && g.pad == 0) {
+            DriverApi* d;
+            rc = get_driver(&d);
+            if (rc) return rc;
+            cuuint64_t dims[4] = {(cuuint64_t)adapt::kBlockK, (cuuint64_t)g.Wo, (cuuint64_t)g.H, (cuuint64_t)g.batch};
+            cuuint64_t strides[3] = {(cuuint64_t)g.Cin * 2, (cuuint64_t)g.W * g.Cin * 2, (cuuint64_t)g.H * g.W * g.Cin * 2};
+            int lower[2] = {0, 0};
+            int upper[2] = {0, -(g.kh - 1)};
+            cuuint32_t estr[4] = {1, 1, 1, 1};
+            CUresult r = d->encodeIm2col(&L->tmap_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(in), dims, strides,
+                                         lower, upper, adapt::kBlockK, adapt::kBlockM, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (r == CUDA_SUCCESS) {
+                a_mode = adapt::A_IM2COL;
+                L->a_mode = a_mode;
+                p.kw = 1;
+                p.c_blocks = 1;
+            } else {
+                L->tmap_a = L->tmap_b;
+            }
+        }
     }
     // staged epilogue: bf16 output whose width the tile divides; the direct epilogue remains for fp32
     // logits (Dense) and as a switchable fall-back (ADAPT_EPI_DIRECT=1)
@@ -297,21 +332,51 @@ int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const vo
             if (rc) return rc;
         }
     }
+    // Split the 227 KiB of shared memory between operand stages and epilogue staging.
+    const bool has_res = residual != nullptr && p.epi_tma != 0;
+    int stages, d_out, d_res;
+    if (memory_bound) {
+        stages = p.num_k_blocks < 2 ? 2 : (p.num_k_blocks > 4 ? 4 : p.num_k_blocks);
+        d_out = 4;
+        d_res = has_res ? 6 : 0;
+    } else {
+        stages = adapt::kMaxStages;
+        d_out = 2;
+        d_res = has_res ? 2 : 0;
+    }
+    if (!p.epi_tma) d_out = 2;  // slabs unused by the direct epilogue; keep the layout minimal
+    stages = env_int("ADAPT_STAGES", stages);
+    d_out = env_int("ADAPT_DOUT", d_out) >= 4 ? 4 : 2;
+    if (has_res) d_res = env_int("ADAPT_DRES", d_res);
+    if (d_res > adapt::kMaxRes) d_res = adapt::kMaxRes;
+    if (has_res && d_res < 2) d_res = 2;
+    if (stages > adapt::kMaxStages) stages = adapt::kMaxStages;
+    if (stages < 2) stages = 2;
+    while (adapt::conv_gemm_smem_bytes(bn, stages, d_out, d_res) > adapt::kMaxSmemBytes) {
+        if (memory_bound ? (stages > 2) : (stages > 3)) --stages;
+        else if (d_res > 2) --d_res;
+        else if (d_out > 2) d_out = 2;
+        else if (stages > 2) --stages;
+        else return fail(ADAPT_EINVAL, "conv: no shared-memory configuration fits (bn=%d)", bn);
+    }
+    p.stages = stages;
+    p.d_out = d_out;
+    p.d_res = d_res;
+    L->smem = adapt::conv_gemm_smem_bytes(bn, stages, d_out, d_res);
     return ADAPT_OK;
 }
 
 template <int BN>
 void launch_conv_bn(const ConvLaunch& L, cudaStream_t s) {
-    using Cfg = adapt::ConvGemmCfg<BN>;
     switch (L.a_mode) {
         case adapt::A_TILED:
-            adapt::conv_gemm_kernel<BN, adapt::A_TILED><<<L.grid, 192, Cfg::kSmemBytes, s>>>(L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
+            adapt::conv_gemm_kernel<BN, adapt::A_TILED><<<L.grid, 192, L.smem, s>>>(L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
             break;
         case adapt::A_IM2COL:
-            adapt::conv_gemm_kernel<BN, adapt::A_IM2COL><<<L.grid, 192, Cfg::kSmemBytes, s>>>(L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
+            adapt::conv_gemm_kernel<BN, adapt::A_IM2COL><<<L.grid, 192, L.smem, s>>>(L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
             break;
         default:
-            adapt::conv_gemm_kernel<BN, adapt::A_GATHER><<<L.grid, 320, Cfg::kSmemBytes, s>>>(L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
+            adapt::conv_gemm_kernel<BN, adapt::A_GATHER><<<L.grid, 320, L.smem, s>>>(L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
             break;
     }
 }
@@ -478,7 +543,16 @@ int run_steps(adapt_stage* st, const std::vector<Step>& steps, cudaStream_t stre
         switch (s.kind) {
             case ADAPT_OP_INGEST: {
                 const long long pixels = (long long)B * o.H * o.W;
-                if (st->mode == ADAPT_MODE_BF16) {
+                if (st->mode == ADAPT_MODE_BF16 && o.Cout == 16) {
+                    // space-to-depth ingest for the stem: (H, W, 3) -> (Ho, Wo, 16) with `pad` folded in
+                    if (o.Cin != 3 || o.Ho * 2 != o.H + 2 * o.pad || o.Wo * 2 != o.W + 2 * o.pad)
+                        return fail(ADAPT_EINVAL, "ingest(s2d): expects 3 channels and Ho = (H + 2*pad) / 2");
+                    const long long outs = (long long)B * o.Ho * o.Wo;
+                    const int threads = 256;
+                    adapt::ingest_s2d_kernel<<<(unsigned)((outs + threads - 1) / threads), threads, 0, stream>>>(
+                        reinterpret_cast<const float*>(s.in), reinterpret_cast<__nv_bfloat16*>(s.out), B, o.H, o.W, o.Ho, o.Wo,
+                        o.pad);
+                } else if (st->mode == ADAPT_MODE_BF16) {
                     if (o.Cout != 8 || o.Cin > 8) return fail(ADAPT_EINVAL, "ingest: expects Cin<=8 -> 8 channels");
                     const int threads = 256;
                     const long long blocks = (pixels + threads - 1) / threads;

@@ -13,10 +13,14 @@
 // Structure: persistent CTAs (one per SM), warp-specialised:
 //   warp 0      TMA producer   (A tile: tiled 2-D box, or im2col box; B tile: tiled 2-D box)
 //   warp 1      MMA issuer     (one elected lane issues tcgen05.mma; owns the TMEM allocation)
-//   warps 2..5  epilogue       (tcgen05.ld -> scale/bias/residual/ReLU -> bf16 -> global)
+//   warps 2..5  epilogue       (tcgen05.ld -> scale/bias/residual/ReLU -> bf16 -> smem slab -> TMA store;
+//                               the residual arrives through a per-warp TMA ring that prefetches
+//                               across tile boundaries)
 //   warps 6..9  (A_GATHER only) software im2col producers for thin-channel inputs (the stem)
 // Three pipelines: smem full/empty ring (TMA <-> MMA), TMEM full/empty double buffer
-// (MMA <-> epilogue), and a static round-robin tile schedule.
+// (MMA <-> epilogue), and a static round-robin tile schedule.  The shared-memory budget is split
+// at launch time between operand stages and epilogue staging (ConvGemmParams::stages/d_out/d_res):
+// HBM-bound layers want many bytes of residual/output in flight, tensor-bound layers want stages.
 #pragma once
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
@@ -46,7 +50,11 @@ struct ConvGemmParams {
     __nv_bfloat16* out_bf16;        // [M, N] or nullptr
     float* out_f32;                 // [M, N] or nullptr (Dense logits)
     int relu;
-    int epi_tma;  // 1: staged epilogue (TMA residual load + TMA store); 0: direct per-thread global accesses
+    int epi_tma;  // 1: staged epilogue (TMA residual ring + TMA store); 2: staged + coalesced st.global; 0: direct
+    // shared-memory split (chosen by the host per layer)
+    int stages;  // operand pipeline depth, 2..kMaxStages
+    int d_out;   // output staging slabs per epilogue warp (2 or 4)
+    int d_res;   // residual staging slabs per epilogue warp (2..kMaxRes; ignored without residual)
     // A_GATHER source
     const __nv_bfloat16* in;
 };
@@ -55,30 +63,33 @@ constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;  // 64 bf16 = one 128-byte swizzle row
 constexpr int kUmmaK = 16;
 constexpr int kABytes = kBlockM * kBlockK * 2;
+constexpr int kMaxStages = 8;
+constexpr int kMaxRes = 8;
 
-// Epilogue staging (per epilogue warp): the warp's 32-row x 64-column slab travels through shared
-// memory in the 128-byte-swizzled layout so that both the residual read and the output write are
-// full-line TMA transfers instead of per-thread row-strided accesses.
-constexpr int kEpiCols = 64;                        // columns per staged chunk (64 bf16 = 128 B per row)
-constexpr int kEpiSlabBytes = 32 * kEpiCols * 2;    // 4 KiB: 32 rows x 128 B
-constexpr int kEpiWarpBytes = 4 * kEpiSlabBytes;    // residual[2] + out[2]
+// Epilogue staging unit: one warp's 32-row x 64-column bf16 slab in the 128-byte-swizzled layout.
+constexpr int kEpiCols = 64;
+constexpr int kEpiSlabBytes = 32 * kEpiCols * 2;  // 4 KiB
+constexpr int kBarrierBytes = 512;                // full[8] empty[8] tmem_full[2] tmem_empty[2] res[4][8] + tmem slot
+constexpr int kMaxSmemBytes = 227 * 1024;
 
-template <int BLOCK_N>
-struct ConvGemmCfg {
-    static constexpr int kBBytes = BLOCK_N * kBlockK * 2;
-    static constexpr int kStageBytes = kABytes + kBBytes;
-    static constexpr int kEpiBytes = 4 * kEpiWarpBytes + 4 * 2 * BLOCK_N * 4;  // staging + per-warp scale/bias
-    static constexpr int kBarrierBytes = 256;
-    static constexpr int kBudget = 227 * 1024 - 1024 - kBarrierBytes - kEpiBytes;
-    static constexpr int kStagesRaw = kBudget / kStageBytes;
-    static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
-    static constexpr int kTmemCols = 2 * BLOCK_N;  // double-buffered accumulator (power of 2 >= 32)
-    static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + kBarrierBytes + 1024;  // +1024 alignment slack
-};
+__host__ __device__ constexpr int conv_gemm_stage_bytes(int block_n) { return kABytes + block_n * kBlockK * 2; }
+__host__ __device__ constexpr int conv_gemm_epi_bytes(int block_n, int d_out, int d_res) {
+    return 4 * (d_out + d_res) * kEpiSlabBytes + 4 * 2 * block_n * 4;
+}
+__host__ __device__ constexpr int conv_gemm_smem_bytes(int block_n, int stages, int d_out, int d_res) {
+    return stages * conv_gemm_stage_bytes(block_n) + conv_gemm_epi_bytes(block_n, d_out, d_res) + kBarrierBytes + 1024;
+}
 
 template <int A_MODE>
 constexpr int conv_gemm_threads() {
     return A_MODE == A_GATHER ? 320 : 192;
+}
+
+__device__ __forceinline__ void epi_store_wait_read(int allowed_pending) {
+    if (allowed_pending >= 3)
+        ptx::tma_store_wait_read<3>();
+    else
+        ptx::tma_store_wait_read<1>();
 }
 
 template <int BLOCK_N, int A_MODE>
@@ -86,24 +97,28 @@ __global__ void __launch_bounds__(conv_gemm_threads<A_MODE>(), 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
                  const ConvGemmParams p) {
-    using Cfg = ConvGemmCfg<BLOCK_N>;
-    constexpr int kStages = Cfg::kStages;
     static_assert(BLOCK_N % 64 == 0 && BLOCK_N >= 64 && BLOCK_N <= 256, "BLOCK_N");
-    static_assert(kStages >= 2, "pipeline too shallow");
+    constexpr int kBBytes = BLOCK_N * kBlockK * 2;
+    constexpr int kStageBytes = kABytes + kBBytes;
+    constexpr int kTmemCols = 2 * BLOCK_N;  // double-buffered accumulator (power of 2 >= 32)
+    const int kStages = p.stages;
+    const int d_out = p.d_out;
+    const int d_res = p.residual != nullptr ? p.d_res : 0;
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* smem_a = smem;
     uint8_t* smem_b = smem + kStages * kABytes;
-    uint8_t* smem_epi = smem + kStages * Cfg::kStageBytes;                   // 4 x kEpiWarpBytes, 1024-aligned
-    float* smem_sb = reinterpret_cast<float*>(smem_epi + 4 * kEpiWarpBytes);  // 4 x [scale BLOCK_N | bias BLOCK_N]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes + Cfg::kEpiBytes);
+    uint8_t* smem_epi = smem + kStages * kStageBytes;  // [4 warps][d_res + d_out] slabs, 1024-aligned
+    const int epi_warp_bytes = (p.d_out + p.d_res) * kEpiSlabBytes;
+    float* smem_sb = reinterpret_cast<float*>(smem_epi + 4 * epi_warp_bytes);  // 4 x [scale BLOCK_N | bias BLOCK_N]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(smem_sb) + 4 * 2 * BLOCK_N * 4);
     uint64_t* full_bar = bars;
-    uint64_t* empty_bar = bars + kStages;
-    uint64_t* tmem_full_bar = bars + 2 * kStages;
-    uint64_t* tmem_empty_bar = bars + 2 * kStages + 2;
-    uint64_t* res_bar = bars + 2 * kStages + 4;  // [4 warps][2 buffers]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 12);
+    uint64_t* empty_bar = bars + kMaxStages;
+    uint64_t* tmem_full_bar = bars + 2 * kMaxStages;
+    uint64_t* tmem_empty_bar = bars + 2 * kMaxStages + 2;
+    uint64_t* res_bar = bars + 2 * kMaxStages + 4;  // [4 warps][kMaxRes]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kMaxStages + 4 + 4 * kMaxRes);
 
     const int warp_idx = __shfl_sync(0xffffffff, threadIdx.x / 32, 0);
     const int lane = threadIdx.x % 32;
@@ -113,7 +128,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         if (A_MODE != A_GATHER) ptx::prefetch_tmap(&tmap_a);
         ptx::prefetch_tmap(&tmap_b);
         constexpr uint32_t full_count = (A_MODE == A_GATHER) ? (1 + 128) : 1;
-        for (int i = 0; i < kStages; ++i) {
+        for (int i = 0; i < kMaxStages; ++i) {
             ptx::mbar_init(&full_bar[i], full_count);
             ptx::mbar_init(&empty_bar[i], 1);
         }
@@ -121,7 +136,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             ptx::mbar_init(&tmem_full_bar[i], 1);
             ptx::mbar_init(&tmem_empty_bar[i], 4);  // one arrive per epilogue warp
         }
-        for (int i = 0; i < 8; ++i) ptx::mbar_init(&res_bar[i], 1);
+        for (int i = 0; i < 4 * kMaxRes; ++i) ptx::mbar_init(&res_bar[i], 1);
         if (p.epi_tma) {
             ptx::prefetch_tmap(&tmap_out);
             if (p.residual != nullptr) ptx::prefetch_tmap(&tmap_res);
@@ -129,7 +144,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         ptx::fence_mbar_init();
     }
     if (warp_idx == 1) {
-        ptx::tmem_alloc(tmem_slot, Cfg::kTmemCols);
+        ptx::tmem_alloc(tmem_slot, kTmemCols);
         ptx::tmem_relinquish();
     }
     ptx::tc_fence_before();
@@ -140,7 +155,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     if (warp_idx == 0) {
         // ===================== TMA producer =====================
         if (lane == 0) {
-            int it = 0;
+            int stage = 0;
+            uint32_t phase = 0;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
                 const int m_blk = tile / p.n_tiles;
                 const int n_blk = tile % p.n_tiles;
@@ -155,35 +171,40 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     base_w = qo * p.stride - p.pad;
                     base_h = po * p.stride - p.pad;
                 }
-                for (int kb = 0; kb < p.num_k_blocks; ++kb, ++it) {
-                    const int stage = it % kStages;
-                    const uint32_t phase = (it / kStages) & 1;
+                int tap = 0, cb = 0;  // (filter tap, 64-channel block) of the current k-block
+                for (int kb = 0; kb < p.num_k_blocks; ++kb) {
                     ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
                     if (A_MODE == A_GATHER) {
-                        ptx::mbar_expect_tx(&full_bar[stage], Cfg::kBBytes);
+                        ptx::mbar_expect_tx(&full_bar[stage], kBBytes);
                     } else {
-                        ptx::mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+                        ptx::mbar_expect_tx(&full_bar[stage], kStageBytes);
                     }
                     if (A_MODE == A_TILED) {
                         ptx::tma_load_2d(smem_a + stage * kABytes, &tmap_a, &full_bar[stage], kb * kBlockK,
                                          m_blk * kBlockM);
                     } else if (A_MODE == A_IM2COL) {
-                        const int tap = kb / p.c_blocks;
-                        const int c0 = (kb - tap * p.c_blocks) * kBlockK;
                         const int r = tap / p.kw;
                         const int s = tap - r * p.kw;
-                        ptx::tma_load_im2col_4d(smem_a + stage * kABytes, &tmap_a, &full_bar[stage], c0, base_w,
+                        ptx::tma_load_im2col_4d(smem_a + stage * kABytes, &tmap_a, &full_bar[stage], cb * kBlockK, base_w,
                                                 base_h, img, static_cast<uint16_t>(s), static_cast<uint16_t>(r));
+                        if (++cb == p.c_blocks) {
+                            cb = 0;
+                            ++tap;
+                        }
                     }
-                    ptx::tma_load_2d(smem_b + stage * Cfg::kBBytes, &tmap_b, &full_bar[stage], kb * kBlockK,
-                                     n_blk * BLOCK_N);
+                    ptx::tma_load_2d(smem_b + stage * kBBytes, &tmap_b, &full_bar[stage], kb * kBlockK, n_blk * BLOCK_N);
+                    if (++stage == kStages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
                 }
             }
         }
     } else if (warp_idx == 1) {
         // ===================== MMA issuer =====================
         constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(kBlockM, BLOCK_N);
-        int it = 0;
+        int stage = 0;
+        uint32_t phase = 0;
         int tile_iter = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tile_iter) {
             const int acc_stage = tile_iter & 1;
@@ -191,14 +212,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             ptx::mbar_wait(&tmem_empty_bar[acc_stage], acc_phase ^ 1);
             ptx::tc_fence_after();
             const uint32_t tmem_d = tmem_base + acc_stage * BLOCK_N;
-            for (int kb = 0; kb < p.num_k_blocks; ++kb, ++it) {
-                const int stage = it % kStages;
-                const uint32_t phase = (it / kStages) & 1;
+            for (int kb = 0; kb < p.num_k_blocks; ++kb) {
                 ptx::mbar_wait(&full_bar[stage], phase);
                 ptx::tc_fence_after();
                 if (ptx::elect_one()) {
                     const uint64_t a_desc = ptx::make_kmajor_sw128_desc(ptx::smem_u32(smem_a + stage * kABytes));
-                    const uint64_t b_desc = ptx::make_kmajor_sw128_desc(ptx::smem_u32(smem_b + stage * Cfg::kBBytes));
+                    const uint64_t b_desc = ptx::make_kmajor_sw128_desc(ptx::smem_u32(smem_b + stage * kBBytes));
 #pragma unroll
                     for (int k = 0; k < kBlockK / kUmmaK; ++k) {
                         // advance 16 elements (32 B) along K inside the swizzle atom: +2 in 16-byte units
@@ -208,14 +227,50 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     if (kb == p.num_k_blocks - 1) ptx::umma_commit(&tmem_full_bar[acc_stage]);
                 }
                 __syncwarp();
+                if (++stage == kStages) {
+                    stage = 0;
+                    phase ^= 1;
+                }
             }
         }
     } else if (warp_idx < 6) {
         // ===================== epilogue =====================
         const int lane_group = warp_idx & 3;  // TMEM lanes this warp may touch: [32*lane_group, +32)
+        constexpr int kChunks = BLOCK_N / kEpiCols;
+        uint8_t* my_res = smem_epi + lane_group * epi_warp_bytes;  // d_res slabs
+        uint8_t* my_out = my_res + p.d_res * kEpiSlabBytes;        // d_out slabs
+        float* my_scale = smem_sb + lane_group * 2 * BLOCK_N;
+        float* my_bias = my_scale + BLOCK_N;
+        uint64_t* my_res_bar = res_bar + lane_group * kMaxRes;
+        const bool has_res = d_res > 0;
+        uint32_t res_par = 0;    // bit s: parity the next wait on residual slot s expects
+        uint32_t res_issue = 0;  // chunks (in consumption order over this CTA's tiles) whose load was issued
+        uint32_t res_slot_i = 0, res_slot_c = 0;  // ring positions of the next issue / next consume
+        uint32_t out_slot = 0;
+
+        // Issue the residual load for the `res_issue`-th chunk this warp will consume (lane 0 does the TMA).
+        auto issue_residual = [&]() {
+            const uint32_t tile_i = res_issue / kChunks;
+            const uint32_t c = res_issue - tile_i * kChunks;
+            const long long tile = blockIdx.x + static_cast<long long>(tile_i) * gridDim.x;
+            if (tile < num_tiles) {
+                const int m_blk = static_cast<int>(tile) / p.n_tiles;
+                const int n_blk = static_cast<int>(tile) - m_blk * p.n_tiles;
+                const int m_row0 = m_blk * kBlockM + lane_group * 32;
+                if (m_row0 < p.M && lane == 0) {
+                    ptx::mbar_expect_tx(&my_res_bar[res_slot_i], kEpiSlabBytes);
+                    ptx::tma_load_2d(my_res + res_slot_i * kEpiSlabBytes, &tmap_res, &my_res_bar[res_slot_i],
+                                     n_blk * BLOCK_N + c * kEpiCols, m_row0);
+                }
+            }
+            ++res_issue;
+            if (++res_slot_i == static_cast<uint32_t>(d_res)) res_slot_i = 0;
+        };
+        if (p.epi_tma && has_res) {
+            for (int i = 0; i < d_res; ++i) issue_residual();  // prime the ring: d_res chunks in flight
+        }
+
         int tile_iter = 0;
-        uint32_t res_uses = 0;  // bit b: parity the next wait on residual buffer b expects
-        uint32_t out_it = 0;    // running count of staged output chunks (selects the out buffer)
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tile_iter) {
             const int m_blk = tile / p.n_tiles;
             const int n_blk = tile % p.n_tiles;
@@ -224,27 +279,13 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lane_group * 32) << 16) + acc_stage * BLOCK_N;
             if (p.epi_tma) {
                 // ---------- staged epilogue: TMEM -> regs -> swizzled smem slab -> TMA store ----------
-                constexpr int kChunks = BLOCK_N / kEpiCols;
-                uint8_t* my_epi = smem_epi + lane_group * kEpiWarpBytes;  // res[0] res[1] out[0] out[1]
-                float* my_scale = smem_sb + lane_group * 2 * BLOCK_N;
-                float* my_bias = my_scale + BLOCK_N;
-                uint64_t* my_res_bar = res_bar + lane_group * 2;
                 const int m_row0 = m_blk * kBlockM + lane_group * 32;
                 const int n_tile0 = n_blk * BLOCK_N;
                 const bool slab_ok = m_row0 < p.M;
-                const bool has_res = p.residual != nullptr;
                 // this tile's scale / bias -> per-warp smem (read back as broadcasts)
                 for (int i = lane; i < BLOCK_N / 4; i += 32) {
                     reinterpret_cast<float4*>(my_scale)[i] = __ldg(reinterpret_cast<const float4*>(p.scale + n_tile0) + i);
                     reinterpret_cast<float4*>(my_bias)[i] = __ldg(reinterpret_cast<const float4*>(p.bias + n_tile0) + i);
-                }
-                if (has_res && slab_ok && lane == 0) {
-#pragma unroll
-                    for (int c = 0; c < (kChunks < 2 ? kChunks : 2); ++c) {
-                        ptx::mbar_expect_tx(&my_res_bar[c], kEpiSlabBytes);
-                        ptx::tma_load_2d(my_epi + c * kEpiSlabBytes, &tmap_res, &my_res_bar[c], n_tile0 + c * kEpiCols,
-                                         m_row0);
-                    }
                 }
                 __syncwarp();
                 ptx::mbar_wait(&tmem_full_bar[acc_stage], acc_phase);
@@ -260,17 +301,22 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         __syncwarp();
                         if (lane == 0) ptx::mbar_arrive(&tmem_empty_bar[acc_stage]);
                     }
-                    if (!slab_ok) continue;
-                    const int buf = c & 1;
-                    uint8_t* res_slab = my_epi + buf * kEpiSlabBytes;
-                    uint8_t* out_slab = my_epi + (2 + (out_it & 1)) * kEpiSlabBytes;
-                    ++out_it;
+                    uint8_t* res_slab = my_res + res_slot_c * kEpiSlabBytes;
                     if (has_res) {
-                        ptx::mbar_wait(&my_res_bar[buf], (res_uses >> buf) & 1);
-                        res_uses ^= (1u << buf);
+                        if (slab_ok) {
+                            ptx::mbar_wait(&my_res_bar[res_slot_c], (res_par >> res_slot_c) & 1);
+                            res_par ^= (1u << res_slot_c);
+                        }
+                        if (++res_slot_c == static_cast<uint32_t>(d_res)) res_slot_c = 0;
                     }
-                    // the TMA store issued from this out buffer two chunks ago must have read it
-                    if (p.epi_tma == 1 && lane == 0) ptx::tma_store_wait_read<1>();
+                    if (!slab_ok) {
+                        if (has_res) issue_residual();
+                        continue;
+                    }
+                    uint8_t* out_slab = my_out + out_slot * kEpiSlabBytes;
+                    if (++out_slot == static_cast<uint32_t>(d_out)) out_slot = 0;
+                    // the TMA store issued from this out slab d_out chunks ago must have read it
+                    if (p.epi_tma == 1 && lane == 0) epi_store_wait_read(d_out - 1);
                     __syncwarp();
                     const float* sc = my_scale + c * kEpiCols;
                     const float* bi = my_bias + c * kEpiCols;
@@ -303,19 +349,14 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     }
                     if (p.epi_tma == 1) ptx::fence_proxy_async_smem();  // slab writes -> visible to the TMA store
                     __syncwarp();
-                    if (lane == 0) {
-                        if (has_res && c + 2 < kChunks) {  // residual buffer fully consumed: prefetch chunk c+2
-                            ptx::mbar_expect_tx(&my_res_bar[buf], kEpiSlabBytes);
-                            ptx::tma_load_2d(res_slab, &tmap_res, &my_res_bar[buf], n_tile0 + (c + 2) * kEpiCols, m_row0);
-                        }
-                        if (p.epi_tma == 1) {
+                    if (has_res) issue_residual();  // the consumed residual slab is free: keep d_res chunks in flight
+                    if (p.epi_tma == 1) {
+                        if (lane == 0) {
                             ptx::tma_store_2d(&tmap_out, out_slab, n_tile0 + c * kEpiCols, m_row0);
                             ptx::tma_store_commit();
                         }
-                    }
-                    if (p.epi_tma == 2) {
-                        // coalesced write-out: 8 lanes cover one 128-byte row segment, 4 rows per instruction;
-                        // plain stores (also valid for a peer-mapped destination on the next stage's GPU)
+                    } else {
+                        // coalesced write-out: 8 lanes cover one 128-byte row segment, 4 rows per instruction
                         __nv_bfloat16* gout = p.out_bf16 + static_cast<size_t>(m_row0) * p.N + n_tile0 + c * kEpiCols;
                         const int ch = lane & 7;
 #pragma unroll
@@ -325,11 +366,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                             if (m_row0 + row < p.M)
                                 *reinterpret_cast<uint4*>(gout + static_cast<size_t>(row) * p.N + ch * 8) = val;
                         }
-                        // (the slab is re-used two chunks later, after at least one __syncwarp)
                     }
                 }
                 continue;
             }
+            // ---------- direct epilogue (fp32 logits; debugging switch) ----------
             ptx::mbar_wait(&tmem_full_bar[acc_stage], acc_phase);
             ptx::tc_fence_after();
             const int m = m_blk * kBlockM + lane_group * 32 + lane;
@@ -396,13 +437,14 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             }
         }
         // all of this warp's bulk stores must have landed before the CTA may exit
-        if (p.epi_tma && lane == 0) ptx::tma_store_wait<0>();
+        if (p.epi_tma == 1 && lane == 0) ptx::tma_store_wait<0>();
     } else {
         // ===================== software im2col producers (A_GATHER) =====================
         if (A_MODE == A_GATHER) {
             const int row = threadIdx.x - 192;  // 0..127 : one A-tile row per thread
             const int hw = p.Ho * p.Wo;
-            int it = 0;
+            int stage = 0;
+            uint32_t phase = 0;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
                 const int m_blk = tile / p.n_tiles;
                 const int m = m_blk * kBlockM + row;
@@ -416,9 +458,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     hi0 = po * p.stride - p.pad;
                     wi0 = qo * p.stride - p.pad;
                 }
-                for (int kb = 0; kb < p.num_k_blocks; ++kb, ++it) {
-                    const int stage = it % kStages;
-                    const uint32_t phase = (it / kStages) & 1;
+                for (int kb = 0; kb < p.num_k_blocks; ++kb) {
                     uint4 vals[8];
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
@@ -446,6 +486,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     }
                     ptx::fence_proxy_async_smem();
                     ptx::mbar_arrive(&full_bar[stage]);
+                    if (++stage == kStages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
                 }
             }
         }
@@ -456,7 +500,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     __syncthreads();
     if (warp_idx == 1) {
         ptx::tc_fence_after();
-        ptx::tmem_dealloc(tmem_base, Cfg::kTmemCols);
+        ptx::tmem_dealloc(tmem_base, kTmemCols);
     }
 }
 

@@ -29,6 +29,47 @@ __global__ void ingest_f32_to_bf16_pad8_kernel(const float* __restrict__ in, __n
 }
 
 // ---------------------------------------------------------------------------------------------
+// Stem ingest with space-to-depth: fp32 NHWC (B,H,W,3) -> bf16 (B, Hs, Ws, 16) where
+//   X[b, hh, ww, (py*2+px)*3 + c] = in_padded[b, 2*hh+py, 2*ww+px, c]      (channels 12..15 = 0)
+// and in_padded is the image zero-padded by `pad` (3) on every side (conv1_pad folded in).  The
+// 7x7 stride-2 convolution of the stem becomes a 4x4 stride-1 convolution over X with 16 stored
+// channels, whose four horizontally adjacent pixels are one contiguous 128-byte K-slab -- exactly
+// what the implicit-GEMM kernel's 64-element k-block wants.  One thread per X pixel (32 bytes out).
+__global__ void ingest_s2d_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, int B, int H, int W,
+                                  int Hs, int Ws, int pad) {
+    const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+    const long long total = static_cast<long long>(B) * Hs * Ws;
+    if (i >= total) return;
+    const int ww = static_cast<int>(i % Ws);
+    long long t = i / Ws;
+    const int hh = static_cast<int>(t % Hs);
+    const int b = static_cast<int>(t / Hs);
+    float v[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) v[j] = 0.0f;
+#pragma unroll
+    for (int py = 0; py < 2; ++py) {
+        const int hi = 2 * hh + py - pad;
+#pragma unroll
+        for (int px = 0; px < 2; ++px) {
+            const int wi = 2 * ww + px - pad;
+            if (hi >= 0 && hi < H && wi >= 0 && wi < W) {
+                const float* src = in + ((static_cast<long long>(b) * H + hi) * W + wi) * 3;
+#pragma unroll
+                for (int c = 0; c < 3; ++c) v[(py * 2 + px) * 3 + c] = __ldg(src + c);
+            }
+        }
+    }
+    uint4 o[2];
+    __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(o);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o2[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+    uint4* dst = reinterpret_cast<uint4*>(out + i * 16);
+    dst[0] = o[0];
+    dst[1] = o[1];
+}
+
+// ---------------------------------------------------------------------------------------------
 // Zero-pad `pad` on every side, then k x k max-pool with stride s, VALID (Keras pool1_pad + pool1_pool).
 // The padding value takes part in the max, exactly like the Keras graph.  8 channels per thread.
 template <typename T>

@@ -163,6 +163,34 @@ def _consumers(model: Model) -> Dict[str, List[str]]:
     return cons
 
 
+def is_s2d_stem(model: Model, l: Layer) -> bool:
+    """A 7x7 / stride-2 / VALID Conv2D on a 3-channel image behind ZeroPadding2D(3) whose padded size is
+    even: the ResNet stem.  It can run as a 4x4 stride-1 convolution over the space-to-depth image."""
+    if l.class_name != "Conv2D" or l.config["kernel_size"] != [7, 7] or l.config["strides"] != [2, 2]:
+        return False
+    if l.config["padding"] != "valid":
+        return False
+    src = model.get_layer(l.inbound_names[0])
+    if src.class_name != "ZeroPadding2D" or src.config["padding"] != [[3, 3], [3, 3]]:
+        return False
+    img = model.get_layer(src.inbound_names[0])
+    h, w, c = src.output_shape[1:]
+    return img.class_name == "InputLayer" and c == 3 and h % 2 == 0 and w % 2 == 0
+
+
+def s2d_kernel(k: np.ndarray) -> np.ndarray:
+    """(7,7,3,Cout) stride-2 kernel -> (4,4,16,Cout) stride-1 kernel over the space-to-depth image whose
+    channel (py*2+px)*3+c holds padded pixel (2*hh+py, 2*ww+px, c); taps with r or s == 7 and the four pad
+    channels are zero."""
+    out = np.zeros((4, 4, 16, k.shape[3]), dtype=np.float32)
+    for r in range(7):
+        dy, py = divmod(r, 2)
+        for s in range(7):
+            dx, px = divmod(s, 2)
+            out[dy, dx, (py * 2 + px) * 3:(py * 2 + px) * 3 + 3, :] = k[r, s]
+    return out
+
+
 def build_weight_table(model: Model) -> Tuple[List[WeightEntry], Dict[str, int]]:
     cons = _consumers(model)
     entries: List[WeightEntry] = []
@@ -184,6 +212,8 @@ def build_weight_table(model: Model) -> Tuple[List[WeightEntry], Dict[str, int]]
                 if l.name == "conv1_conv":  # the only conv whose BN a valid cut can split off
                     put(l.name, k, np.ones_like(s), b)
                     put(bn.name, None, s, t)
+                if is_s2d_stem(model, l):
+                    put(l.name + "+bn:s2d", s2d_kernel(k), s, b.astype(np.float64) * s + t)
             else:
                 put(l.name, k, np.ones(k.shape[-1]), b)
         elif l.class_name == "Dense":
@@ -284,12 +314,27 @@ def compile_part(part: PartModel, windex: Dict[str, int], mode: int = N.MODE_BF1
         return None
 
     # stage input
+    s2d_pad: Optional[str] = None  # ZeroPadding2D layer absorbed by the space-to-depth ingest
     if part.takes_model_input:
         h, w, c = shape_of(part.start)
         t_in = new_t(h * w * c, N.DT_F32, part.start)
         vt[t_in].role = N.T_INPUT
-        t0 = new_t(h * w * _stored_c(c, mode), N.DT_WORK, part.start + ":ingest")
-        ops.append(Op(N.OP_INGEST, t_in, t0, H=h, W=w, Cin=c, Ho=h, Wo=w, Cout=_stored_c(c, mode), layers=[part.start]))
+        # bf16 stem fast path: pad -> 7x7/2 conv -> BN all inside this part => space-to-depth ingest
+        if mode == N.MODE_BF16 and len(part.layer_names) >= 3:
+            l0, l1, l2 = (model.get_layer(n) for n in part.layer_names[:3])
+            if (l0.class_name == "ZeroPadding2D" and is_s2d_stem(model, l1) and l1.inbound_names == [l0.name]
+                    and l2.class_name == "BatchNormalization" and (l1.name + "+bn:s2d") in windex):
+                s2d_pad = l0.name
+        if s2d_pad is not None:
+            hp, wp = h + 6, w + 6
+            t0 = new_t((hp // 2) * (wp // 2) * 16, N.DT_WORK, part.start + ":s2d")
+            ops.append(Op(N.OP_INGEST, t_in, t0, H=h, W=w, Cin=c, Ho=hp // 2, Wo=wp // 2, Cout=16, pad=3,
+                          layers=[part.start, s2d_pad]))
+            done.add(s2d_pad)
+            val[s2d_pad] = t0
+        else:
+            t0 = new_t(h * w * _stored_c(c, mode), N.DT_WORK, part.start + ":ingest")
+            ops.append(Op(N.OP_INGEST, t_in, t0, H=h, W=w, Cin=c, Ho=h, Wo=w, Cout=_stored_c(c, mode), layers=[part.start]))
         val[part.start] = t0
     else:
         t_in = new_t(cut_tensor_elems(model, part.start, mode), N.DT_WORK, part.start)
@@ -325,7 +370,13 @@ def compile_part(part: PartModel, windex: Dict[str, int], mode: int = N.MODE_BF1
                 k = l.config["kernel_size"][0]
                 stride = l.config["strides"][0]
                 cout = l.config["filters"]
-                if src_name in pend_pad:
+                if src_name == s2d_pad:
+                    # 7x7 stride-2 stem as a 4x4 stride-1 VALID convolution over the space-to-depth image
+                    src_t = val[src_name]
+                    hp, wp, _ = shape_of(src_name)
+                    h, w, cin = hp // 2, wp // 2, 16
+                    k, stride, pad = 4, 1, 0
+                elif src_name in pend_pad:
                     src_t, pad = pend_pad[src_name]
                     covered.insert(0, src_name)
                     h, w, cin = shape_of(model.get_layer(src_name).inbound_names[0])
@@ -340,7 +391,7 @@ def compile_part(part: PartModel, windex: Dict[str, int], mode: int = N.MODE_BF1
             tail = l
             nxt = sole_consumer(tail.name)
             if nxt is not None and nxt.class_name == "BatchNormalization" and (name + "+bn") in windex:
-                wkey = name + "+bn"
+                wkey = name + ("+bn:s2d" if src_name == s2d_pad else "+bn")
                 done.add(nxt.name)
                 covered.append(nxt.name)
                 tail = nxt

@@ -214,12 +214,14 @@ class DEFER:
         h.write_table({"epoch": epoch, "order": order, "part_at": part_at, "warm_batches": self.warm_batches})
         h.g[G_EPOCH] = epoch
         active = list(order)
+        t_start = time.perf_counter()
         if not first:
             h.g[G_PHASE] = PHASE_QUIESCE
             # A worker's host thread can itself be stuck inside a CUDA call that waits for a flag a dead
             # stage will never write (e.g. a pageable host-to-device copy ordered behind such a wait), so
             # the dispatcher releases every flag wait centrally while it collects the acknowledgements.
             self._wait_acks(active, W_ACK_QUIESCE, epoch, 30.0, poison=True)
+        t_quiesced = time.perf_counter()
         h.g[G_PHASE] = PHASE_CONFIGURE
         with self._collect_lock:  # the collector is between iterations: safe to reset its cursor
             self.results.reset()
@@ -231,6 +233,8 @@ class DEFER:
         self.order = order
         self.part_at = part_at
         h.g[G_PHASE] = PHASE_RUN
+        self.stats.setdefault("reconfig_phases_ms", []).append(
+            {"quiesce": round((t_quiesced - t_start) * 1e3, 2), "configure": round((time.perf_counter() - t_quiesced) * 1e3, 2)})
 
     def _wait_acks(self, wids: List[int], word: int, epoch: int, timeout: float, poison: bool = False) -> None:
         t0 = time.monotonic()
@@ -342,7 +346,8 @@ class DEFER:
             self._next_deliver = seq + 1
             if task is not None:
                 self.latencies_ms.append((time.perf_counter() - task["t0"]) * 1e3)
-            if self._kill_time is not None:
+            if self._kill_time is not None and epoch > self._kill_epoch:
+                # first result produced by the re-sliced pipeline: kill -> detection -> reconfiguration -> replay
                 self.stats["failover_ms"].append((time.perf_counter() - self._kill_time) * 1e3)
                 self._kill_time = None
             self.stats["delivered"] += 1
@@ -376,6 +381,8 @@ class DEFER:
 
     def _failover(self, dead: List[int]) -> None:
         t0 = time.perf_counter()
+        if self._kill_time is not None:
+            self.stats.setdefault("detect_ms", []).append(round((t0 - self._kill_time) * 1e3, 2))
         with self._feed_lock:  # feeder paused
             survivors = [w for w in self.order if w not in dead]
             if not survivors:
@@ -425,6 +432,7 @@ class DEFER:
     def inject_kill(self, stage_index: int) -> int:
         """Fault injection: mark the worker currently running stage `stage_index` dead."""
         w = self.order[stage_index]
+        self._kill_epoch = self.health.epoch
         self._kill_time = time.perf_counter()
         self.health.w[w, W_KILL] = 1
         return w

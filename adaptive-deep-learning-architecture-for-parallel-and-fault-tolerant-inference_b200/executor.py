@@ -12,7 +12,7 @@ from typing import Dict, List, Optional, Sequence, Tuple
 import numpy as np
 
 from . import _native as N
-from .dag_util import PartModel, StageProgram, build_weight_table, compile_part, construct_model
+from .dag_util import PartModel, StageProgram, build_weight_table, compile_part, construct_model, layer_macs
 from .resnet50 import Model
 
 MODES = {"bf16": N.MODE_BF16, "fp32": N.MODE_FP32_CHECK, "fp32-check": N.MODE_FP32_CHECK}
@@ -85,9 +85,11 @@ class StageExecutor:
         N.check(self.lib.adapt_stage_profile(self.handle, slot, batch, stream, reps, ms, n))
         out = []
         for op, t in zip(self.program.ops, ms):
-            # algorithmic work uses the layer's true input channels (the stem stores 3 as 8)
-            cin = self.entries[op.weight].geom[2] if op.kind == N.OP_CONV else 0
-            macs = batch * op.Ho * op.Wo * op.Cout * op.kh * op.kw * cin
+            # algorithmic work = the Keras layer's own MAC count (not the padded / space-to-depth form it runs in)
+            macs = 0
+            if op.kind == N.OP_CONV:
+                macs = batch * sum(layer_macs(self.model, self.model.get_layer(n)) for n in op.layers
+                                   if n in self.model._by_name)
             out.append({"layers": op.layers, "kind": op.kind, "ms": float(t), "macs": int(macs),
                         "shape": [op.H, op.W, op.Cin, op.Cout, op.kh, op.stride]})
         return out

@@ -406,6 +406,10 @@ class StageWorker:
             self.backend.close()
         except Exception:
             pass
+        if isinstance(self.session.get("shm"), str):  # this worker attached the control segment itself
+            self.health = self.ring = self.results = self.flags_host = None
+            self.rings = []
+            self.region.close()
 
 
 class Node:
