@@ -240,7 +240,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         uint8_t* my_res = smem_epi + lane_group * epi_warp_bytes;  // d_res slabs
         uint8_t* my_out = my_res + p.d_res * kEpiSlabBytes;        // d_out slabs
         float* my_scale = smem_sb + lane_group * 2 * BLOCK_N;
-        float* my_bias = my_scale + BLOCK_N;
+        const uint32_t scale_sa = ptx::smem_u32(my_scale);  // shared-space addresses for explicit ld/st.shared
+        const uint32_t bias_sa = scale_sa + BLOCK_N * 4;
+        const uint32_t res_sa = ptx::smem_u32(my_res);
+        const uint32_t out_sa = ptx::smem_u32(my_out);
         uint64_t* my_res_bar = res_bar + lane_group * kMaxRes;
         const bool has_res = d_res > 0;
         uint32_t res_par = 0;    // bit s: parity the next wait on residual slot s expects
@@ -284,8 +287,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 const bool slab_ok = m_row0 < p.M;
                 // this tile's scale / bias -> per-warp smem (read back as broadcasts)
                 for (int i = lane; i < BLOCK_N / 4; i += 32) {
-                    reinterpret_cast<float4*>(my_scale)[i] = __ldg(reinterpret_cast<const float4*>(p.scale + n_tile0) + i);
-                    reinterpret_cast<float4*>(my_bias)[i] = __ldg(reinterpret_cast<const float4*>(p.bias + n_tile0) + i);
+                    ptx::sts128f(scale_sa + i * 16, __ldg(reinterpret_cast<const float4*>(p.scale + n_tile0) + i));
+                    ptx::sts128f(bias_sa + i * 16, __ldg(reinterpret_cast<const float4*>(p.bias + n_tile0) + i));
                 }
                 __syncwarp();
                 ptx::mbar_wait(&tmem_full_bar[acc_stage], acc_phase);
@@ -301,7 +304,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         __syncwarp();
                         if (lane == 0) ptx::mbar_arrive(&tmem_empty_bar[acc_stage]);
                     }
-                    uint8_t* res_slab = my_res + res_slot_c * kEpiSlabBytes;
+                    const uint32_t res_slab = res_sa + res_slot_c * kEpiSlabBytes;
                     if (has_res) {
                         if (slab_ok) {
                             ptx::mbar_wait(&my_res_bar[res_slot_c], (res_par >> res_slot_c) & 1);
@@ -313,22 +316,31 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         if (has_res) issue_residual();
                         continue;
                     }
-                    uint8_t* out_slab = my_out + out_slot * kEpiSlabBytes;
+                    const uint32_t out_slab = out_sa + out_slot * kEpiSlabBytes;
+                    uint8_t* out_slab_ptr = my_out + out_slot * kEpiSlabBytes;
                     if (++out_slot == static_cast<uint32_t>(d_out)) out_slot = 0;
                     // the TMA store issued from this out slab d_out chunks ago must have read it
                     if (p.epi_tma == 1 && lane == 0) epi_store_wait_read(d_out - 1);
                     __syncwarp();
-                    const float* sc = my_scale + c * kEpiCols;
-                    const float* bi = my_bias + c * kEpiCols;
+                    const uint32_t sc = scale_sa + c * kEpiCols * 4;
+                    const uint32_t bi = bias_sa + c * kEpiCols * 4;
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {  // 8 columns = one 16-byte unit of this thread's row
                         const uint32_t* vv = (j < 4) ? &v0[j * 8] : &v1[(j - 4) * 8];
+                        const float4 s0 = ptx::lds128f(sc + j * 32), s1 = ptx::lds128f(sc + j * 32 + 16);
+                        const float4 b0 = ptx::lds128f(bi + j * 32), b1 = ptx::lds128f(bi + j * 32 + 16);
                         float y[8];
-#pragma unroll
-                        for (int e = 0; e < 8; ++e) y[e] = fmaf(__uint_as_float(vv[e]), sc[j * 8 + e], bi[j * 8 + e]);
-                        const int sw = ((j ^ (lane & 7)) << 4) + lane * 128;
+                        y[0] = fmaf(__uint_as_float(vv[0]), s0.x, b0.x);
+                        y[1] = fmaf(__uint_as_float(vv[1]), s0.y, b0.y);
+                        y[2] = fmaf(__uint_as_float(vv[2]), s0.z, b0.z);
+                        y[3] = fmaf(__uint_as_float(vv[3]), s0.w, b0.w);
+                        y[4] = fmaf(__uint_as_float(vv[4]), s1.x, b1.x);
+                        y[5] = fmaf(__uint_as_float(vv[5]), s1.y, b1.y);
+                        y[6] = fmaf(__uint_as_float(vv[6]), s1.z, b1.z);
+                        y[7] = fmaf(__uint_as_float(vv[7]), s1.w, b1.w);
+                        const uint32_t sw = ((j ^ (lane & 7)) << 4) + lane * 128;
                         if (has_res) {
-                            const uint4 rv = *reinterpret_cast<const uint4*>(res_slab + sw);
+                            const uint4 rv = ptx::lds128(res_slab + sw);
                             const __nv_bfloat162* r2 = reinterpret_cast<const __nv_bfloat162*>(&rv);
 #pragma unroll
                             for (int e = 0; e < 4; ++e) {
@@ -345,14 +357,14 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&ov);
 #pragma unroll
                         for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(y[2 * e], y[2 * e + 1]);
-                        *reinterpret_cast<uint4*>(out_slab + sw) = ov;
+                        ptx::sts128(out_slab + sw, ov);
                     }
                     if (p.epi_tma == 1) ptx::fence_proxy_async_smem();  // slab writes -> visible to the TMA store
                     __syncwarp();
                     if (has_res) issue_residual();  // the consumed residual slab is free: keep d_res chunks in flight
                     if (p.epi_tma == 1) {
                         if (lane == 0) {
-                            ptx::tma_store_2d(&tmap_out, out_slab, n_tile0 + c * kEpiCols, m_row0);
+                            ptx::tma_store_2d(&tmap_out, out_slab_ptr, n_tile0 + c * kEpiCols, m_row0);
                             ptx::tma_store_commit();
                         }
                     } else {
@@ -362,7 +374,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
                             const int row = i * 4 + (lane >> 3);
-                            const uint4 val = *reinterpret_cast<const uint4*>(out_slab + row * 128 + ((ch ^ (row & 7)) << 4));
+                            const uint4 val = ptx::lds128(out_slab + row * 128 + ((ch ^ (row & 7)) << 4));
                             if (m_row0 + row < p.M)
                                 *reinterpret_cast<uint4*>(gout + static_cast<size_t>(row) * p.N + ch * 8) = val;
                         }
