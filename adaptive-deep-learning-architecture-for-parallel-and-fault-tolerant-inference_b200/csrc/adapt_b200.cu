@@ -335,10 +335,10 @@ int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const vo
     // Split the 227 KiB of shared memory between operand stages and epilogue staging.
     const bool has_res = residual != nullptr && p.epi_tma != 0;
     int stages, d_out, d_res;
-    if (memory_bound) {
-        stages = p.num_k_blocks < 2 ? 2 : (p.num_k_blocks > 4 ? 4 : p.num_k_blocks);
-        d_out = 4;
-        d_res = has_res ? 6 : 0;
+    if (memory_bound) {  // (8 epilogue warps: the per-warp depths below are half of what 4 warps would need)
+        stages = p.num_k_blocks < 3 ? 3 : (p.num_k_blocks > 4 ? 4 : p.num_k_blocks);
+        d_out = 2;
+        d_res = has_res ? 3 : 0;
     } else {
         stages = adapt::kMaxStages;
         d_out = 2;
@@ -346,10 +346,11 @@ int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const vo
     }
     if (!p.epi_tma) d_out = 2;  // slabs unused by the direct epilogue; keep the layout minimal
     stages = env_int("ADAPT_STAGES", stages);
-    d_out = env_int("ADAPT_DOUT", d_out) >= 4 ? 4 : 2;
+    d_out = env_int("ADAPT_DOUT", d_out);
+    d_out = d_out >= 4 ? 4 : (d_out >= 2 ? 2 : 1);
     if (has_res) d_res = env_int("ADAPT_DRES", d_res);
     if (d_res > adapt::kMaxRes) d_res = adapt::kMaxRes;
-    if (has_res && d_res < 2) d_res = 2;
+    if (has_res && d_res < 1) d_res = 1;
     if (stages > adapt::kMaxStages) stages = adapt::kMaxStages;
     if (stages < 2) stages = 2;
     while (adapt::conv_gemm_smem_bytes(bn, stages, d_out, d_res) > adapt::kMaxSmemBytes) {
@@ -357,6 +358,8 @@ int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const vo
         else if (d_res > 2) --d_res;
         else if (d_out > 2) d_out = 2;
         else if (stages > 2) --stages;
+        else if (d_res > 1) --d_res;
+        else if (d_out > 1) d_out = 1;
         else return fail(ADAPT_EINVAL, "conv: no shared-memory configuration fits (bn=%d)", bn);
     }
     p.stages = stages;
@@ -370,13 +373,16 @@ template <int BN>
 void launch_conv_bn(const ConvLaunch& L, cudaStream_t s) {
     switch (L.a_mode) {
         case adapt::A_TILED:
-            adapt::conv_gemm_kernel<BN, adapt::A_TILED><<<L.grid, 192, L.smem, s>>>(L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
+            adapt::conv_gemm_kernel<BN, adapt::A_TILED><<<L.grid, adapt::conv_gemm_threads<adapt::A_TILED>(), L.smem, s>>>(
+                L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
             break;
         case adapt::A_IM2COL:
-            adapt::conv_gemm_kernel<BN, adapt::A_IM2COL><<<L.grid, 192, L.smem, s>>>(L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
+            adapt::conv_gemm_kernel<BN, adapt::A_IM2COL><<<L.grid, adapt::conv_gemm_threads<adapt::A_IM2COL>(), L.smem, s>>>(
+                L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
             break;
         default:
-            adapt::conv_gemm_kernel<BN, adapt::A_GATHER><<<L.grid, 320, L.smem, s>>>(L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
+            adapt::conv_gemm_kernel<BN, adapt::A_GATHER><<<L.grid, adapt::conv_gemm_threads<adapt::A_GATHER>(), L.smem, s>>>(
+                L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
             break;
     }
 }

@@ -69,12 +69,13 @@ constexpr int kMaxRes = 8;
 // Epilogue staging unit: one warp's 32-row x 64-column bf16 slab in the 128-byte-swizzled layout.
 constexpr int kEpiCols = 64;
 constexpr int kEpiSlabBytes = 32 * kEpiCols * 2;  // 4 KiB
-constexpr int kBarrierBytes = 512;                // full[8] empty[8] tmem_full[2] tmem_empty[2] res[4][8] + tmem slot
+constexpr int kBarrierBytes = 1024;               // full[8] empty[8] tmem_full[2] tmem_empty[2] res[8][8] + tmem slot
 constexpr int kMaxSmemBytes = 227 * 1024;
+constexpr int kEpiWarps = 8;  // two groups of four: group g drains accumulator stage g (tiles g, g+2, ...)
 
 __host__ __device__ constexpr int conv_gemm_stage_bytes(int block_n) { return kABytes + block_n * kBlockK * 2; }
 __host__ __device__ constexpr int conv_gemm_epi_bytes(int block_n, int d_out, int d_res) {
-    return 4 * (d_out + d_res) * kEpiSlabBytes + 4 * 2 * block_n * 4;
+    return kEpiWarps * (d_out + d_res) * kEpiSlabBytes + kEpiWarps * 2 * block_n * 4;
 }
 __host__ __device__ constexpr int conv_gemm_smem_bytes(int block_n, int stages, int d_out, int d_res) {
     return stages * conv_gemm_stage_bytes(block_n) + conv_gemm_epi_bytes(block_n, d_out, d_res) + kBarrierBytes + 1024;
@@ -82,14 +83,16 @@ __host__ __device__ constexpr int conv_gemm_smem_bytes(int block_n, int stages, 
 
 template <int A_MODE>
 constexpr int conv_gemm_threads() {
-    return A_MODE == A_GATHER ? 320 : 192;
+    return A_MODE == A_GATHER ? 448 : 320;  // TMA + MMA + 8 epilogue warps (+ 4 gather warps)
 }
 
 __device__ __forceinline__ void epi_store_wait_read(int allowed_pending) {
     if (allowed_pending >= 3)
         ptx::tma_store_wait_read<3>();
-    else
+    else if (allowed_pending >= 1)
         ptx::tma_store_wait_read<1>();
+    else
+        ptx::tma_store_wait_read<0>();
 }
 
 template <int BLOCK_N, int A_MODE>
@@ -111,14 +114,14 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     uint8_t* smem_b = smem + kStages * kABytes;
     uint8_t* smem_epi = smem + kStages * kStageBytes;  // [4 warps][d_res + d_out] slabs, 1024-aligned
     const int epi_warp_bytes = (p.d_out + p.d_res) * kEpiSlabBytes;
-    float* smem_sb = reinterpret_cast<float*>(smem_epi + 4 * epi_warp_bytes);  // 4 x [scale BLOCK_N | bias BLOCK_N]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(smem_sb) + 4 * 2 * BLOCK_N * 4);
+    float* smem_sb = reinterpret_cast<float*>(smem_epi + kEpiWarps * epi_warp_bytes);  // per warp [scale | bias]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(smem_sb) + kEpiWarps * 2 * BLOCK_N * 4);
     uint64_t* full_bar = bars;
     uint64_t* empty_bar = bars + kMaxStages;
     uint64_t* tmem_full_bar = bars + 2 * kMaxStages;
     uint64_t* tmem_empty_bar = bars + 2 * kMaxStages + 2;
-    uint64_t* res_bar = bars + 2 * kMaxStages + 4;  // [4 warps][kMaxRes]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kMaxStages + 4 + 4 * kMaxRes);
+    uint64_t* res_bar = bars + 2 * kMaxStages + 4;  // [kEpiWarps][kMaxRes]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kMaxStages + 4 + kEpiWarps * kMaxRes);
 
     const int warp_idx = __shfl_sync(0xffffffff, threadIdx.x / 32, 0);
     const int lane = threadIdx.x % 32;
@@ -136,7 +139,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             ptx::mbar_init(&tmem_full_bar[i], 1);
             ptx::mbar_init(&tmem_empty_bar[i], 4);  // one arrive per epilogue warp
         }
-        for (int i = 0; i < 4 * kMaxRes; ++i) ptx::mbar_init(&res_bar[i], 1);
+        for (int i = 0; i < kEpiWarps * kMaxRes; ++i) ptx::mbar_init(&res_bar[i], 1);
         if (p.epi_tma) {
             ptx::prefetch_tmap(&tmap_out);
             if (p.residual != nullptr) ptx::prefetch_tmap(&tmap_res);
@@ -233,18 +236,22 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 }
             }
         }
-    } else if (warp_idx < 6) {
+    } else if (warp_idx < 2 + kEpiWarps) {
         // ===================== epilogue =====================
+        // Two groups of four warps; group g owns accumulator stage g, i.e. this CTA's tiles g, g+2, g+4, ...
+        // so that two tiles are being drained at any time (one warp per SM sub-partition per group).
+        const int epi_warp = warp_idx - 2;   // 0..7: staging buffers, barriers
+        const int group = epi_warp >> 2;     // accumulator stage this warp drains
         const int lane_group = warp_idx & 3;  // TMEM lanes this warp may touch: [32*lane_group, +32)
         constexpr int kChunks = BLOCK_N / kEpiCols;
-        uint8_t* my_res = smem_epi + lane_group * epi_warp_bytes;  // d_res slabs
-        uint8_t* my_out = my_res + p.d_res * kEpiSlabBytes;        // d_out slabs
-        float* my_scale = smem_sb + lane_group * 2 * BLOCK_N;
+        uint8_t* my_res = smem_epi + epi_warp * epi_warp_bytes;  // d_res slabs
+        uint8_t* my_out = my_res + p.d_res * kEpiSlabBytes;      // d_out slabs
+        float* my_scale = smem_sb + epi_warp * 2 * BLOCK_N;
         const uint32_t scale_sa = ptx::smem_u32(my_scale);  // shared-space addresses for explicit ld/st.shared
         const uint32_t bias_sa = scale_sa + BLOCK_N * 4;
         const uint32_t res_sa = ptx::smem_u32(my_res);
         const uint32_t out_sa = ptx::smem_u32(my_out);
-        uint64_t* my_res_bar = res_bar + lane_group * kMaxRes;
+        uint64_t* my_res_bar = res_bar + epi_warp * kMaxRes;
         const bool has_res = d_res > 0;
         uint32_t res_par = 0;    // bit s: parity the next wait on residual slot s expects
         uint32_t res_issue = 0;  // chunks (in consumption order over this CTA's tiles) whose load was issued
@@ -255,7 +262,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         auto issue_residual = [&]() {
             const uint32_t tile_i = res_issue / kChunks;
             const uint32_t c = res_issue - tile_i * kChunks;
-            const long long tile = blockIdx.x + static_cast<long long>(tile_i) * gridDim.x;
+            const long long tile = blockIdx.x + static_cast<long long>(group + 2 * tile_i) * gridDim.x;
             if (tile < num_tiles) {
                 const int m_blk = static_cast<int>(tile) / p.n_tiles;
                 const int n_blk = static_cast<int>(tile) - m_blk * p.n_tiles;
@@ -273,12 +280,13 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             for (int i = 0; i < d_res; ++i) issue_residual();  // prime the ring: d_res chunks in flight
         }
 
-        int tile_iter = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tile_iter) {
+        for (long long tile_ll = blockIdx.x + static_cast<long long>(group) * gridDim.x, tile_iter = group;
+             tile_ll < num_tiles; tile_ll += 2LL * gridDim.x, tile_iter += 2) {
+            const int tile = static_cast<int>(tile_ll);
             const int m_blk = tile / p.n_tiles;
             const int n_blk = tile % p.n_tiles;
-            const int acc_stage = tile_iter & 1;
-            const uint32_t acc_phase = (tile_iter >> 1) & 1;
+            const int acc_stage = group;  // == tile_iter & 1
+            const uint32_t acc_phase = static_cast<uint32_t>(tile_iter >> 1) & 1;
             const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lane_group * 32) << 16) + acc_stage * BLOCK_N;
             if (p.epi_tma) {
                 // ---------- staged epilogue: TMEM -> regs -> swizzled smem slab -> TMA store ----------
@@ -453,7 +461,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     } else {
         // ===================== software im2col producers (A_GATHER) =====================
         if (A_MODE == A_GATHER) {
-            const int row = threadIdx.x - 192;  // 0..127 : one A-tile row per thread
+            const int row = threadIdx.x - 320;  // 0..127 : one A-tile row per thread
             const int hw = p.Ho * p.Wo;
             int stage = 0;
             uint32_t phase = 0;

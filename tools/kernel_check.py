@@ -145,8 +145,11 @@ def run_perf() -> int:
         ("conv5_3_res", 7, 7, 512, 2048, 1, 1, 0, 1),
     ]
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+    only = os.environ.get("KC_ONLY")
     for lay in layers:
         (name, H, W, Cin, Cout, k, stride, pad) = lay[:8]
+        if only and only not in name:
+            continue
         use_res = len(lay) > 8 and lay[8]
         x = torch.randn(B, H, W, Cin, device=dev).to(torch.bfloat16)
         w = (torch.randn(Cout, k, k, Cin, device=dev) / (k * k * Cin) ** 0.5).to(torch.bfloat16)
