@@ -58,23 +58,58 @@ def block_boundaries(model) -> List[str]:
     return [l.name for l in model.layers if l.name == "pool1_pool" or (l.name.endswith("_out") and "block" in l.name)]
 
 
-def balanced_part_at(model, n_stages: int, cut_bytes_weight: float = 0.0) -> List[str]:
-    """`part_at` for `n_stages` stages minimising the heaviest stage (MACs, optionally plus a
-    per-byte cost of the hand-off it emits): dynamic programme over residual-block boundaries."""
+def estimate_layer_seconds(model, l, batch: int = 128) -> float:
+    """Roofline estimate of one Keras layer's time on a B200 inside a fused stage program (bf16):
+    max(FLOPs / sustained tensor rate, HBM bytes / sustained bandwidth) for convolutions, bytes /
+    bandwidth for the pooling layers, 0 for layers that are fused away.  Constants calibrated on
+    profiles/ (within ~15% of the measured per-layer times)."""
+    cons = [c for c in model.layers if l.name in c.inbound_names]
+    if l.class_name in ("Conv2D", "Dense"):
+        macs = layer_macs(model, l) * batch
+        src = model.get_layer(l.inbound_names[0])
+        k = l.config["kernel_size"][0] if l.class_name == "Conv2D" else 1
+        stride = l.config["strides"][0] if l.class_name == "Conv2D" else 1
+        in_elems = float(np.prod(src.output_shape[1:])) / (stride * stride if k == 1 else 1)
+        out_elems = float(np.prod(l.output_shape[1:]))
+        bn = cons[0] if len(cons) == 1 and cons[0].class_name == "BatchNormalization" else None
+        fused_add = bn is not None and any(c.class_name == "Add" for c in model.layers if bn.name in c.inbound_names)
+        byts = 2.0 * batch * (in_elems + out_elems * (2 if fused_add else 1))
+        rate = 400e12 if (k == 3 and l.output_shape[-1] <= 64) else (650e12 if k == 3 else 700e12)
+        if k == 7:  # stem: space-to-depth form, 0.14 ms measured at batch 128
+            return 1.1e-6 * batch
+        return max(2.0 * macs / rate, byts / 5.0e12) + 4e-6
+    if l.class_name == "MaxPooling2D":
+        return 2.0 * batch * float(np.prod(model.get_layer(l.inbound_names[0]).output_shape[1:])) / 3.2e12
+    if l.class_name == "InputLayer":
+        return 0.27e-6 * batch  # ingest
+    if l.class_name == "GlobalAveragePooling2D":
+        return 15e-6
+    return 0.0
+
+
+def balanced_part_at(model, n_stages: int, cost_model: str = "time", batch: int = 128, link_gbs: float = 650.0) -> List[str]:
+    """`part_at` for `n_stages` stages minimising the slowest stage: dynamic programme over
+    residual-block boundaries.  cost_model "time": a stage costs max(sum of its layers' estimated
+    times, its hand-off bytes / NVLink bandwidth) (the hand-off is overlapped with compute);
+    "macs": multiply-accumulates only."""
     if n_stages <= 1:
         return []
     cands = block_boundaries(model)
     if n_stages - 1 > len(cands):
         raise ValueError(f"cannot cut {model.name} into {n_stages} stages")
     order = {l.name: i for i, l in enumerate(model.layers)}
-    pref = np.cumsum([layer_macs(model, l) for l in model.layers]).astype(np.float64)
+    if cost_model == "macs":
+        per_layer = [float(layer_macs(model, l)) for l in model.layers]
+    else:
+        per_layer = [estimate_layer_seconds(model, l, batch) for l in model.layers]
+    pref = np.cumsum(per_layer).astype(np.float64)
     idx = [order[c] for c in cands]
     last = len(model.layers) - 1
 
     def cost(a: int, b: int, emits: bool) -> float:  # layers (a, b]
         c = pref[b] - pref[a]
-        if emits and cut_bytes_weight:
-            c += cut_bytes_weight * float(np.prod(model.layers[b].output_shape[1:]))
+        if emits and cost_model != "macs":
+            c = max(c, 2.0 * batch * float(np.prod(model.layers[b].output_shape[1:])) / (link_gbs * 1e9))
         return c
 
     INF = float("inf")
@@ -115,7 +150,7 @@ class ResidentBatch:
 class DEFER:
     def __init__(self, computeNodes, mode: str = "bf16", max_batch: int = 128, heartbeat_timeout: float = 0.05,
                  max_inflight: Optional[int] = None, backend_factory=None, warm_batches: Sequence[int] = (),
-                 silent_kill: bool = True) -> None:
+                 silent_kill: bool = True, handoff: str = "auto") -> None:
         self.computeNodes = computeNodes
         self.dispatchIP = self.get_local_ip()
         self.chunk_size = 512 * 1000
@@ -127,6 +162,12 @@ class DEFER:
         self.backend_factory = backend_factory or (lambda device: CudaBackend(device))
         self.warm_batches = list(warm_batches) or [self.max_batch]
         self.silent_kill = silent_kill  # an injected kill stops the heartbeat without announcing itself (like a crash)
+        # stage-to-stage hand-off: "direct" = the last kernel's epilogue stores into the consumer's slot over
+        # NVLink; "copy" = local write + copy-engine push overlapped with the next micro-batch; "auto" = copy
+        # for cut tensors of at least 300 KB per image (an NVLink-bound last kernel would stall the stage)
+        if handoff not in ("auto", "direct", "copy"):
+            raise ValueError("handoff must be 'auto', 'direct' or 'copy'")
+        self.handoff = handoff
         # -- runtime state
         self._shutdown_event = threading.Event()
         self.inflight_lock = threading.Lock()
@@ -211,7 +252,8 @@ class DEFER:
         then CONFIGURE (flags zeroed, programs re-sliced, neighbours re-wired)."""
         h = self.health
         epoch = h.epoch + 1
-        h.write_table({"epoch": epoch, "order": order, "part_at": part_at, "warm_batches": self.warm_batches})
+        h.write_table({"epoch": epoch, "order": order, "part_at": part_at, "warm_batches": self.warm_batches,
+                       "handoff": self.handoff})
         h.g[G_EPOCH] = epoch
         active = list(order)
         t_start = time.perf_counter()

@@ -288,6 +288,10 @@ class CudaBackend:
     def d2h(self, dst_addr: int, src: int, nbytes: int, stream: int) -> None:
         N.check(self.lib.adapt_memcpy_d2h(self.device, dst_addr, src, int(nbytes), stream))
 
+    def d2d(self, dst: int, src: int, nbytes: int, stream: int) -> None:
+        """Device-to-device copy (same GPU, peer GPU or IPC-mapped peer memory) on a copy engine."""
+        N.check(self.lib.adapt_memcpy_d2d(self.device, dst, src, int(nbytes), stream))
+
     def memset(self, dst: int, value: int, nbytes: int, stream: int) -> None:
         N.check(self.lib.adapt_memset(self.device, dst, value, int(nbytes), stream))
 

@@ -35,7 +35,8 @@ from .fabric import (G_EPOCH, G_PHASE, G_T0, G_T1, G_TIMING_REQ, KIND_DATA, KIND
 # control segment (host memory): GPUs write / wait on them with stream memory operations, and the
 # host can overwrite them with plain stores -- which is what lets a reconfiguration release a
 # blocked stream without having to get a copy scheduled behind it.
-F_IN_READY, F_OUT_FREE, F_H2D_DONE, F_IN_CONSUMED = 0, 2, 4, 6
+F_IN_READY, F_OUT_FREE, F_H2D_DONE, F_IN_CONSUMED, F_OUT_READY, F_OUT_COPIED = 0, 2, 4, 6, 8, 10
+COPY_HANDOFF_MIN_BYTES = 300 * 1024  # cut tensors at least this big per image go through a copy engine
 FLAG_WORDS = 64
 IMAGE_BYTES = 224 * 224 * 3 * 4
 OUT_ROW_BYTES = 1000 * 4
@@ -112,6 +113,7 @@ class StageWorker:
         self.launches = 0
         self._timing_events = None
         self._timing_armed = False
+        self.handoff_copy = False
         self.on_kill: Optional[Callable[[], None]] = None
         if hasattr(self.backend, "abort_check"):  # synchronous test backends must be able to give up a wait
             self.backend.abort_check = lambda: (self.health.phase != PHASE_RUN or bool(self.health.w[self.wid, W_KILL])
@@ -122,10 +124,11 @@ class StageWorker:
         """Allocate this worker's arena [in_buf 0 | in_buf 1], its result scratch, its pinned input
         staging and its streams; returns the token peers use to map the arena."""
         b = self.backend
-        self.arena = b.alloc(2 * self.slot_bytes)
+        self.arena = b.alloc(4 * self.slot_bytes)  # [in 0 | in 1 | local out 0 | local out 1]
         self.d_out = b.alloc(self.max_batch * OUT_ROW_BYTES)
         self.stream = b.new_stream()
         self.copy_stream = b.new_stream()
+        self.xfer_stream = b.new_stream()  # copy-engine hand-off of large cut tensors
         # pinned staging for pageable inputs (only the first stage of a session uses it)
         stage_bytes = self.max_batch * self.session["in_row_bytes"]
         self._stage_np = np.zeros(2 * stage_bytes + 4096, dtype=np.uint8)
@@ -163,6 +166,10 @@ class StageWorker:
     def in_buf(self, wid: int, slot: int) -> int:
         return self.peers[wid] + slot * self.slot_bytes
 
+    def out_buf(self, slot: int) -> int:
+        """Local staging slot for this stage's output when the hand-off goes through a copy engine."""
+        return self.arena + (2 + slot) * self.slot_bytes
+
     # ------------------------------------------------------------------ reconfiguration
     def _write_own_flags(self, value: int) -> None:
         self.flags_host[self.wid, :] = value
@@ -174,7 +181,8 @@ class StageWorker:
         t0 = time.monotonic()
         while True:
             self._write_own_flags(POISON)
-            if not self.backend.busy(self.copy_stream) and not self.backend.busy(self.stream):
+            if not (self.backend.busy(self.copy_stream) or self.backend.busy(self.stream)
+                    or self.backend.busy(self.xfer_stream)):
                 return
             if time.monotonic() - t0 > 20:
                 raise TimeoutError("stage streams did not drain")
@@ -204,8 +212,16 @@ class StageWorker:
             self.stage_index, self.n_stages = i, len(order)
             self.prev_wid = order[i - 1] if i > 0 else -1
             self.next_wid = order[i + 1] if i + 1 < len(order) else -1
+            mode = table.get("handoff", "auto")
+            big = getattr(self.executor, "out_bytes_per_image", 0) >= COPY_HANDOFF_MIN_BYTES
+            self.handoff_copy = self.next_wid >= 0 and (mode == "copy" or (mode == "auto" and big))
             for s in (0, 1):
-                out_ptr = self.in_buf(self.next_wid, s) if self.next_wid >= 0 else self.d_out
+                if self.next_wid < 0:
+                    out_ptr = self.d_out
+                elif self.handoff_copy:
+                    out_ptr = self.out_buf(s)
+                else:
+                    out_ptr = self.in_buf(self.next_wid, s)  # epilogue stores straight into the consumer's slot
                 self.executor.bind_io(s, self.in_buf(self.wid, s), out_ptr)
             if table.get("warm_batches"):
                 self._warm(table["warm_batches"])
@@ -259,7 +275,11 @@ class StageWorker:
             b.wait_flag(self.stream, self.flag(self.wid, F_H2D_DONE + s), k + 1)
         else:
             b.wait_flag(self.stream, self.flag(self.wid, F_IN_READY + s), k + 1)
-        if not last and k >= 2:
+        staged = (not last) and self.handoff_copy
+        if staged and k >= 2:
+            # local output slot s is re-used: its copy to the consumer (micro-batch k-2) must be done
+            b.wait_flag(self.stream, self.flag(self.wid, F_OUT_COPIED + s), k - 1)
+        elif not last and k >= 2:
             b.wait_flag(self.stream, self.flag(self.wid, F_OUT_FREE + s), k - 1)
         if last:
             r = k % ResultRing.SLOTS
@@ -285,7 +305,21 @@ class StageWorker:
             off = r * self.results.stride
             b.d2h(self.results_dev + off + ResultRing.HDR, self.d_out, batch * OUT_ROW_BYTES, self.stream)
             b.write_flag(self.stream, self.results_dev + off, k + 1)
+        elif staged:
+            # Large cut tensor: the stage wrote it to a LOCAL slot; a copy engine pushes it over NVLink on
+            # the transfer stream while this stage's SMs start the next micro-batch (hand-off overlapped
+            # with compute instead of stretching the last kernel to NVLink speed).
+            x = self.xfer_stream
+            b.write_flag(self.stream, self.flag(self.wid, F_OUT_READY + s), k + 1)
+            b.wait_flag(x, self.flag(self.wid, F_OUT_READY + s), k + 1)
+            if k >= 2:
+                b.wait_flag(x, self.flag(self.wid, F_OUT_FREE + s), k - 1)  # consumer done with its slot s
+            b.d2d(self.in_buf(self.next_wid, s), self.out_buf(s), batch * self.executor.out_bytes_per_image, x)
+            b.write_flag(x, self.flag(self.wid, F_OUT_COPIED + s), k + 1)
+            b.write_flag(x, self.flag(self.next_wid, F_IN_READY + s), k + 1)
+            self.rings[self.next_wid].push((kind, epoch, k, seq, batch, 0))
         else:
+            # Small cut tensor: the last kernel's epilogue stored it straight into the consumer's slot
             b.write_flag(self.stream, self.flag(self.next_wid, F_IN_READY + s), k + 1)
             self.rings[self.next_wid].push((kind, epoch, k, seq, batch, 0))
         if timed and k == int(self.health.g[G_T1]) - 1:

@@ -36,6 +36,10 @@ class HostExecutor:
     def num_launches(self):
         return 1
 
+    @property
+    def out_bytes_per_image(self):
+        return int(np.prod(self.out_shape)) * 4
+
     def bind_io(self, slot, in_ptr, out_ptr):
         self.io[slot] = (in_ptr, out_ptr)
 
@@ -107,6 +111,7 @@ class HostBackend:
         ctypes.memmove(dst, src, int(nbytes))
 
     d2h = h2d
+    d2d = h2d
 
     def memset(self, dst, value, nbytes, stream):
         ctypes.memset(dst, value, int(nbytes))

@@ -70,8 +70,10 @@ def test_balanced_part_at(pkg, model50):
     valid = set(valid_cut_points(model50))
     d = DEFER([0], backend_factory=HostBackend)
     for n, eff_floor in ((2, 0.90), (4, 0.85), (7, 0.80), (8, 0.80)):
-        cuts = balanced_part_at(model50, n)
+        cuts = balanced_part_at(model50, n, cost_model="macs")
         assert len(cuts) == n - 1 and set(cuts) <= valid
+        tcuts = balanced_part_at(model50, n)              # default: roofline time model, overlapped hand-off
+        assert len(tcuts) == n - 1 and set(tcuts) <= valid and tcuts == sorted(tcuts, key=[l.name for l in model50.layers].index)
         macs = [p.macs() for p in d._partition(model50, cuts)]
         assert sum(macs) / (n * max(macs)) >= eff_floor, (n, cuts, macs)
     assert balanced_part_at(model50, 1) == []
