@@ -167,6 +167,7 @@ struct ConvLaunch {
     CUtensorMap tmap_out;  // [M, N] bf16 output, 64-column x 32-row boxes (staged epilogue)
     CUtensorMap tmap_res;  // [M, N] bf16 residual, same boxes
     int smem = 0;          // dynamic shared memory of this launch (operand stages + epilogue staging)
+    int cluster = 1;       // thread-block cluster size (B operand multicast) or 1
     adapt::ConvGemmParams p;
     int block_n = 0;
     int a_mode = 0;
@@ -219,6 +220,12 @@ int init_conv_kernels_for_device() {
     SET(64, A_IM2COL) SET(128, A_IM2COL) SET(256, A_IM2COL)
     SET(64, A_GATHER) SET(128, A_GATHER) SET(256, A_GATHER)
 #undef SET
+#define SETC(BN, MODE, CL)                                                                                       \
+    CUDA_TRY(cudaFuncSetAttribute(adapt::conv_gemm_kernel<BN, adapt::MODE, CL>,                                  \
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, adapt::kMaxSmemBytes));
+    SETC(128, A_TILED, 2) SETC(256, A_TILED, 2) SETC(128, A_IM2COL, 2) SETC(256, A_IM2COL, 2)
+    SETC(128, A_TILED, 4) SETC(256, A_TILED, 4) SETC(128, A_IM2COL, 4) SETC(256, A_IM2COL, 4)
+#undef SETC
     return ADAPT_OK;
 }
 
@@ -276,10 +283,25 @@ int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const vo
     p.in = reinterpret_cast<const __nv_bfloat16*>(in);
     L->block_n = bn;
     L->a_mode = a_mode;
-    const int tiles = p.m_tiles * p.n_tiles;
-    L->grid = tiles < num_sms ? tiles : num_sms;
+    // Thread-block clusters with a multicast B operand for the layers that are bound by L2 -> SM traffic
+    // (tensor-bound class, TMA A path, bf16 output whose width the tile divides).
+    int cluster = 1;
+    if (!memory_bound && a_mode != adapt::A_GATHER && bn >= 128 && !out_f32 && g.Cout % bn == 0 &&
+        env_int("ADAPT_EPI_MODE", 1) != 0) {
+        // Measured on B200 (profiles/): multicasting B does not speed these layers up -- they are bound by
+        // shared-memory bandwidth (TMA fills + MMA operand reads), not by L2 -> SM traffic -- so it is off by
+        // default and kept as a tested switch.
+        cluster = env_int("ADAPT_CLUSTER", 1);
+        if (cluster != 2 && cluster != 4) cluster = 1;
+        while (cluster > 1 && p.m_tiles < 2 * cluster) cluster /= 2;
+    }
+    L->cluster = cluster;
+    const long long units = (long long)((p.m_tiles + cluster - 1) / cluster) * p.n_tiles;  // per cluster
+    const long long max_clusters = num_sms / cluster;
+    L->grid = (int)((units < max_clusters ? units : max_clusters) * cluster);
 
-    int rc = encode_tiled_2d_bf16(&L->tmap_b, w_bf16, (uint64_t)K, (uint64_t)g.Cout, adapt::kBlockK, (uint32_t)bn);
+    int rc = encode_tiled_2d_bf16(&L->tmap_b, w_bf16, (uint64_t)K, (uint64_t)g.Cout, adapt::kBlockK,
+                                  (uint32_t)(bn / cluster));  // each CTA of a cluster loads (and multicasts) 1/cluster of B
     if (rc) return rc;
     if (a_mode == adapt::A_TILED) {
         rc = encode_tiled_2d_bf16(&L->tmap_a, in, (uint64_t)g.Cin, (uint64_t)M, adapt::kBlockK, adapt::kBlockM);
@@ -387,7 +409,35 @@ void launch_conv_bn(const ConvLaunch& L, cudaStream_t s) {
     }
 }
 
+template <int BN, int MODE, int CL>
+cudaError_t launch_conv_cluster(const ConvLaunch& L, cudaStream_t s) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)L.grid);
+    cfg.blockDim = dim3((unsigned)adapt::conv_gemm_threads<MODE>());
+    cfg.dynamicSmemBytes = (size_t)L.smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CL;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, adapt::conv_gemm_kernel<BN, MODE, CL>, L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
+}
+
+template <int BN>
+cudaError_t launch_conv_clustered_bn(const ConvLaunch& L, cudaStream_t s) {
+    if (L.a_mode == adapt::A_TILED)
+        return L.cluster == 2 ? launch_conv_cluster<BN, adapt::A_TILED, 2>(L, s) : launch_conv_cluster<BN, adapt::A_TILED, 4>(L, s);
+    return L.cluster == 2 ? launch_conv_cluster<BN, adapt::A_IM2COL, 2>(L, s) : launch_conv_cluster<BN, adapt::A_IM2COL, 4>(L, s);
+}
+
 int run_conv_launch(const ConvLaunch& L, cudaStream_t s) {
+    if (L.cluster > 1) {
+        CUDA_TRY(L.block_n == 128 ? launch_conv_clustered_bn<128>(L, s) : launch_conv_clustered_bn<256>(L, s));
+        return ADAPT_OK;
+    }
     if (L.block_n == 64)
         launch_conv_bn<64>(L, s);
     else if (L.block_n == 128)

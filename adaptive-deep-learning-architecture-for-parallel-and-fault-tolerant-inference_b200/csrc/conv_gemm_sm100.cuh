@@ -95,12 +95,18 @@ __device__ __forceinline__ void epi_store_wait_read(int allowed_pending) {
         ptx::tma_store_wait_read<0>();
 }
 
-template <int BLOCK_N, int A_MODE>
+// CL = thread-block cluster size (1, 2 or 4).  With CL > 1 the CL CTAs of a cluster work on CL
+// consecutive m-tiles of the same n-tile and share the B (weight) operand: each CTA loads 1/CL of
+// the B tile and TMA-multicasts it into every CTA's shared memory, so the L2 -> SM traffic for B
+// drops CL-fold (the 3x3 and conv5 layers are L2-bandwidth-bound with private B tiles).
+template <int BLOCK_N, int A_MODE, int CL = 1>
 __global__ void __launch_bounds__(conv_gemm_threads<A_MODE>(), 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
                  const ConvGemmParams p) {
     static_assert(BLOCK_N % 64 == 0 && BLOCK_N >= 64 && BLOCK_N <= 256, "BLOCK_N");
+    static_assert(CL == 1 || CL == 2 || CL == 4, "cluster size");
+    static_assert(CL == 1 || A_MODE != A_GATHER, "the gather path does not multicast");
     constexpr int kBBytes = BLOCK_N * kBlockK * 2;
     constexpr int kStageBytes = kABytes + kBBytes;
     constexpr int kTmemCols = 2 * BLOCK_N;  // double-buffered accumulator (power of 2 >= 32)
@@ -125,7 +131,24 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
     const int warp_idx = __shfl_sync(0xffffffff, threadIdx.x / 32, 0);
     const int lane = threadIdx.x % 32;
-    const int num_tiles = p.m_tiles * p.n_tiles;
+    // Work distribution.  A "unit" is one tile (CL == 1) or CL consecutive m-tiles of one n-tile (CL > 1);
+    // units are dealt round-robin to CTAs / clusters, n fastest so that concurrently running CTAs share
+    // A through L2.  Every role of a CTA walks the same sequence with tile_at().
+    const int cl_rank = CL > 1 ? static_cast<int>(ptx::cluster_ctarank()) : 0;
+    const long long num_units = CL > 1 ? static_cast<long long>((p.m_tiles + CL - 1) / CL) * p.n_tiles
+                                       : static_cast<long long>(p.m_tiles) * p.n_tiles;
+    const int unit0 = blockIdx.x / CL;
+    const int unit_step = gridDim.x / CL;
+    constexpr uint16_t kClusterMask = static_cast<uint16_t>((1u << CL) - 1);
+    auto tile_at = [&](long long i, int& m_blk, int& n_blk, bool& m_valid) -> bool {
+        const long long u = unit0 + i * unit_step;
+        if (u >= num_units) return false;
+        const int g = static_cast<int>(u / p.n_tiles);
+        n_blk = static_cast<int>(u - static_cast<long long>(g) * p.n_tiles);
+        m_blk = g * CL + cl_rank;
+        m_valid = m_blk < p.m_tiles;  // (a cluster's last unit may hang over the end of M)
+        return true;
+    };
 
     if (warp_idx == 0 && lane == 0) {
         if (A_MODE != A_GATHER) ptx::prefetch_tmap(&tmap_a);
@@ -133,7 +156,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         constexpr uint32_t full_count = (A_MODE == A_GATHER) ? (1 + 128) : 1;
         for (int i = 0; i < kMaxStages; ++i) {
             ptx::mbar_init(&full_bar[i], full_count);
-            ptx::mbar_init(&empty_bar[i], 1);
+            ptx::mbar_init(&empty_bar[i], CL);  // every CTA of the cluster must have drained the stage
         }
         for (int i = 0; i < 2; ++i) {
             ptx::mbar_init(&tmem_full_bar[i], 1);
@@ -152,6 +175,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
     ptx::tc_fence_before();
     __syncthreads();
+    if (CL > 1) ptx::cluster_sync();  // peers' barriers are initialised before anyone multicasts into them
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
@@ -160,9 +184,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const int m_blk = tile / p.n_tiles;
-                const int n_blk = tile % p.n_tiles;
+            int m_blk_raw = 0, n_blk = 0;
+            bool m_valid = true;
+            for (long long ti = 0; tile_at(ti, m_blk_raw, n_blk, m_valid); ++ti) {
+                const int m_blk = m_valid ? m_blk_raw : p.m_tiles - 1;  // overhanging CTA: re-load a valid tile
                 int img = 0, base_w = 0, base_h = 0;
                 if (A_MODE == A_IM2COL) {
                     const int m0 = m_blk * kBlockM;
@@ -195,7 +220,15 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                             ++tap;
                         }
                     }
-                    ptx::tma_load_2d(smem_b + stage * kBBytes, &tmap_b, &full_bar[stage], kb * kBlockK, n_blk * BLOCK_N);
+                    if (CL == 1) {
+                        ptx::tma_load_2d(smem_b + stage * kBBytes, &tmap_b, &full_bar[stage], kb * kBlockK, n_blk * BLOCK_N);
+                    } else {
+                        // this CTA's 1/CL slice of the B tile, delivered to all CTAs of the cluster
+                        constexpr int kSliceRows = BLOCK_N / CL;
+                        ptx::tma_load_2d_multicast(smem_b + stage * kBBytes + cl_rank * kSliceRows * kBlockK * 2, &tmap_b,
+                                                   &full_bar[stage], kb * kBlockK, n_blk * BLOCK_N + cl_rank * kSliceRows,
+                                                   kClusterMask);
+                    }
                     if (++stage == kStages) {
                         stage = 0;
                         phase ^= 1;
@@ -208,10 +241,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(kBlockM, BLOCK_N);
         int stage = 0;
         uint32_t phase = 0;
-        int tile_iter = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tile_iter) {
-            const int acc_stage = tile_iter & 1;
-            const uint32_t acc_phase = (tile_iter >> 1) & 1;
+        int m_blk_u = 0, n_blk_u = 0;
+        bool m_valid_u = true;
+        for (long long tile_iter = 0; tile_at(tile_iter, m_blk_u, n_blk_u, m_valid_u); ++tile_iter) {
+            const int acc_stage = static_cast<int>(tile_iter & 1);
+            const uint32_t acc_phase = static_cast<uint32_t>(tile_iter >> 1) & 1;
             ptx::mbar_wait(&tmem_empty_bar[acc_stage], acc_phase ^ 1);
             ptx::tc_fence_after();
             const uint32_t tmem_d = tmem_base + acc_stage * BLOCK_N;
@@ -226,7 +260,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         // advance 16 elements (32 B) along K inside the swizzle atom: +2 in 16-byte units
                         ptx::umma_bf16_ss(tmem_d, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
                     }
-                    ptx::umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
+                    // free the smem slot once these MMAs retire (in every CTA whose multicast refills it)
+                    if (CL == 1)
+                        ptx::umma_commit(&empty_bar[stage]);
+                    else
+                        ptx::umma_commit_multicast(&empty_bar[stage], kClusterMask);
                     if (kb == p.num_k_blocks - 1) ptx::umma_commit(&tmem_full_bar[acc_stage]);
                 }
                 __syncwarp();
@@ -262,12 +300,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         auto issue_residual = [&]() {
             const uint32_t tile_i = res_issue / kChunks;
             const uint32_t c = res_issue - tile_i * kChunks;
-            const long long tile = blockIdx.x + static_cast<long long>(group + 2 * tile_i) * gridDim.x;
-            if (tile < num_tiles) {
-                const int m_blk = static_cast<int>(tile) / p.n_tiles;
-                const int n_blk = static_cast<int>(tile) - m_blk * p.n_tiles;
+            int m_blk = 0, n_blk = 0;
+            bool m_valid = true;
+            if (tile_at(group + 2LL * tile_i, m_blk, n_blk, m_valid)) {
                 const int m_row0 = m_blk * kBlockM + lane_group * 32;
-                if (m_row0 < p.M && lane == 0) {
+                if (m_valid && m_row0 < p.M && lane == 0) {
                     ptx::mbar_expect_tx(&my_res_bar[res_slot_i], kEpiSlabBytes);
                     ptx::tma_load_2d(my_res + res_slot_i * kEpiSlabBytes, &tmap_res, &my_res_bar[res_slot_i],
                                      n_blk * BLOCK_N + c * kEpiCols, m_row0);
@@ -280,11 +317,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             for (int i = 0; i < d_res; ++i) issue_residual();  // prime the ring: d_res chunks in flight
         }
 
-        for (long long tile_ll = blockIdx.x + static_cast<long long>(group) * gridDim.x, tile_iter = group;
-             tile_ll < num_tiles; tile_ll += 2LL * gridDim.x, tile_iter += 2) {
-            const int tile = static_cast<int>(tile_ll);
-            const int m_blk = tile / p.n_tiles;
-            const int n_blk = tile % p.n_tiles;
+        int m_blk = 0, n_blk = 0;
+        bool m_valid = true;
+        for (long long tile_iter = group; tile_at(tile_iter, m_blk, n_blk, m_valid); tile_iter += 2) {
             const int acc_stage = group;  // == tile_iter & 1
             const uint32_t acc_phase = static_cast<uint32_t>(tile_iter >> 1) & 1;
             const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lane_group * 32) << 16) + acc_stage * BLOCK_N;
@@ -292,7 +327,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 // ---------- staged epilogue: TMEM -> regs -> swizzled smem slab -> TMA store ----------
                 const int m_row0 = m_blk * kBlockM + lane_group * 32;
                 const int n_tile0 = n_blk * BLOCK_N;
-                const bool slab_ok = m_row0 < p.M;
+                const bool slab_ok = m_valid && m_row0 < p.M;
                 // this tile's scale / bias -> per-warp smem (read back as broadcasts)
                 for (int i = lane; i < BLOCK_N / 4; i += 32) {
                     ptx::sts128f(scale_sa + i * 16, __ldg(reinterpret_cast<const float4*>(p.scale + n_tile0) + i));
@@ -465,8 +500,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             const int hw = p.Ho * p.Wo;
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const int m_blk = tile / p.n_tiles;
+            int m_blk = 0, n_blk_g = 0;
+            bool m_valid_g = true;
+            for (long long ti = 0; tile_at(ti, m_blk, n_blk_g, m_valid_g); ++ti) {
                 const int m = m_blk * kBlockM + row;
                 const bool row_ok = m < p.M;
                 int img = 0, hi0 = 0, wi0 = 0;
@@ -518,6 +554,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     // ===================== teardown =====================
     ptx::tc_fence_before();
     __syncthreads();
+    if (CL > 1) ptx::cluster_sync();  // no CTA leaves while a peer may still multicast into it / arrive on its barriers
     if (warp_idx == 1) {
         ptx::tc_fence_after();
         ptx::tmem_dealloc(tmem_base, kTmemCols);
