@@ -270,7 +270,8 @@ class DEFER:
             self._k_collect = 0
         for r in self.rings:
             r.clear()
-        self._wait_acks(active, W_ACK_READY, epoch, 120.0)
+        # (graph capture + warm-up happen here; under a profiler that replays every kernel it takes minutes)
+        self._wait_acks(active, W_ACK_READY, epoch, float(os.environ.get("ADAPT_CONFIG_TIMEOUT_S", "120")))
         self._k_feed = 0
         self.order = order
         self.part_at = part_at

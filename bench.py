@@ -51,6 +51,26 @@ def measured_peaks():
     return {"bf16_sustained": 1400.0, "bf16_burst": 1590.0, "hbm": 6650.0, "source": "fallback"}
 
 
+def ncu_traffic_per_launch():
+    """Mean DRAM bytes (read + write) per conv_gemm launch from the committed ncu --set full capture."""
+    import csv
+
+    path = os.path.join(ROOT, "profiles", "r1_conv_gemm_full_metrics.csv")
+    if not os.path.exists(path):
+        return None
+    rows = list(csv.reader(open(path)))
+    col = {h: i for i, h in enumerate(rows[0])}
+    unit = {"Mbyte": 1e6, "Kbyte": 1e3, "Gbyte": 1e9, "byte": 1.0}
+    tot, n = 0.0, 0
+    for r in rows[2:]:
+        try:
+            tot += sum(float(r[col[k]]) * unit.get(rows[1][col[k]], 1.0) for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
+            n += 1
+        except (ValueError, KeyError, IndexError):
+            continue
+    return round(tot / n) if n else None
+
+
 class ClockSampler:
     """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
 
@@ -253,7 +273,9 @@ def run_ours(args) -> int:
     achieved_tf = conv_flop / (conv_ms / 1e3) / 1e12
     roofline = {
         "bound": "tensor", "kernel": "conv_gemm_kernel", "achieved": round(achieved_tf, 2), "peak": peaks["bf16_sustained"],
-        "unit": "TFLOP/s", "frac": round(achieved_tf / peaks["bf16_sustained"], 4), "traffic": None,
+        "unit": "TFLOP/s", "frac": round(achieved_tf / peaks["bf16_sustained"], 4), "traffic": ncu_traffic_per_launch(),
+        "traffic_note": "mean dram__bytes_read.sum + dram__bytes_write.sum per conv_gemm launch, from the committed "
+                        "ncu --set full capture profiles/r1_conv_gemm_full_metrics.csv (bytes)",
         "peak_source": f"{peaks['source']} bf16 sustained (kernel timed inside a long step)",
         "launches_per_step": len(conv), "avg_launch_ms": round(conv_ms / max(1, len(conv)), 5),
         "kernel_share_of_step": round(conv_ms / all_ms, 4),
@@ -338,8 +360,8 @@ def main() -> int:
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=128, help="micro-batch (images per step)")
-    ap.add_argument("--ref-batch", type=int, default=16, help="micro-batch of the CPU reference sample")
-    ap.add_argument("--cpu-steps", type=int, default=12)
+    ap.add_argument("--ref-batch", type=int, default=32, help="micro-batch of the CPU reference sample")
+    ap.add_argument("--cpu-steps", type=int, default=48, help="micro-batches of the cpu_baseline sample (10-30 s of CPU work)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-failover", action="store_true")
     ap.add_argument("--dump-ops", default=None, help="write the per-launch timing table (JSON) here")
