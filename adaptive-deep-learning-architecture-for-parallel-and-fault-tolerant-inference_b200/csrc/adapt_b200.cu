@@ -168,6 +168,7 @@ struct ConvLaunch {
     CUtensorMap tmap_res;  // [M, N] bf16 residual, same boxes
     int smem = 0;          // dynamic shared memory of this launch (operand stages + epilogue staging)
     int cluster = 1;       // thread-block cluster size (B operand multicast) or 1
+    bool pair = false;     // cluster of 2 running as one CTA pair (tcgen05 cta_group::2, 256-row tiles)
     adapt::ConvGemmParams p;
     int block_n = 0;
     int a_mode = 0;
@@ -182,7 +183,9 @@ int env_int(const char* name, int dflt) {
     return (v && *v) ? atoi(v) : dflt;
 }
 
-int pick_block_n(int m_tiles, int N, int num_sms) {
+// Tile width for the tensor-bound class.  `pair` = the layer will run on CTA pairs (256-row tiles, one
+// unit per pair of SMs): the wave count is then taken over pairs.
+int pick_block_n(int m_tiles, int N, int num_sms, bool pair) {
     const int cands[3] = {256, 128, 64};
     const float penalty[3] = {1.0f, 1.1f, 1.5f};  // narrower tiles re-read A from smem more often
     int best = 64;
@@ -193,9 +196,12 @@ int pick_block_n(int m_tiles, int N, int num_sms) {
         const int n_tiles = (N + bn - 1) / bn;
         // do not waste more than ~12% of the MMA columns on padding
         if ((float)(n_tiles * bn - N) > 0.125f * (float)N && bn > 64) continue;
-        const int tiles = m_tiles * n_tiles;
-        const int waves = (tiles + num_sms - 1) / num_sms;
-        const float cost = (float)waves * (float)bn * penalty[i];
+        const bool as_pair = pair && bn >= 128 && N % bn == 0;
+        const int units = (as_pair ? (m_tiles + 1) / 2 : m_tiles) * n_tiles;
+        const int slots = as_pair ? num_sms / 2 : num_sms;
+        const int waves = (units + slots - 1) / slots;
+        // a pair halves the B bytes each SM ingests, which is what paces these layers (profiles/r1)
+        const float cost = (float)waves * (float)bn * penalty[i] * (as_pair ? 0.85f : 1.0f);
         if (cost < best_cost) {
             best_cost = cost;
             best = bn;
@@ -203,6 +209,10 @@ int pick_block_n(int m_tiles, int N, int num_sms) {
     }
     return best;
 }
+
+// Number of clusters of `cluster` CTAs (one CTA per SM: each takes the whole shared memory) that can be
+// resident at once; cached per cluster size.  Returns 0 if the query fails (the caller keeps its bound).
+int max_resident_clusters(int cluster);
 
 template <int BN, int MODE>
 int set_smem_attr() {
@@ -226,6 +236,11 @@ int init_conv_kernels_for_device() {
     SETC(128, A_TILED, 2) SETC(256, A_TILED, 2) SETC(128, A_IM2COL, 2) SETC(256, A_IM2COL, 2)
     SETC(128, A_TILED, 4) SETC(256, A_TILED, 4) SETC(128, A_IM2COL, 4) SETC(256, A_IM2COL, 4)
 #undef SETC
+#define SETP(BN, MODE)                                                                                           \
+    CUDA_TRY(cudaFuncSetAttribute(adapt::conv_gemm_kernel<BN, adapt::MODE, 2, true>,                             \
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, adapt::kMaxSmemBytes));
+    SETP(128, A_TILED) SETP(256, A_TILED) SETP(128, A_IM2COL) SETP(256, A_IM2COL)
+#undef SETP
     return ADAPT_OK;
 }
 
@@ -267,7 +282,11 @@ int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const vo
                                     (double)M * g.Cout * (residual ? 2 : 1) + (double)g.Cout * K);
     const bool memory_bound = (2.0 * (double)M * g.Cout * K) / hbm_bytes < 300.0;
     int bn = block_n_req > 0 ? block_n_req : (g_force_block_n > 0 ? g_force_block_n : 0);
-    if (bn == 0) bn = memory_bound ? (g.Cout >= 128 ? 128 : 64) : pick_block_n(p.m_tiles, g.Cout, num_sms);
+    // 0: never, 1 (default): tensor-bound layers run on CTA pairs, 2: every eligible layer (tests)
+    const int pair_env = env_int("ADAPT_PAIR", 1);
+    const bool pair_ok = a_mode != adapt::A_GATHER && !out_f32 && env_int("ADAPT_EPI_MODE", 1) != 0 && p.m_tiles >= 2 &&
+                         (pair_env == 2 || (pair_env == 1 && !memory_bound));
+    if (bn == 0) bn = memory_bound ? (g.Cout >= 128 ? 128 : 64) : pick_block_n(p.m_tiles, g.Cout, num_sms, pair_ok);
     if (bn != 64 && bn != 128 && bn != 256) return fail(ADAPT_EINVAL, "conv: block_n=%d unsupported", bn);
     p.n_tiles = (g.Cout + bn - 1) / bn;
     p.H = g.H; p.W = g.W; p.Cin = g.Cin; p.Ho = g.Ho; p.Wo = g.Wo;
@@ -295,9 +314,22 @@ int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const vo
         if (cluster != 2 && cluster != 4) cluster = 1;
         while (cluster > 1 && p.m_tiles < 2 * cluster) cluster /= 2;
     }
+    // CTA pairs (cta_group::2): same eligibility; the pair replaces the multicast cluster
+    bool pair = false;
+    if (pair_ok && bn >= 128 && g.Cout % bn == 0) {
+        pair = true;
+        cluster = 2;
+    }
+    L->pair = pair;
     L->cluster = cluster;
     const long long units = (long long)((p.m_tiles + cluster - 1) / cluster) * p.n_tiles;  // per cluster
-    const long long max_clusters = num_sms / cluster;
+    long long max_clusters = num_sms / cluster;
+    if (cluster > 1) {
+        // a persistent grid must be co-resident: ask how many clusters of this size the device can hold
+        // (GPCs with an odd number of usable SMs leave some SMs without a partner)
+        const int resident = max_resident_clusters(cluster);
+        if (resident > 0 && resident < max_clusters) max_clusters = resident;
+    }
     L->grid = (int)((units < max_clusters ? units : max_clusters) * cluster);
 
     int rc = encode_tiled_2d_bf16(&L->tmap_b, w_bf16, (uint64_t)K, (uint64_t)g.Cout, adapt::kBlockK,
@@ -375,7 +407,7 @@ int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const vo
     if (has_res && d_res < 1) d_res = 1;
     if (stages > adapt::kMaxStages) stages = adapt::kMaxStages;
     if (stages < 2) stages = 2;
-    while (adapt::conv_gemm_smem_bytes(bn, stages, d_out, d_res) > adapt::kMaxSmemBytes) {
+    while (adapt::conv_gemm_smem_bytes(bn, stages, d_out, d_res, L->pair) > adapt::kMaxSmemBytes) {
         if (memory_bound ? (stages > 2) : (stages > 3)) --stages;
         else if (d_res > 2) --d_res;
         else if (d_out > 2) d_out = 2;
@@ -387,8 +419,36 @@ int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const vo
     p.stages = stages;
     p.d_out = d_out;
     p.d_res = d_res;
-    L->smem = adapt::conv_gemm_smem_bytes(bn, stages, d_out, d_res);
+    L->smem = adapt::conv_gemm_smem_bytes(bn, stages, d_out, d_res, L->pair);
     return ADAPT_OK;
+}
+
+int max_resident_clusters(int cluster) {
+    static int cached[5] = {-1, -1, -1, -1, -1};
+    if (cluster < 2 || cluster > 4) return 0;
+    if (cached[cluster] >= 0) return cached[cluster];
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(148 * 4);
+    cfg.blockDim = dim3((unsigned)adapt::conv_gemm_threads<adapt::A_TILED>());
+    cfg.dynamicSmemBytes = (size_t)adapt::kMaxSmemBytes;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)cluster;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int n = 0;
+    cudaError_t e = cluster == 2
+                        ? cudaOccupancyMaxActiveClusters(&n, adapt::conv_gemm_kernel<128, adapt::A_TILED, 2, true>, &cfg)
+                        : cudaOccupancyMaxActiveClusters(&n, adapt::conv_gemm_kernel<128, adapt::A_TILED, 4>, &cfg);
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        n = 0;
+    }
+    if (env_int("ADAPT_DEBUG", 0)) fprintf(stderr, "[adapt] resident clusters of %d: %d\n", cluster, n);
+    cached[cluster] = n;
+    return n;
 }
 
 template <int BN>
@@ -426,8 +486,28 @@ cudaError_t launch_conv_cluster(const ConvLaunch& L, cudaStream_t s) {
     return cudaLaunchKernelEx(&cfg, adapt::conv_gemm_kernel<BN, MODE, CL>, L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
 }
 
+template <int BN, int MODE>
+cudaError_t launch_conv_pair(const ConvLaunch& L, cudaStream_t s) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)L.grid);
+    cfg.blockDim = dim3((unsigned)adapt::conv_gemm_threads<MODE>());
+    cfg.dynamicSmemBytes = (size_t)L.smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, adapt::conv_gemm_kernel<BN, MODE, 2, true>, L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
+}
+
 template <int BN>
 cudaError_t launch_conv_clustered_bn(const ConvLaunch& L, cudaStream_t s) {
+    if (L.pair)
+        return L.a_mode == adapt::A_TILED ? launch_conv_pair<BN, adapt::A_TILED>(L, s)
+                                          : launch_conv_pair<BN, adapt::A_IM2COL>(L, s);
     if (L.a_mode == adapt::A_TILED)
         return L.cluster == 2 ? launch_conv_cluster<BN, adapt::A_TILED, 2>(L, s) : launch_conv_cluster<BN, adapt::A_TILED, 4>(L, s);
     return L.cluster == 2 ? launch_conv_cluster<BN, adapt::A_IM2COL, 2>(L, s) : launch_conv_cluster<BN, adapt::A_IM2COL, 4>(L, s);

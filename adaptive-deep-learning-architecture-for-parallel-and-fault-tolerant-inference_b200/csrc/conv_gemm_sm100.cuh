@@ -73,12 +73,15 @@ constexpr int kBarrierBytes = 1024;               // full[8] empty[8] tmem_full[
 constexpr int kMaxSmemBytes = 227 * 1024;
 constexpr int kEpiWarps = 8;  // two groups of four: group g drains accumulator stage g (tiles g, g+2, ...)
 
-__host__ __device__ constexpr int conv_gemm_stage_bytes(int block_n) { return kABytes + block_n * kBlockK * 2; }
+// (CTA-pair mode: each CTA of the pair holds only half of the B tile)
+__host__ __device__ constexpr int conv_gemm_stage_bytes(int block_n, bool pair = false) {
+    return kABytes + (pair ? block_n / 2 : block_n) * kBlockK * 2;
+}
 __host__ __device__ constexpr int conv_gemm_epi_bytes(int block_n, int d_out, int d_res) {
     return kEpiWarps * (d_out + d_res) * kEpiSlabBytes + kEpiWarps * 2 * block_n * 4;
 }
-__host__ __device__ constexpr int conv_gemm_smem_bytes(int block_n, int stages, int d_out, int d_res) {
-    return stages * conv_gemm_stage_bytes(block_n) + conv_gemm_epi_bytes(block_n, d_out, d_res) + kBarrierBytes + 1024;
+__host__ __device__ constexpr int conv_gemm_smem_bytes(int block_n, int stages, int d_out, int d_res, bool pair = false) {
+    return stages * conv_gemm_stage_bytes(block_n, pair) + conv_gemm_epi_bytes(block_n, d_out, d_res) + kBarrierBytes + 1024;
 }
 
 template <int A_MODE>
@@ -99,7 +102,13 @@ __device__ __forceinline__ void epi_store_wait_read(int allowed_pending) {
 // consecutive m-tiles of the same n-tile and share the B (weight) operand: each CTA loads 1/CL of
 // the B tile and TMA-multicasts it into every CTA's shared memory, so the L2 -> SM traffic for B
 // drops CL-fold (the 3x3 and conv5 layers are L2-bandwidth-bound with private B tiles).
-template <int BLOCK_N, int A_MODE, int CL = 1>
+//
+// PAIR (needs CL == 2) = CTA-pair tensor-core mode: the two CTAs of a cluster form one 256 x BLOCK_N tile
+// computed by `tcgen05.mma.cta_group::2`, issued by the leader (even) CTA.  Each CTA loads its own 128
+// A rows and only HALF of the B tile, and drains its own 128 accumulator rows from its own TMEM.  This
+// halves the shared-memory traffic for B (TMA fill + operand read), which is what bounds the 3x3 and
+// conv5 layers with single-CTA tiles.
+template <int BLOCK_N, int A_MODE, int CL = 1, bool PAIR = false>
 __global__ void __launch_bounds__(conv_gemm_threads<A_MODE>(), 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
@@ -107,7 +116,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     static_assert(BLOCK_N % 64 == 0 && BLOCK_N >= 64 && BLOCK_N <= 256, "BLOCK_N");
     static_assert(CL == 1 || CL == 2 || CL == 4, "cluster size");
     static_assert(CL == 1 || A_MODE != A_GATHER, "the gather path does not multicast");
-    constexpr int kBBytes = BLOCK_N * kBlockK * 2;
+    static_assert(!PAIR || CL == 2, "a CTA pair is a cluster of two");
+    constexpr int kBBytes = (PAIR ? BLOCK_N / 2 : BLOCK_N) * kBlockK * 2;
     constexpr int kStageBytes = kABytes + kBBytes;
     constexpr int kTmemCols = 2 * BLOCK_N;  // double-buffered accumulator (power of 2 >= 32)
     const int kStages = p.stages;
@@ -156,11 +166,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         constexpr uint32_t full_count = (A_MODE == A_GATHER) ? (1 + 128) : 1;
         for (int i = 0; i < kMaxStages; ++i) {
             ptx::mbar_init(&full_bar[i], full_count);
-            ptx::mbar_init(&empty_bar[i], CL);  // every CTA of the cluster must have drained the stage
+            // multicast: every CTA of the cluster must have drained the stage; pair: the leader's MMA commit
+            ptx::mbar_init(&empty_bar[i], PAIR ? 1 : CL);
         }
         for (int i = 0; i < 2; ++i) {
             ptx::mbar_init(&tmem_full_bar[i], 1);
-            ptx::mbar_init(&tmem_empty_bar[i], 4);  // one arrive per epilogue warp
+            ptx::mbar_init(&tmem_empty_bar[i], PAIR ? 8 : 4);  // one arrive per epilogue warp (of both CTAs of a pair)
         }
         for (int i = 0; i < kEpiWarps * kMaxRes; ++i) ptx::mbar_init(&res_bar[i], 1);
         if (p.epi_tma) {
@@ -170,8 +181,13 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         ptx::fence_mbar_init();
     }
     if (warp_idx == 1) {
-        ptx::tmem_alloc(tmem_slot, kTmemCols);
-        ptx::tmem_relinquish();
+        if (PAIR) {
+            ptx::tmem_alloc_pair(tmem_slot, kTmemCols);
+            ptx::tmem_relinquish_pair();
+        } else {
+            ptx::tmem_alloc(tmem_slot, kTmemCols);
+            ptx::tmem_relinquish();
+        }
     }
     ptx::tc_fence_before();
     __syncthreads();
@@ -181,69 +197,95 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
     if (warp_idx == 0) {
         // ===================== TMA producer =====================
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            int m_blk_raw = 0, n_blk = 0;
-            bool m_valid = true;
-            for (long long ti = 0; tile_at(ti, m_blk_raw, n_blk, m_valid); ++ti) {
-                const int m_blk = m_valid ? m_blk_raw : p.m_tiles - 1;  // overhanging CTA: re-load a valid tile
-                int img = 0, base_w = 0, base_h = 0;
-                if (A_MODE == A_IM2COL) {
-                    const int m0 = m_blk * kBlockM;
-                    const int hw = p.Ho * p.Wo;
-                    img = m0 / hw;
-                    const int rem = m0 - img * hw;
-                    const int po = rem / p.Wo;
-                    const int qo = rem - po * p.Wo;
-                    base_w = qo * p.stride - p.pad;
-                    base_h = po * p.stride - p.pad;
-                }
-                int tap = 0, cb = 0;  // (filter tap, 64-channel block) of the current k-block
-                for (int kb = 0; kb < p.num_k_blocks; ++kb) {
-                    ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-                    if (A_MODE == A_GATHER) {
+        // The whole warp walks the loop (uniform control flow keeps the coordinates in uniform registers and
+        // the per-k-block instruction count low -- measured: a single-lane loop with a tap division per
+        // k-block, not the memory system, was pacing the 3x3 layers); one elected lane issues.
+        int stage = 0;
+        uint32_t phase = 0;
+        int m_blk_raw = 0, n_blk = 0;
+        bool m_valid = true;
+        for (long long ti = 0; tile_at(ti, m_blk_raw, n_blk, m_valid); ++ti) {
+            const int m_blk = m_valid ? m_blk_raw : p.m_tiles - 1;  // overhanging CTA: re-load a valid tile
+            int img = 0, base_w = 0, base_h = 0;
+            if (A_MODE == A_IM2COL) {
+                const int m0 = m_blk * kBlockM;
+                const int hw = p.Ho * p.Wo;
+                img = m0 / hw;
+                const int rem = m0 - img * hw;
+                const int po = rem / p.Wo;
+                const int qo = rem - po * p.Wo;
+                base_w = qo * p.stride - p.pad;
+                base_h = po * p.stride - p.pad;
+            }
+            const int a_row = m_blk * kBlockM;
+            const int b_row = PAIR ? n_blk * BLOCK_N + cl_rank * (BLOCK_N / 2)
+                                   : (CL == 1 ? n_blk * BLOCK_N : n_blk * BLOCK_N + cl_rank * (BLOCK_N / CL));
+            int tap_r = 0, tap_s = 0, cb = 0;  // (filter tap, 64-channel block) of the current k-block
+            int k_elem = 0;
+            for (int kb = 0; kb < p.num_k_blocks; ++kb, k_elem += kBlockK) {
+                ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+                if (ptx::elect_one()) {
+                    uint8_t* a_dst = smem_a + stage * kABytes;
+                    uint8_t* b_dst = smem_b + stage * kBBytes;
+                    if (PAIR) {
+                        // both CTAs' loads report to the LEADER's barrier, which the leader arms for all of them
+                        if (cl_rank == 0) ptx::mbar_expect_tx(&full_bar[stage], 2 * kStageBytes);
+                    } else if (A_MODE == A_GATHER) {
                         ptx::mbar_expect_tx(&full_bar[stage], kBBytes);
                     } else {
                         ptx::mbar_expect_tx(&full_bar[stage], kStageBytes);
                     }
                     if (A_MODE == A_TILED) {
-                        ptx::tma_load_2d(smem_a + stage * kABytes, &tmap_a, &full_bar[stage], kb * kBlockK,
-                                         m_blk * kBlockM);
+                        if (PAIR)
+                            ptx::tma_load_2d_pair(a_dst, &tmap_a, &full_bar[stage], k_elem, a_row);
+                        else
+                            ptx::tma_load_2d(a_dst, &tmap_a, &full_bar[stage], k_elem, a_row);
                     } else if (A_MODE == A_IM2COL) {
-                        const int r = tap / p.kw;
-                        const int s = tap - r * p.kw;
-                        ptx::tma_load_im2col_4d(smem_a + stage * kABytes, &tmap_a, &full_bar[stage], cb * kBlockK, base_w,
-                                                base_h, img, static_cast<uint16_t>(s), static_cast<uint16_t>(r));
-                        if (++cb == p.c_blocks) {
-                            cb = 0;
-                            ++tap;
-                        }
+                        if (PAIR)
+                            ptx::tma_load_im2col_4d_pair(a_dst, &tmap_a, &full_bar[stage], cb * kBlockK, base_w, base_h, img,
+                                                         static_cast<uint16_t>(tap_s), static_cast<uint16_t>(tap_r));
+                        else
+                            ptx::tma_load_im2col_4d(a_dst, &tmap_a, &full_bar[stage], cb * kBlockK, base_w, base_h, img,
+                                                    static_cast<uint16_t>(tap_s), static_cast<uint16_t>(tap_r));
                     }
-                    if (CL == 1) {
-                        ptx::tma_load_2d(smem_b + stage * kBBytes, &tmap_b, &full_bar[stage], kb * kBlockK, n_blk * BLOCK_N);
+                    if (PAIR) {
+                        // this CTA's half of the B tile (the pair's MMA reads both halves in place)
+                        ptx::tma_load_2d_pair(b_dst, &tmap_b, &full_bar[stage], k_elem, b_row);
+                    } else if (CL == 1) {
+                        ptx::tma_load_2d(b_dst, &tmap_b, &full_bar[stage], k_elem, b_row);
                     } else {
                         // this CTA's 1/CL slice of the B tile, delivered to all CTAs of the cluster
                         constexpr int kSliceRows = BLOCK_N / CL;
-                        ptx::tma_load_2d_multicast(smem_b + stage * kBBytes + cl_rank * kSliceRows * kBlockK * 2, &tmap_b,
-                                                   &full_bar[stage], kb * kBlockK, n_blk * BLOCK_N + cl_rank * kSliceRows,
-                                                   kClusterMask);
+                        ptx::tma_load_2d_multicast(b_dst + cl_rank * kSliceRows * kBlockK * 2, &tmap_b, &full_bar[stage],
+                                                   k_elem, b_row, kClusterMask);
                     }
-                    if (++stage == kStages) {
-                        stage = 0;
-                        phase ^= 1;
+                }
+                __syncwarp();
+                if (A_MODE == A_IM2COL) {  // next (tap, channel block), without dividing
+                    if (++cb == p.c_blocks) {
+                        cb = 0;
+                        if (++tap_s == p.kw) {
+                            tap_s = 0;
+                            ++tap_r;
+                        }
                     }
+                }
+                if (++stage == kStages) {
+                    stage = 0;
+                    phase ^= 1;
                 }
             }
         }
     } else if (warp_idx == 1) {
         // ===================== MMA issuer =====================
-        constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(kBlockM, BLOCK_N);
+        constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(PAIR ? 2 * kBlockM : kBlockM, BLOCK_N);
         int stage = 0;
         uint32_t phase = 0;
         int m_blk_u = 0, n_blk_u = 0;
         bool m_valid_u = true;
-        for (long long tile_iter = 0; tile_at(tile_iter, m_blk_u, n_blk_u, m_valid_u); ++tile_iter) {
+        // (pair mode: only the leader CTA issues MMAs; the peer's warp 1 just owns its TMEM allocation)
+        for (long long tile_iter = 0; !(PAIR && cl_rank != 0) && tile_at(tile_iter, m_blk_u, n_blk_u, m_valid_u);
+             ++tile_iter) {
             const int acc_stage = static_cast<int>(tile_iter & 1);
             const uint32_t acc_phase = static_cast<uint32_t>(tile_iter >> 1) & 1;
             ptx::mbar_wait(&tmem_empty_bar[acc_stage], acc_phase ^ 1);
@@ -258,14 +300,24 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 #pragma unroll
                     for (int k = 0; k < kBlockK / kUmmaK; ++k) {
                         // advance 16 elements (32 B) along K inside the swizzle atom: +2 in 16-byte units
-                        ptx::umma_bf16_ss(tmem_d, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                        if (PAIR)
+                            ptx::umma_bf16_ss_pair(tmem_d, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                        else
+                            ptx::umma_bf16_ss(tmem_d, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
                     }
-                    // free the smem slot once these MMAs retire (in every CTA whose multicast refills it)
-                    if (CL == 1)
+                    // free the smem slot once these MMAs retire (in every CTA whose loads refill it)
+                    if (PAIR)
+                        ptx::umma_commit_pair(&empty_bar[stage], kClusterMask);
+                    else if (CL == 1)
                         ptx::umma_commit(&empty_bar[stage]);
                     else
                         ptx::umma_commit_multicast(&empty_bar[stage], kClusterMask);
-                    if (kb == p.num_k_blocks - 1) ptx::umma_commit(&tmem_full_bar[acc_stage]);
+                    if (kb == p.num_k_blocks - 1) {
+                        if (PAIR)
+                            ptx::umma_commit_pair(&tmem_full_bar[acc_stage], kClusterMask);  // both CTAs' epilogues
+                        else
+                            ptx::umma_commit(&tmem_full_bar[acc_stage]);
+                    }
                 }
                 __syncwarp();
                 if (++stage == kStages) {
@@ -345,7 +397,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     if (c == kChunks - 1) {
                         ptx::tc_fence_before();
                         __syncwarp();
-                        if (lane == 0) ptx::mbar_arrive(&tmem_empty_bar[acc_stage]);
+                        if (lane == 0) {
+                            if (PAIR)
+                                ptx::mbar_arrive_remote(&tmem_empty_bar[acc_stage], 0);  // the leader's MMA warp waits for both CTAs
+                            else
+                                ptx::mbar_arrive(&tmem_empty_bar[acc_stage]);
+                        }
                     }
                     const uint32_t res_slab = res_sa + res_slot_c * kEpiSlabBytes;
                     if (has_res) {
@@ -557,7 +614,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     if (CL > 1) ptx::cluster_sync();  // no CTA leaves while a peer may still multicast into it / arrive on its barriers
     if (warp_idx == 1) {
         ptx::tc_fence_after();
-        ptx::tmem_dealloc(tmem_base, kTmemCols);
+        if (PAIR)
+            ptx::tmem_dealloc_pair(tmem_base, kTmemCols);
+        else
+            ptx::tmem_dealloc(tmem_base, kTmemCols);
     }
 }
 

@@ -56,14 +56,31 @@ CASES = {
         ("g_stem", 2, 224, 224, 8, 64, 7, 2, 3, 0, 1, 0),
         ("g_cin24", 2, 20, 20, 24, 64, 3, 1, 1, 1, 1, 0),
     ],
+    # CTA-pair mode (run with ADAPT_PAIR=2): odd tile counts, partial last tiles, residuals
+    "pair_tiled": [
+        ("p_t_even", 8, 28, 28, 256, 256, 1, 1, 0, 0, 1, 0),
+        ("p_t_res", 4, 28, 28, 128, 512, 1, 1, 0, 1, 1, 0),
+        ("p_t_odd_tiles", 5, 14, 14, 256, 1024, 1, 1, 0, 1, 1, 0),
+        ("p_t_k2048", 8, 7, 7, 2048, 512, 1, 1, 0, 0, 1, 0),
+        ("p_t_bigM", 32, 56, 56, 64, 256, 1, 1, 0, 1, 1, 0),
+    ],
+    "pair_im2col": [
+        ("p_c3_28", 16, 28, 28, 128, 128, 3, 1, 1, 0, 1, 0),
+        ("p_c3_14_odd", 8, 14, 14, 256, 256, 3, 1, 1, 0, 1, 0),
+        ("p_c3_7_straddle", 16, 7, 7, 512, 512, 3, 1, 1, 0, 1, 0),
+        ("p_c3_7_b5", 5, 7, 7, 512, 512, 3, 1, 1, 1, 1, 0),
+        ("p_s2_14", 16, 14, 14, 1024, 2048, 1, 2, 0, 0, 0, 0),
+    ],
 }
-MODE = {"tiled": 0, "im2col": 1, "gather": 2}
+MODE = {"tiled": 0, "im2col": 1, "gather": 2, "pair_tiled": 0, "pair_im2col": 1}
 
 
 def run_group(group: str) -> int:
     import torch
     import torch.nn.functional as F
 
+    if group.startswith("pair"):
+        os.environ["ADAPT_PAIR"] = "2"
     nat = load_native()
     lib = nat.lib()
     dev = torch.device("cuda:0")
@@ -159,11 +176,15 @@ def run_perf() -> int:
         Wo = (W + 2 * pad - k) // stride + 1
         out = torch.empty(B, Ho, Wo, Cout, device=dev, dtype=torch.bfloat16)
         res = torch.randn(B, Ho, Wo, Cout, device=dev).to(torch.bfloat16) if use_res else None
+        only_bn = int(os.environ.get("KC_BN", "0"))
+        iters = int(os.environ.get("KC_ITERS", "6"))
         for bn in (64, 128, 256):
             if bn > 64 and Cout < bn:
                 continue
+            if only_bn and bn != only_bn:
+                continue
             times = []
-            for it in range(6):
+            for it in range(iters):
                 flush.zero_()
                 e0 = torch.cuda.Event(enable_timing=True)
                 e1 = torch.cuda.Event(enable_timing=True)
@@ -177,7 +198,7 @@ def run_perf() -> int:
                 if rc != 0:
                     print(json.dumps({"layer": name, "bn": bn, "error": lib.adapt_last_error().decode()}))
                     break
-                if it >= 2:
+                if it >= min(2, iters - 1):
                     times.append(e0.elapsed_time(e1))
             if not times:
                 continue
@@ -200,7 +221,8 @@ def main() -> int:
     if args.group:
         return run_group(args.group)
     rc_all = 0
-    for g in ("tiled", "im2col", "gather", "perf"):
+    groups = os.environ.get("KC_GROUPS", "tiled,im2col,gather,pair_tiled,pair_im2col,perf").split(",")
+    for g in groups:
         t0 = time.time()
         p = subprocess.run([sys.executable, os.path.abspath(__file__), "--group", g], timeout=600)
         print(f"== group {g}: exit {p.returncode} in {time.time() - t0:.1f}s", flush=True)
