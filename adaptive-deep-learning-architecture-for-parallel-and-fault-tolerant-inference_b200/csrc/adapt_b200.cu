@@ -386,33 +386,40 @@ int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const vo
             if (rc) return rc;
         }
     }
-    // Split the 227 KiB of shared memory between operand stages and epilogue staging.
+    // Split the 227 KiB of shared memory between operand stages and epilogue staging.  Each of the 8 epilogue
+    // warps owns a ring of 4 KiB slabs: `d_out` deep without a residual; with one, `d_res` deep and used in
+    // place (residual in, sum out), so d_out is 0.  d_res >= 3 keeps at least one residual chunk in flight
+    // while another is being worked on.
     const bool has_res = residual != nullptr && p.epi_tma != 0;
     int stages, d_out, d_res;
-    if (memory_bound) {  // (8 epilogue warps: the per-warp depths below are half of what 4 warps would need)
+    if (memory_bound) {
         stages = p.num_k_blocks < 3 ? 3 : (p.num_k_blocks > 4 ? 4 : p.num_k_blocks);
-        d_out = 2;
-        d_res = has_res ? 3 : 0;
+        d_out = has_res ? 0 : 2;
+        d_res = has_res ? 4 : 0;
     } else {
         stages = adapt::kMaxStages;
-        d_out = 2;
-        d_res = has_res ? 2 : 0;
+        d_out = has_res ? 0 : 2;
+        d_res = has_res ? 3 : 0;
     }
     if (!p.epi_tma) d_out = 2;  // slabs unused by the direct epilogue; keep the layout minimal
     stages = env_int("ADAPT_STAGES", stages);
-    d_out = env_int("ADAPT_DOUT", d_out);
-    d_out = d_out >= 4 ? 4 : (d_out >= 2 ? 2 : 1);
-    if (has_res) d_res = env_int("ADAPT_DRES", d_res);
-    if (d_res > adapt::kMaxRes) d_res = adapt::kMaxRes;
-    if (has_res && d_res < 1) d_res = 1;
+    if (!has_res) {
+        d_out = env_int("ADAPT_DOUT", d_out);
+        d_out = d_out >= 4 ? 4 : (d_out >= 2 ? 2 : 1);
+    } else {
+        d_res = env_int("ADAPT_DRES", d_res);
+        if (d_res > adapt::kMaxRes) d_res = adapt::kMaxRes;
+        if (d_res < 2) d_res = 2;
+    }
     if (stages > adapt::kMaxStages) stages = adapt::kMaxStages;
     if (stages < 2) stages = 2;
     while (adapt::conv_gemm_smem_bytes(bn, stages, d_out, d_res, L->pair) > adapt::kMaxSmemBytes) {
-        if (memory_bound ? (stages > 2) : (stages > 3)) --stages;
-        else if (d_res > 2) --d_res;
+        if (stages > 4) --stages;
+        else if (d_res > 3) --d_res;
+        else if (stages > 3) --stages;
         else if (d_out > 2) d_out = 2;
         else if (stages > 2) --stages;
-        else if (d_res > 1) --d_res;
+        else if (d_res > 2) --d_res;
         else if (d_out > 1) d_out = 1;
         else return fail(ADAPT_EINVAL, "conv: no shared-memory configuration fits (bn=%d)", bn);
     }
@@ -1063,7 +1070,34 @@ int adapt_conv2d_bf16(int device, const void* in, const void* w, const float* sc
     ConvLaunch L;
     rc = build_conv_launch(&L, g, in, w, scale, bias, residual, out, out_is_f32 != 0, relu, a_mode, block_n, num_sms);
     if (rc) return rc;
-    return run_conv_launch(L, reinterpret_cast<cudaStream_t>(stream));
+    // Developer timeline (tools/kernel_check.py --group trace): with ADAPT_TRACE_FILE set, every call of this
+    // entry point runs synchronously and appends the per-CTA, per-tile role timestamps to that file.
+    static const char* trace_file = ADAPT_ENABLE_TRACE ? getenv("ADAPT_TRACE_FILE") : nullptr;
+    if (trace_file == nullptr || trace_file[0] == 0) return run_conv_launch(L, reinterpret_cast<cudaStream_t>(stream));
+    const size_t n_stamps = (size_t)L.grid * adapt::kTraceTiles * adapt::kTraceEvents;
+    long long* dtrace = nullptr;
+    CUDA_TRY(cudaMalloc(&dtrace, n_stamps * sizeof(long long)));
+    CUDA_TRY(cudaMemset(dtrace, 0, n_stamps * sizeof(long long)));
+    L.p.trace = dtrace;
+    rc = run_conv_launch(L, reinterpret_cast<cudaStream_t>(stream));
+    if (rc == ADAPT_OK) {
+        std::vector<long long> host(n_stamps);
+        cudaError_t e = cudaStreamSynchronize(reinterpret_cast<cudaStream_t>(stream));
+        if (e == cudaSuccess) e = cudaMemcpy(host.data(), dtrace, n_stamps * sizeof(long long), cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) {
+            rc = fail(ADAPT_ECUDA, "trace read-back: %s", cudaGetErrorString(e));
+        } else if (FILE* f = fopen(trace_file, "a")) {
+            fprintf(f, "{\"grid\": %d, \"block_n\": %d, \"a_mode\": %d, \"pair\": %d, \"m_tiles\": %d, \"n_tiles\": %d, "
+                       "\"k_blocks\": %d, \"stages\": %d, \"tiles\": %d, \"events\": %d, \"stamps\": [",
+                    L.grid, L.block_n, L.a_mode, L.pair ? 1 : 0, L.p.m_tiles, L.p.n_tiles, L.p.num_k_blocks, L.p.stages,
+                    adapt::kTraceTiles, adapt::kTraceEvents);
+            for (size_t i = 0; i < n_stamps; ++i) fprintf(f, i ? ",%lld" : "%lld", host[i]);
+            fprintf(f, "]}\n");
+            fclose(f);
+        }
+    }
+    cudaFree(dtrace);
+    return rc;
 }
 
 // ---------------------------------------------------------------- classifier head without allocations

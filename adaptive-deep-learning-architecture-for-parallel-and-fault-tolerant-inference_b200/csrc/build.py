@@ -12,6 +12,7 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB = os.path.join(HERE, "libadapt_b200.so")
+TRACE_LIB = os.path.join(HERE, "libadapt_b200_trace.so")  # developer build with the role timeline compiled in
 SOURCES = ["adapt_b200.cu"]
 HEADERS = ["conv_gemm_sm100.cuh", "ptx_sm100.cuh", "simt_kernels.cuh", os.path.join("..", "..", "include", "adapt_b200.h")]
 
@@ -34,15 +35,17 @@ def needs_build() -> bool:
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and not needs_build():
+    trace = os.environ.get("ADAPT_BUILD_TRACE", "0") == "1"
+    if not trace and not force and not needs_build():
         return LIB
+    out = TRACE_LIB if trace else LIB
     cmd = [
         _nvcc(),
         "-gencode", "arch=compute_100a,code=sm_100a",
         "-lineinfo", "-O3", "-std=c++17",
         "--shared", "-Xcompiler", "-fPIC",
-        "-o", LIB,
-    ] + SOURCES
+        "-o", out,
+    ] + (["-DADAPT_ENABLE_TRACE=1"] if trace else []) + SOURCES
     if verbose:
         cmd.insert(1, "-Xptxas")
         cmd.insert(2, "-v")
@@ -51,7 +54,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         raise RuntimeError("nvcc failed:\n" + proc.stdout + proc.stderr)
     if verbose:
         sys.stderr.write(proc.stderr)
-    return LIB
+    return out
 
 
 if __name__ == "__main__":

@@ -26,6 +26,8 @@
 #include <cuda_runtime.h>
 #include <cuda.h>
 #include <cstdint>
+#include <type_traits>
+
 #include "ptx_sm100.cuh"
 
 namespace adapt {
@@ -57,6 +59,26 @@ struct ConvGemmParams {
     int d_res;   // residual staging slabs per epilogue warp (2..kMaxRes; ignored without residual)
     // A_GATHER source
     const __nv_bfloat16* in;
+    // developer timeline (nullptr in production): [grid][kTraceTiles][kTraceEvents] SM clock stamps
+    long long* trace;
+};
+
+#ifndef ADAPT_ENABLE_TRACE
+#define ADAPT_ENABLE_TRACE 0
+#endif
+
+// Timeline slots written when ConvGemmParams::trace is set (tools/kernel_check.py --group trace).
+constexpr int kTraceTiles = 24;
+constexpr int kTraceEvents = 8;
+enum : int {
+    TR_CTA_START = 0,   // (tile 0 only) kernel entry
+    TR_PROD_FIRST = 1,  // producer: first load of the tile issued
+    TR_PROD_LAST = 2,   // producer: last load of the tile issued
+    TR_MMA_START = 3,   // MMA warp: accumulator stage acquired
+    TR_MMA_FIRST = 4,   // MMA warp: first operand stage arrived
+    TR_MMA_DONE = 5,    // MMA warp: last commit issued
+    TR_EPI_START = 6,   // epilogue warp 0 of the tile's group: accumulator ready
+    TR_EPI_DONE = 7,    // epilogue warp 0 of the tile's group: last store issued
 };
 
 constexpr int kBlockM = 128;
@@ -160,6 +182,19 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         return true;
     };
 
+    // (compiled in only for the developer build `ADAPT_BUILD_TRACE=1 python csrc/build.py`: even a never-taken
+    // branch per k-block in the MMA / producer loops costs the 3x3 layers a few percent)
+    auto stamp = [&](long long tile, int ev) {
+#if ADAPT_ENABLE_TRACE
+        if (p.trace != nullptr && tile < kTraceTiles)
+            p.trace[(static_cast<long long>(blockIdx.x) * kTraceTiles + tile) * kTraceEvents + ev] = clock64();
+#else
+        (void)tile;
+        (void)ev;
+#endif
+    };
+    if (threadIdx.x == 0) stamp(0, TR_CTA_START);
+
     if (warp_idx == 0 && lane == 0) {
         if (A_MODE != A_GATHER) ptx::prefetch_tmap(&tmap_a);
         ptx::prefetch_tmap(&tmap_b);
@@ -225,6 +260,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             for (int kb = 0; kb < p.num_k_blocks; ++kb, k_elem += kBlockK) {
                 ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
                 if (ptx::elect_one()) {
+                    if (kb == 0) stamp(ti, TR_PROD_FIRST);
+                    if (kb == p.num_k_blocks - 1) stamp(ti, TR_PROD_LAST);
                     uint8_t* a_dst = smem_a + stage * kABytes;
                     uint8_t* b_dst = smem_b + stage * kBBytes;
                     if (PAIR) {
@@ -290,10 +327,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             const uint32_t acc_phase = static_cast<uint32_t>(tile_iter >> 1) & 1;
             ptx::mbar_wait(&tmem_empty_bar[acc_stage], acc_phase ^ 1);
             ptx::tc_fence_after();
+            if (lane == 0) stamp(tile_iter, TR_MMA_START);
             const uint32_t tmem_d = tmem_base + acc_stage * BLOCK_N;
             for (int kb = 0; kb < p.num_k_blocks; ++kb) {
                 ptx::mbar_wait(&full_bar[stage], phase);
                 ptx::tc_fence_after();
+                if (kb == 0 && lane == 0) stamp(tile_iter, TR_MMA_FIRST);
                 if (ptx::elect_one()) {
                     const uint64_t a_desc = ptx::make_kmajor_sw128_desc(ptx::smem_u32(smem_a + stage * kABytes));
                     const uint64_t b_desc = ptx::make_kmajor_sw128_desc(ptx::smem_u32(smem_b + stage * kBBytes));
@@ -317,6 +356,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                             ptx::umma_commit_pair(&tmem_full_bar[acc_stage], kClusterMask);  // both CTAs' epilogues
                         else
                             ptx::umma_commit(&tmem_full_bar[acc_stage]);
+                        stamp(tile_iter, TR_MMA_DONE);
                     }
                 }
                 __syncwarp();
@@ -334,39 +374,51 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const int group = epi_warp >> 2;     // accumulator stage this warp drains
         const int lane_group = warp_idx & 3;  // TMEM lanes this warp may touch: [32*lane_group, +32)
         constexpr int kChunks = BLOCK_N / kEpiCols;
-        uint8_t* my_res = smem_epi + epi_warp * epi_warp_bytes;  // d_res slabs
-        uint8_t* my_out = my_res + p.d_res * kEpiSlabBytes;      // d_out slabs
+        // Per-warp ring of 4 KiB slabs.  Without a residual a slab only stages the outgoing chunk.  With one,
+        // the slab is used IN PLACE: TMA loads the residual chunk into it, the warp adds and overwrites, TMA
+        // stores it; the slab stored one chunk ago is then refilled with the residual `ring - 1` chunks ahead.
+        const bool has_res = d_res > 0;
+        const uint32_t ring = static_cast<uint32_t>(has_res ? d_res : d_out);
+        uint8_t* my_slabs = smem_epi + epi_warp * epi_warp_bytes;
+        const uint32_t slabs_sa = ptx::smem_u32(my_slabs);
         float* my_scale = smem_sb + epi_warp * 2 * BLOCK_N;
         const uint32_t scale_sa = ptx::smem_u32(my_scale);  // shared-space addresses for explicit ld/st.shared
         const uint32_t bias_sa = scale_sa + BLOCK_N * 4;
-        const uint32_t res_sa = ptx::smem_u32(my_res);
-        const uint32_t out_sa = ptx::smem_u32(my_out);
         uint64_t* my_res_bar = res_bar + epi_warp * kMaxRes;
-        const bool has_res = d_res > 0;
-        uint32_t res_par = 0;    // bit s: parity the next wait on residual slot s expects
-        uint32_t res_issue = 0;  // chunks (in consumption order over this CTA's tiles) whose load was issued
-        uint32_t res_slot_i = 0, res_slot_c = 0;  // ring positions of the next issue / next consume
-        uint32_t out_slot = 0;
+        uint32_t res_par = 0;  // bit s: parity the next wait on slab s expects
+        uint32_t slot = 0;     // slab of the chunk being drained
 
-        // Issue the residual load for the `res_issue`-th chunk this warp will consume (lane 0 does the TMA).
-        auto issue_residual = [&]() {
-            const uint32_t tile_i = res_issue / kChunks;
-            const uint32_t c = res_issue - tile_i * kChunks;
-            int m_blk = 0, n_blk = 0;
-            bool m_valid = true;
-            if (tile_at(group + 2LL * tile_i, m_blk, n_blk, m_valid)) {
-                const int m_row0 = m_blk * kBlockM + lane_group * 32;
-                if (m_valid && m_row0 < p.M && lane == 0) {
-                    ptx::mbar_expect_tx(&my_res_bar[res_slot_i], kEpiSlabBytes);
-                    ptx::tma_load_2d(my_res + res_slot_i * kEpiSlabBytes, &tmap_res, &my_res_bar[res_slot_i],
-                                     n_blk * BLOCK_N + c * kEpiCols, m_row0);
-                }
+        // Residual prefetch cursor: walks this warp's chunks in consumption order, one tile_at() per tile.
+        long long ri_iter = group;
+        int ri_c = 0, ri_row0 = 0, ri_col0 = 0;
+        uint32_t ri_slot = 0;
+        bool ri_live = false;
+        auto ri_locate = [&]() {
+            int mb = 0, nb = 0;
+            bool mv = true;
+            ri_live = false;
+            if (tile_at(ri_iter, mb, nb, mv)) {
+                ri_row0 = mb * kBlockM + lane_group * 32;
+                ri_col0 = nb * BLOCK_N;
+                ri_live = mv && ri_row0 < p.M;
             }
-            ++res_issue;
-            if (++res_slot_i == static_cast<uint32_t>(d_res)) res_slot_i = 0;
+        };
+        auto issue_residual = [&]() {
+            if (ri_live && lane == 0) {
+                ptx::mbar_expect_tx(&my_res_bar[ri_slot], kEpiSlabBytes);
+                ptx::tma_load_2d(my_slabs + ri_slot * kEpiSlabBytes, &tmap_res, &my_res_bar[ri_slot],
+                                 ri_col0 + ri_c * kEpiCols, ri_row0);
+            }
+            if (++ri_slot == ring) ri_slot = 0;
+            if (++ri_c == kChunks) {
+                ri_c = 0;
+                ri_iter += 2;
+                ri_locate();
+            }
         };
         if (p.epi_tma && has_res) {
-            for (int i = 0; i < d_res; ++i) issue_residual();  // prime the ring: d_res chunks in flight
+            ri_locate();
+            for (uint32_t i = 0; i + 1 < ring; ++i) issue_residual();  // prime: ring - 1 chunks in flight
         }
 
         int m_blk = 0, n_blk = 0;
@@ -388,6 +440,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 __syncwarp();
                 ptx::mbar_wait(&tmem_full_bar[acc_stage], acc_phase);
                 ptx::tc_fence_after();
+                if ((epi_warp & 3) == 0 && lane == 0) stamp(tile_iter, TR_EPI_START);
 #pragma unroll 1
                 for (int c = 0; c < kChunks; ++c) {
                     uint32_t v0[32], v1[32];
@@ -404,67 +457,73 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                                 ptx::mbar_arrive(&tmem_empty_bar[acc_stage]);
                         }
                     }
-                    const uint32_t res_slab = res_sa + res_slot_c * kEpiSlabBytes;
-                    if (has_res) {
-                        if (slab_ok) {
-                            ptx::mbar_wait(&my_res_bar[res_slot_c], (res_par >> res_slot_c) & 1);
-                            res_par ^= (1u << res_slot_c);
-                        }
-                        if (++res_slot_c == static_cast<uint32_t>(d_res)) res_slot_c = 0;
-                    }
+                    const uint32_t slab = slabs_sa + slot * kEpiSlabBytes;
+                    uint8_t* slab_ptr = my_slabs + slot * kEpiSlabBytes;
+                    const uint32_t this_slot = slot;
+                    if (++slot == ring) slot = 0;
                     if (!slab_ok) {
-                        if (has_res) issue_residual();
+                        if (has_res) {
+                            // (rare: rows past the end of M) nothing was stored from this chunk, so the newest
+                            // store group may still be reading the slab the prefetch is about to refill
+                            if (p.epi_tma == 1 && lane == 0) ptx::tma_store_wait_read<0>();
+                            __syncwarp();
+                            issue_residual();
+                        }
                         continue;
                     }
-                    const uint32_t out_slab = out_sa + out_slot * kEpiSlabBytes;
-                    uint8_t* out_slab_ptr = my_out + out_slot * kEpiSlabBytes;
-                    if (++out_slot == static_cast<uint32_t>(d_out)) out_slot = 0;
-                    // the TMA store issued from this out slab d_out chunks ago must have read it
-                    if (p.epi_tma == 1 && lane == 0) epi_store_wait_read(d_out - 1);
-                    __syncwarp();
+                    if (has_res) {
+                        ptx::mbar_wait(&my_res_bar[this_slot], (res_par >> this_slot) & 1);
+                        res_par ^= (1u << this_slot);
+                    } else {
+                        // the TMA store issued from this slab `ring` chunks ago must have read it
+                        if (p.epi_tma == 1 && lane == 0) epi_store_wait_read(static_cast<int>(ring) - 1);
+                        __syncwarp();
+                    }
                     const uint32_t sc = scale_sa + c * kEpiCols * 4;
                     const uint32_t bi = bias_sa + c * kEpiCols * 4;
+                    auto drain = [&](auto relu_tag) {
+                        constexpr bool kRelu = decltype(relu_tag)::value;
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {  // 8 columns = one 16-byte unit of this thread's row
-                        const uint32_t* vv = (j < 4) ? &v0[j * 8] : &v1[(j - 4) * 8];
-                        const float4 s0 = ptx::lds128f(sc + j * 32), s1 = ptx::lds128f(sc + j * 32 + 16);
-                        const float4 b0 = ptx::lds128f(bi + j * 32), b1 = ptx::lds128f(bi + j * 32 + 16);
-                        float y[8];
-                        y[0] = fmaf(__uint_as_float(vv[0]), s0.x, b0.x);
-                        y[1] = fmaf(__uint_as_float(vv[1]), s0.y, b0.y);
-                        y[2] = fmaf(__uint_as_float(vv[2]), s0.z, b0.z);
-                        y[3] = fmaf(__uint_as_float(vv[3]), s0.w, b0.w);
-                        y[4] = fmaf(__uint_as_float(vv[4]), s1.x, b1.x);
-                        y[5] = fmaf(__uint_as_float(vv[5]), s1.y, b1.y);
-                        y[6] = fmaf(__uint_as_float(vv[6]), s1.z, b1.z);
-                        y[7] = fmaf(__uint_as_float(vv[7]), s1.w, b1.w);
-                        const uint32_t sw = ((j ^ (lane & 7)) << 4) + lane * 128;
-                        if (has_res) {
-                            const uint4 rv = ptx::lds128(res_slab + sw);
-                            const __nv_bfloat162* r2 = reinterpret_cast<const __nv_bfloat162*>(&rv);
+                        for (int j = 0; j < 8; ++j) {  // 8 columns = one 16-byte unit of this thread's row
+                            const uint32_t* vv = (j < 4) ? &v0[j * 8] : &v1[(j - 4) * 8];
+                            const float4 s0 = ptx::lds128f(sc + j * 32), s1 = ptx::lds128f(sc + j * 32 + 16);
+                            const float4 b0 = ptx::lds128f(bi + j * 32), b1 = ptx::lds128f(bi + j * 32 + 16);
+                            float y[8];
+                            y[0] = fmaf(__uint_as_float(vv[0]), s0.x, b0.x);
+                            y[1] = fmaf(__uint_as_float(vv[1]), s0.y, b0.y);
+                            y[2] = fmaf(__uint_as_float(vv[2]), s0.z, b0.z);
+                            y[3] = fmaf(__uint_as_float(vv[3]), s0.w, b0.w);
+                            y[4] = fmaf(__uint_as_float(vv[4]), s1.x, b1.x);
+                            y[5] = fmaf(__uint_as_float(vv[5]), s1.y, b1.y);
+                            y[6] = fmaf(__uint_as_float(vv[6]), s1.z, b1.z);
+                            y[7] = fmaf(__uint_as_float(vv[7]), s1.w, b1.w);
+                            const uint32_t sw = ((j ^ (lane & 7)) << 4) + lane * 128;
+                            if (has_res) {
+                                const uint4 rv = ptx::lds128(slab + sw);
+                                const uint32_t r[4] = {rv.x, rv.y, rv.z, rv.w};
 #pragma unroll
-                            for (int e = 0; e < 4; ++e) {
-                                const float2 f = __bfloat1622float2(r2[e]);
-                                y[2 * e] += f.x;
-                                y[2 * e + 1] += f.y;
+                                for (int e = 0; e < 4; ++e) {  // bf16 pair -> two fp32: shift / mask, no permute
+                                    y[2 * e] += __uint_as_float(r[e] << 16);
+                                    y[2 * e + 1] += __uint_as_float(r[e] & 0xffff0000u);
+                                }
                             }
+                            uint4 ov;  // (ReLU rides on the fp32 -> bf16x2 conversion)
+                            ov.x = kRelu ? ptx::pack_bf16x2_relu(y[0], y[1]) : ptx::pack_bf16x2(y[0], y[1]);
+                            ov.y = kRelu ? ptx::pack_bf16x2_relu(y[2], y[3]) : ptx::pack_bf16x2(y[2], y[3]);
+                            ov.z = kRelu ? ptx::pack_bf16x2_relu(y[4], y[5]) : ptx::pack_bf16x2(y[4], y[5]);
+                            ov.w = kRelu ? ptx::pack_bf16x2_relu(y[6], y[7]) : ptx::pack_bf16x2(y[6], y[7]);
+                            ptx::sts128(slab + sw, ov);
                         }
-                        if (p.relu) {
-#pragma unroll
-                            for (int e = 0; e < 8; ++e) y[e] = fmaxf(y[e], 0.0f);
-                        }
-                        uint4 ov;
-                        __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&ov);
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(y[2 * e], y[2 * e + 1]);
-                        ptx::sts128(out_slab + sw, ov);
-                    }
+                    };
+                    if (p.relu)
+                        drain(std::true_type{});
+                    else
+                        drain(std::false_type{});
                     if (p.epi_tma == 1) ptx::fence_proxy_async_smem();  // slab writes -> visible to the TMA store
                     __syncwarp();
-                    if (has_res) issue_residual();  // the consumed residual slab is free: keep d_res chunks in flight
                     if (p.epi_tma == 1) {
                         if (lane == 0) {
-                            ptx::tma_store_2d(&tmap_out, out_slab_ptr, n_tile0 + c * kEpiCols, m_row0);
+                            ptx::tma_store_2d(&tmap_out, slab_ptr, n_tile0 + c * kEpiCols, m_row0);
                             ptx::tma_store_commit();
                         }
                     } else {
@@ -474,12 +533,21 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
                             const int row = i * 4 + (lane >> 3);
-                            const uint4 val = ptx::lds128(out_slab + row * 128 + ((ch ^ (row & 7)) << 4));
+                            const uint4 val = ptx::lds128(slab + row * 128 + ((ch ^ (row & 7)) << 4));
                             if (m_row0 + row < p.M)
                                 *reinterpret_cast<uint4*>(gout + static_cast<size_t>(row) * p.N + ch * 8) = val;
                         }
+                        __syncwarp();
+                    }
+                    if (has_res) {
+                        // every store but the one just issued has read its slab: the previous chunk's slab is free
+                        // for the residual `ring - 1` chunks ahead
+                        if (p.epi_tma == 1 && lane == 0) ptx::tma_store_wait_read<1>();
+                        __syncwarp();
+                        issue_residual();
                     }
                 }
+                if ((epi_warp & 3) == 0 && lane == 0) stamp(tile_iter, TR_EPI_DONE);
                 continue;
             }
             // ---------- direct epilogue (fp32 logits; debugging switch) ----------

@@ -23,6 +23,8 @@ def load_native():
     spec = importlib.util.spec_from_file_location("adapt_native", os.path.join(PKG, "_native.py"))
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
+    if os.environ.get("KC_LIB"):  # A/B against another build of the library
+        mod.LIB_PATH = os.path.abspath(os.environ["KC_LIB"])
     return mod
 
 
@@ -212,12 +214,68 @@ def run_perf() -> int:
     return 0
 
 
+def run_trace() -> int:
+    """One launch per selected perf layer with the role timeline enabled; prints per-launch medians (SM clocks)."""
+    import statistics as st
+    import tempfile
+
+    trace_lib = os.path.join(PKG, "csrc", "libadapt_b200_trace.so")
+    if not os.path.exists(trace_lib):
+        print("build the timeline library first: ADAPT_BUILD_TRACE=1 python <pkg>/csrc/build.py", file=sys.stderr)
+        return 2
+    os.environ["KC_LIB"] = trace_lib
+    tf = tempfile.NamedTemporaryFile(suffix=".jsonl", delete=False)
+    tf.close()
+    os.environ["ADAPT_TRACE_FILE"] = tf.name
+    os.environ["KC_ITERS"] = "1"
+    run_perf()
+    ev = {"cta": 0, "p0": 1, "p1": 2, "m0": 3, "m1": 4, "m2": 5, "e0": 6, "e1": 7}
+    for line in open(tf.name):
+        r = json.loads(line)
+        T, E, G = r["tiles"], r["events"], r["grid"]
+        s = r["stamps"]
+        at = lambda c, t, e: s[(c * T + t) * E + e]  # noqa: E731
+        agg = {k: [] for k in ("prologue", "first_data", "mma_tile", "mma_gap", "epi_wait", "epi_tile", "span",
+                               "prod_tile", "tiles")}
+        for c in range(G):
+            t0 = at(c, 0, ev["cta"])
+            if t0 == 0:
+                continue
+            n = 0
+            while n < T and at(c, n, ev["m2"]) != 0:
+                n += 1
+            if n == 0:
+                continue
+            agg["tiles"].append(n)
+            agg["prologue"].append(at(c, 0, ev["p0"]) - t0)
+            agg["first_data"].append(at(c, 0, ev["m1"]) - at(c, 0, ev["p0"]))
+            last = t0
+            for t in range(n):
+                agg["mma_tile"].append(at(c, t, ev["m2"]) - at(c, t, ev["m1"]))
+                agg["prod_tile"].append(at(c, t, ev["p1"]) - at(c, t, ev["p0"]))
+                if t:
+                    agg["mma_gap"].append(at(c, t, ev["m1"]) - at(c, t - 1, ev["m2"]))
+                if at(c, t, ev["e0"]):
+                    agg["epi_wait"].append(at(c, t, ev["e0"]) - at(c, t, ev["m2"]))
+                    agg["epi_tile"].append(at(c, t, ev["e1"]) - at(c, t, ev["e0"]))
+                    last = max(last, at(c, t, ev["e1"]))
+            agg["span"].append(last - t0)
+        med = {k: (round(st.median(v)) if v else None) for k, v in agg.items()}
+        med["span_max"] = max(agg["span"]) if agg["span"] else None
+        print(json.dumps({k: r[k] for k in ("grid", "block_n", "a_mode", "pair", "m_tiles", "n_tiles", "k_blocks", "stages")}
+                         | med), flush=True)
+    os.unlink(tf.name)
+    return 0
+
+
 def main() -> int:
     ap = argparse.ArgumentParser()
     ap.add_argument("--group", default=None)
     args = ap.parse_args()
     if args.group == "perf":
         return run_perf()
+    if args.group == "trace":
+        return run_trace()
     if args.group:
         return run_group(args.group)
     rc_all = 0
