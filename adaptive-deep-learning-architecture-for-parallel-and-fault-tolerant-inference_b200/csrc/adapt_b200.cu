@@ -458,80 +458,65 @@ int max_resident_clusters(int cluster) {
     return n;
 }
 
-template <int BN>
-void launch_conv_bn(const ConvLaunch& L, cudaStream_t s) {
-    switch (L.a_mode) {
-        case adapt::A_TILED:
-            adapt::conv_gemm_kernel<BN, adapt::A_TILED><<<L.grid, adapt::conv_gemm_threads<adapt::A_TILED>(), L.smem, s>>>(
-                L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
-            break;
-        case adapt::A_IM2COL:
-            adapt::conv_gemm_kernel<BN, adapt::A_IM2COL><<<L.grid, adapt::conv_gemm_threads<adapt::A_IM2COL>(), L.smem, s>>>(
-                L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
-            break;
-        default:
-            adapt::conv_gemm_kernel<BN, adapt::A_GATHER><<<L.grid, adapt::conv_gemm_threads<adapt::A_GATHER>(), L.smem, s>>>(
-                L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
-            break;
+// Every conv_gemm launch goes through cudaLaunchKernelEx: cluster dimension for the multicast / CTA-pair
+// variants, and (unless ADAPT_PDL=0) programmatic stream serialization, so that a layer's CTAs may start
+// their prologue -- barrier init, TMEM allocation, descriptor and weight prefetch -- on SMs the previous
+// layer has already left; the kernel then blocks in griddepcontrol.wait before touching activations.
+bool pdl_enabled() {
+    static int v = env_int("ADAPT_PDL", 1);
+    return v != 0;
+}
+
+template <int BN, int MODE, int CL, bool PAIR>
+cudaError_t launch_conv_ex(const ConvLaunch& L, cudaStream_t s) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)L.grid);
+    cfg.blockDim = dim3((unsigned)adapt::conv_gemm_threads<MODE>());
+    cfg.dynamicSmemBytes = (size_t)L.smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[2];
+    unsigned n = 0;
+    if (CL > 1) {
+        attr[n].id = cudaLaunchAttributeClusterDimension;
+        attr[n].val.clusterDim.x = CL;
+        attr[n].val.clusterDim.y = 1;
+        attr[n].val.clusterDim.z = 1;
+        ++n;
     }
-}
-
-template <int BN, int MODE, int CL>
-cudaError_t launch_conv_cluster(const ConvLaunch& L, cudaStream_t s) {
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3((unsigned)L.grid);
-    cfg.blockDim = dim3((unsigned)adapt::conv_gemm_threads<MODE>());
-    cfg.dynamicSmemBytes = (size_t)L.smem;
-    cfg.stream = s;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = CL;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
+    if (pdl_enabled()) {
+        attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[n].val.programmaticStreamSerializationAllowed = 1;
+        ++n;
+    }
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, adapt::conv_gemm_kernel<BN, MODE, CL>, L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
-}
-
-template <int BN, int MODE>
-cudaError_t launch_conv_pair(const ConvLaunch& L, cudaStream_t s) {
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3((unsigned)L.grid);
-    cfg.blockDim = dim3((unsigned)adapt::conv_gemm_threads<MODE>());
-    cfg.dynamicSmemBytes = (size_t)L.smem;
-    cfg.stream = s;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 2;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, adapt::conv_gemm_kernel<BN, MODE, 2, true>, L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res, L.p);
+    cfg.numAttrs = n;
+    return cudaLaunchKernelEx(&cfg, adapt::conv_gemm_kernel<BN, MODE, CL, PAIR>, L.tmap_a, L.tmap_b, L.tmap_out, L.tmap_res,
+                              L.p);
 }
 
 template <int BN>
-cudaError_t launch_conv_clustered_bn(const ConvLaunch& L, cudaStream_t s) {
-    if (L.pair)
-        return L.a_mode == adapt::A_TILED ? launch_conv_pair<BN, adapt::A_TILED>(L, s)
-                                          : launch_conv_pair<BN, adapt::A_IM2COL>(L, s);
-    if (L.a_mode == adapt::A_TILED)
-        return L.cluster == 2 ? launch_conv_cluster<BN, adapt::A_TILED, 2>(L, s) : launch_conv_cluster<BN, adapt::A_TILED, 4>(L, s);
-    return L.cluster == 2 ? launch_conv_cluster<BN, adapt::A_IM2COL, 2>(L, s) : launch_conv_cluster<BN, adapt::A_IM2COL, 4>(L, s);
+cudaError_t launch_conv_bn(const ConvLaunch& L, cudaStream_t s) {
+    if (L.a_mode == adapt::A_GATHER) return launch_conv_ex<BN, adapt::A_GATHER, 1, false>(L, s);
+    const bool tiled = L.a_mode == adapt::A_TILED;
+    if constexpr (BN >= 128) {
+        if (L.pair)
+            return tiled ? launch_conv_ex<BN, adapt::A_TILED, 2, true>(L, s) : launch_conv_ex<BN, adapt::A_IM2COL, 2, true>(L, s);
+        if (L.cluster == 2)
+            return tiled ? launch_conv_ex<BN, adapt::A_TILED, 2, false>(L, s) : launch_conv_ex<BN, adapt::A_IM2COL, 2, false>(L, s);
+        if (L.cluster == 4)
+            return tiled ? launch_conv_ex<BN, adapt::A_TILED, 4, false>(L, s) : launch_conv_ex<BN, adapt::A_IM2COL, 4, false>(L, s);
+    }
+    return tiled ? launch_conv_ex<BN, adapt::A_TILED, 1, false>(L, s) : launch_conv_ex<BN, adapt::A_IM2COL, 1, false>(L, s);
 }
 
 int run_conv_launch(const ConvLaunch& L, cudaStream_t s) {
-    if (L.cluster > 1) {
-        CUDA_TRY(L.block_n == 128 ? launch_conv_clustered_bn<128>(L, s) : launch_conv_clustered_bn<256>(L, s));
-        return ADAPT_OK;
-    }
+    if (L.cluster > 1 && L.block_n < 128) return fail(ADAPT_EINVAL, "conv: clusters need block_n >= 128");
     if (L.block_n == 64)
-        launch_conv_bn<64>(L, s);
+        CUDA_TRY(launch_conv_bn<64>(L, s));
     else if (L.block_n == 128)
-        launch_conv_bn<128>(L, s);
+        CUDA_TRY(launch_conv_bn<128>(L, s));
     else
-        launch_conv_bn<256>(L, s);
-    CUDA_TRY(cudaGetLastError());
+        CUDA_TRY(launch_conv_bn<256>(L, s));
     return ADAPT_OK;
 }
 

@@ -230,6 +230,22 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
+    // Programmatic dependent launch: everything above ran while the previous layer may still have been
+    // finishing on other SMs.  Let the next layer start the same way, pull this CTA's first weight tiles
+    // (which no kernel writes) towards L2, then wait for the previous layer's activations to be complete.
+    ptx::griddep_launch_dependents();
+    if (warp_idx == 0 && ptx::elect_one()) {
+        int mb = 0, nb = 0;
+        bool mv = true;
+        if (tile_at(0, mb, nb, mv)) {
+            const int rows = PAIR ? BLOCK_N / 2 : (CL == 1 ? BLOCK_N : BLOCK_N / CL);
+            const int row0 = nb * BLOCK_N + (CL > 1 ? cl_rank * rows : 0);
+            const int nkb = p.num_k_blocks < kStages ? p.num_k_blocks : kStages;
+            for (int kb = 0; kb < nkb; ++kb) ptx::tma_prefetch_2d(&tmap_b, kb * kBlockK, row0);
+        }
+    }
+    ptx::griddep_wait();
+
     if (warp_idx == 0) {
         // ===================== TMA producer =====================
         // The whole warp walks the loop (uniform control flow keeps the coordinates in uniform registers and

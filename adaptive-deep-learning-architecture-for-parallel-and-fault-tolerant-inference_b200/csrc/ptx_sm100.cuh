@@ -154,6 +154,17 @@ __device__ __forceinline__ void mbar_arrive_remote(uint64_t* bar, uint32_t cta_r
         : "memory");
 }
 
+// ---- programmatic dependent launch: a kernel launched with programmatic stream serialization may start
+// while its predecessor in the stream is still running; griddep_wait() blocks until the predecessor has
+// completed and its writes are visible, griddep_launch_dependents() lets the successor start early.
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+// L2 prefetch of a 2-D tile (no shared-memory destination, no barrier)
+__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* m, int x, int y) {
+    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];" ::"l"(reinterpret_cast<uint64_t>(m)), "r"(x), "r"(y)
+                 : "memory");
+}
+
 // two fp32 -> packed bf16x2 (round to nearest even), `lo` in the low half; the _relu form clamps negatives to 0
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     uint32_t d;
