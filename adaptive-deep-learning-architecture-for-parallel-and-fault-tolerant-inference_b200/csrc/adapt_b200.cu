@@ -413,7 +413,16 @@ int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const vo
     }
     if (stages > adapt::kMaxStages) stages = adapt::kMaxStages;
     if (stages < 2) stages = 2;
-    while (adapt::conv_gemm_smem_bytes(bn, stages, d_out, d_res, L->pair) > adapt::kMaxSmemBytes) {
+    // Resident B: one n-tile, several m-tiles per CTA and a weight matrix of at most 96 KiB -> keep it in shared
+    // memory for the whole launch instead of re-fetching it with every tile (stem, conv2 3x3, 1x1 -> 64).
+    int b_res_blocks = 0;
+    if (env_int("ADAPT_B_RESIDENT", 1) && p.n_tiles == 1 && L->cluster == 1 && a_mode != adapt::A_GATHER &&
+        p.num_k_blocks * bn * adapt::kBlockK * 2 <= 96 * 1024 && p.m_tiles > L->grid) {
+        b_res_blocks = p.num_k_blocks;
+        stages = adapt::kMaxStages;  // the ring carries 16 KiB A tiles only: take what fits
+    }
+    p.b_resident = b_res_blocks > 0 ? 1 : 0;
+    while (adapt::conv_gemm_smem_bytes(bn, stages, d_out, d_res, L->pair, b_res_blocks) > adapt::kMaxSmemBytes) {
         if (stages > 4) --stages;
         else if (d_res > 3) --d_res;
         else if (stages > 3) --stages;
@@ -426,7 +435,7 @@ int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const vo
     p.stages = stages;
     p.d_out = d_out;
     p.d_res = d_res;
-    L->smem = adapt::conv_gemm_smem_bytes(bn, stages, d_out, d_res, L->pair);
+    L->smem = adapt::conv_gemm_smem_bytes(bn, stages, d_out, d_res, L->pair, b_res_blocks);
     return ADAPT_OK;
 }
 
@@ -714,7 +723,7 @@ int run_steps(adapt_stage* st, const std::vector<Step>& steps, cudaStream_t stre
                 const int threads = 256;
                 const unsigned blocks = (unsigned)((total + threads - 1) / threads);
                 if (st->mode == ADAPT_MODE_BF16)
-                    adapt::maxpool_zeropad_kernel<__nv_bfloat16><<<blocks, threads, 0, stream>>>(
+                    adapt::maxpool_zeropad_bf16_kernel<<<blocks, threads, 0, stream>>>(
                         reinterpret_cast<const __nv_bfloat16*>(s.in), reinterpret_cast<__nv_bfloat16*>(s.out), B, o.H,
                         o.W, o.Cin, o.Ho, o.Wo, o.kh, o.stride, o.pad);
                 else

@@ -57,6 +57,9 @@ struct ConvGemmParams {
     int stages;  // operand pipeline depth, 2..kMaxStages
     int d_out;   // output staging slabs per epilogue warp (2 or 4)
     int d_res;   // residual staging slabs per epilogue warp (2..kMaxRes; ignored without residual)
+    // 1: the whole B operand (n_tiles == 1, num_k_blocks tiles) stays in shared memory; loaded with the CTA's
+    // first tile, after which the operand ring carries A only
+    int b_resident;
     // A_GATHER source
     const __nv_bfloat16* in;
     // developer timeline (nullptr in production): [grid][kTraceTiles][kTraceEvents] SM clock stamps
@@ -102,8 +105,12 @@ __host__ __device__ constexpr int conv_gemm_stage_bytes(int block_n, bool pair =
 __host__ __device__ constexpr int conv_gemm_epi_bytes(int block_n, int d_out, int d_res) {
     return kEpiWarps * (d_out + d_res) * kEpiSlabBytes + kEpiWarps * 2 * block_n * 4;
 }
-__host__ __device__ constexpr int conv_gemm_smem_bytes(int block_n, int stages, int d_out, int d_res, bool pair = false) {
-    return stages * conv_gemm_stage_bytes(block_n, pair) + conv_gemm_epi_bytes(block_n, d_out, d_res) + kBarrierBytes + 1024;
+// (b_resident_blocks > 0: B is held once, `b_resident_blocks` k-blocks deep, instead of once per stage)
+__host__ __device__ constexpr int conv_gemm_smem_bytes(int block_n, int stages, int d_out, int d_res, bool pair = false,
+                                                       int b_resident_blocks = 0) {
+    return (b_resident_blocks > 0 ? stages * kABytes + b_resident_blocks * (conv_gemm_stage_bytes(block_n, pair) - kABytes)
+                                  : stages * conv_gemm_stage_bytes(block_n, pair)) +
+           conv_gemm_epi_bytes(block_n, d_out, d_res) + kBarrierBytes + 1024;
 }
 
 template <int A_MODE>
@@ -150,7 +157,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* smem_a = smem;
     uint8_t* smem_b = smem + kStages * kABytes;
-    uint8_t* smem_epi = smem + kStages * kStageBytes;  // [4 warps][d_res + d_out] slabs, 1024-aligned
+    const int b_slots = p.b_resident ? p.num_k_blocks : kStages;  // B tiles held: the whole operand, or one per stage
+    uint8_t* smem_epi = smem + kStages * kABytes + b_slots * kBBytes;  // [8 warps][ring] slabs, 1024-aligned
     const int epi_warp_bytes = (p.d_out + p.d_res) * kEpiSlabBytes;
     float* smem_sb = reinterpret_cast<float*>(smem_epi + kEpiWarps * epi_warp_bytes);  // per warp [scale | bias]
     uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(smem_sb) + kEpiWarps * 2 * BLOCK_N * 4);
@@ -279,8 +287,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     if (kb == 0) stamp(ti, TR_PROD_FIRST);
                     if (kb == p.num_k_blocks - 1) stamp(ti, TR_PROD_LAST);
                     uint8_t* a_dst = smem_a + stage * kABytes;
-                    uint8_t* b_dst = smem_b + stage * kBBytes;
-                    if (PAIR) {
+                    uint8_t* b_dst = smem_b + (p.b_resident ? kb : stage) * kBBytes;
+                    const bool load_b = !p.b_resident || ti == 0;  // resident B arrives with the CTA's first tile
+                    if (!PAIR && CL == 1 && A_MODE != A_GATHER && !load_b) {
+                        ptx::mbar_expect_tx(&full_bar[stage], kABytes);
+                    } else if (PAIR) {
                         // both CTAs' loads report to the LEADER's barrier, which the leader arms for all of them
                         if (cl_rank == 0) ptx::mbar_expect_tx(&full_bar[stage], 2 * kStageBytes);
                     } else if (A_MODE == A_GATHER) {
@@ -305,7 +316,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         // this CTA's half of the B tile (the pair's MMA reads both halves in place)
                         ptx::tma_load_2d_pair(b_dst, &tmap_b, &full_bar[stage], k_elem, b_row);
                     } else if (CL == 1) {
-                        ptx::tma_load_2d(b_dst, &tmap_b, &full_bar[stage], k_elem, b_row);
+                        if (load_b) ptx::tma_load_2d(b_dst, &tmap_b, &full_bar[stage], k_elem, b_row);
                     } else {
                         // this CTA's 1/CL slice of the B tile, delivered to all CTAs of the cluster
                         constexpr int kSliceRows = BLOCK_N / CL;
@@ -351,7 +362,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 if (kb == 0 && lane == 0) stamp(tile_iter, TR_MMA_FIRST);
                 if (ptx::elect_one()) {
                     const uint64_t a_desc = ptx::make_kmajor_sw128_desc(ptx::smem_u32(smem_a + stage * kABytes));
-                    const uint64_t b_desc = ptx::make_kmajor_sw128_desc(ptx::smem_u32(smem_b + stage * kBBytes));
+                    const uint64_t b_desc =
+                        ptx::make_kmajor_sw128_desc(ptx::smem_u32(smem_b + (p.b_resident ? kb : stage) * kBBytes));
 #pragma unroll
                     for (int k = 0; k < kBlockK / kUmmaK; ++k) {
                         // advance 16 elements (32 B) along K inside the swizzle atom: +2 in 16-byte units

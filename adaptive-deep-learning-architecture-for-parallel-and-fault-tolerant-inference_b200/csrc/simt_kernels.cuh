@@ -157,6 +157,60 @@ __global__ void maxpool_zeropad_kernel(const T* __restrict__ in, T* __restrict__
     o.store(out + ((static_cast<long long>(b) * Ho + po) * Wo + qo) * C + cv * 8);
 }
 
+// bf16 specialisation: the maximum is exact in any format, so it is taken on packed bf16x2 lanes (4 HMNMX2
+// per 16-byte load instead of 8 conversions + 8 FMNMX), with 32-bit index arithmetic.
+__global__ void maxpool_zeropad_bf16_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, int B,
+                                            int H, int W, int C, int Ho, int Wo, int k, int s, int pad) {
+    const int cvecs = C / 8;
+    const long long total = static_cast<long long>(B) * Ho * Wo * cvecs;
+    const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+    if (i >= total) return;
+    const unsigned per_img = static_cast<unsigned>(Ho * Wo * cvecs);
+    const int b = static_cast<int>(i / per_img);
+    unsigned rem = static_cast<unsigned>(i - static_cast<long long>(b) * per_img);
+    const int cv = static_cast<int>(rem % static_cast<unsigned>(cvecs));
+    rem /= static_cast<unsigned>(cvecs);
+    const int qo = static_cast<int>(rem % static_cast<unsigned>(Wo));
+    const int po = static_cast<int>(rem / static_cast<unsigned>(Wo));
+    const __nv_bfloat162 neg_inf = __float2bfloat162_rn(-INFINITY);
+    __nv_bfloat162 m0 = neg_inf, m1 = neg_inf, m2 = neg_inf, m3 = neg_inf;
+    bool any_pad = false;
+    const __nv_bfloat16* img = in + static_cast<long long>(b) * H * W * C + cv * 8;
+    const int h0 = po * s - pad, w0 = qo * s - pad;
+    for (int r = 0; r < k; ++r) {
+        const int hi = h0 + r;
+        if (hi < 0 || hi >= H) {
+            any_pad = true;
+            continue;
+        }
+        for (int t = 0; t < k; ++t) {
+            const int wi = w0 + t;
+            if (wi < 0 || wi >= W) {
+                any_pad = true;
+                continue;
+            }
+            const uint4 v = __ldg(reinterpret_cast<const uint4*>(img + (hi * W + wi) * C));
+            m0 = __hmax2(m0, *reinterpret_cast<const __nv_bfloat162*>(&v.x));
+            m1 = __hmax2(m1, *reinterpret_cast<const __nv_bfloat162*>(&v.y));
+            m2 = __hmax2(m2, *reinterpret_cast<const __nv_bfloat162*>(&v.z));
+            m3 = __hmax2(m3, *reinterpret_cast<const __nv_bfloat162*>(&v.w));
+        }
+    }
+    if (any_pad) {  // the ZeroPadding2D samples
+        const __nv_bfloat162 zero = __float2bfloat162_rn(0.0f);
+        m0 = __hmax2(m0, zero);
+        m1 = __hmax2(m1, zero);
+        m2 = __hmax2(m2, zero);
+        m3 = __hmax2(m3, zero);
+    }
+    uint4 o;
+    o.x = *reinterpret_cast<uint32_t*>(&m0);
+    o.y = *reinterpret_cast<uint32_t*>(&m1);
+    o.z = *reinterpret_cast<uint32_t*>(&m2);
+    o.w = *reinterpret_cast<uint32_t*>(&m3);
+    *reinterpret_cast<uint4*>(out + ((static_cast<long long>(b) * Ho + po) * Wo + qo) * C + cv * 8) = o;
+}
+
 // ---------------------------------------------------------------------------------------------
 // Stand-alone per-channel affine (+ReLU): a BatchNormalization / Activation that a cut separated
 // from its convolution.  scale == nullptr means ReLU only.  8 channels per thread.
