@@ -32,7 +32,12 @@
 
 namespace adapt {
 
-enum AMode : int { A_TILED = 0, A_IM2COL = 1, A_GATHER = 2 };
+// A_ROW3: 3x3 / stride 1 / pad 1 convolutions with the three horizontal taps of a filter row served from ONE
+// shared-memory tile.  The output is walked in "padded-flat" order (rows of W + 2 positions, the last two of
+// each row are discarded), so that tap s of output position m is input position m + s of the same walk: one
+// im2col load of 128 + 2 (rounded to 136) positions per (filter row, channel block) feeds three k-blocks
+// through descriptors whose start is shifted by s pixel rows.  The A bytes an SM ingests drop 3x.
+enum AMode : int { A_TILED = 0, A_IM2COL = 1, A_GATHER = 2, A_ROW3 = 3 };
 
 struct ConvGemmParams {
     int M;             // output pixels in this launch: batch * Ho * Wo
@@ -60,6 +65,9 @@ struct ConvGemmParams {
     // 1: the whole B operand (n_tiles == 1, num_k_blocks tiles) stays in shared memory; loaded with the CTA's
     // first tile, after which the operand ring carries A only
     int b_resident;
+    // A_ROW3: positions per padded-flat row (W + 2), valid positions per row (W); M and m_tiles count padded-flat
+    // positions.
+    int row_pitch, row_valid;
     // A_GATHER source
     const __nv_bfloat16* in;
     // developer timeline (nullptr in production): [grid][kTraceTiles][kTraceEvents] SM clock stamps
@@ -88,6 +96,8 @@ constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;  // 64 bf16 = one 128-byte swizzle row
 constexpr int kUmmaK = 16;
 constexpr int kABytes = kBlockM * kBlockK * 2;
+constexpr int kRow3Rows = 136;  // 128 + 2 shifted rows, rounded up to whole 8-row swizzle groups
+constexpr int kRow3ABytes = kRow3Rows * kBlockK * 2;  // 17 KiB
 constexpr int kMaxStages = 8;
 constexpr int kMaxRes = 8;
 
@@ -106,10 +116,13 @@ __host__ __device__ constexpr int conv_gemm_epi_bytes(int block_n, int d_out, in
     return kEpiWarps * (d_out + d_res) * kEpiSlabBytes + kEpiWarps * 2 * block_n * 4;
 }
 // (b_resident_blocks > 0: B is held once, `b_resident_blocks` k-blocks deep, instead of once per stage)
+// (row3: a stage is one 17 KiB A tile plus the three B tiles of a filter row)
 __host__ __device__ constexpr int conv_gemm_smem_bytes(int block_n, int stages, int d_out, int d_res, bool pair = false,
-                                                       int b_resident_blocks = 0) {
-    return (b_resident_blocks > 0 ? stages * kABytes + b_resident_blocks * (conv_gemm_stage_bytes(block_n, pair) - kABytes)
-                                  : stages * conv_gemm_stage_bytes(block_n, pair)) +
+                                                       int b_resident_blocks = 0, bool row3 = false) {
+    const int a_bytes = row3 ? kRow3ABytes : kABytes;
+    const int b_bytes = conv_gemm_stage_bytes(block_n, pair) - kABytes;
+    return (b_resident_blocks > 0 ? stages * a_bytes + b_resident_blocks * b_bytes
+                                  : stages * (a_bytes + (row3 ? 3 : 1) * b_bytes)) +
            conv_gemm_epi_bytes(block_n, d_out, d_res) + kBarrierBytes + 1024;
 }
 
@@ -146,8 +159,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     static_assert(CL == 1 || CL == 2 || CL == 4, "cluster size");
     static_assert(CL == 1 || A_MODE != A_GATHER, "the gather path does not multicast");
     static_assert(!PAIR || CL == 2, "a CTA pair is a cluster of two");
+    static_assert(A_MODE != A_ROW3 || CL == 1 || PAIR, "row-reuse mode: single CTA or CTA pair");
+    constexpr bool ROW3 = A_MODE == A_ROW3;
     constexpr int kBBytes = (PAIR ? BLOCK_N / 2 : BLOCK_N) * kBlockK * 2;
-    constexpr int kStageBytes = kABytes + kBBytes;
+    constexpr int kATile = ROW3 ? kRow3ABytes : kABytes;  // A bytes per stage
+    constexpr int kBPerStage = ROW3 ? 3 : 1;              // B tiles (k-blocks) per stage
+    constexpr int kStageBytes = kATile + kBPerStage * kBBytes;
     constexpr int kTmemCols = 2 * BLOCK_N;  // double-buffered accumulator (power of 2 >= 32)
     const int kStages = p.stages;
     const int d_out = p.d_out;
@@ -156,9 +173,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* smem_a = smem;
-    uint8_t* smem_b = smem + kStages * kABytes;
-    const int b_slots = p.b_resident ? p.num_k_blocks : kStages;  // B tiles held: the whole operand, or one per stage
-    uint8_t* smem_epi = smem + kStages * kABytes + b_slots * kBBytes;  // [8 warps][ring] slabs, 1024-aligned
+    uint8_t* smem_b = smem + kStages * kATile;
+    const int b_slots = p.b_resident ? p.num_k_blocks : kStages * kBPerStage;  // B tiles held: whole operand, or per stage
+    uint8_t* smem_epi = smem + kStages * kATile + b_slots * kBBytes;  // [8 warps][ring] slabs, 1024-aligned
+    const int k_iters = ROW3 ? 3 * p.c_blocks : p.num_k_blocks;  // pipeline steps per tile
     const int epi_warp_bytes = (p.d_out + p.d_res) * kEpiSlabBytes;
     float* smem_sb = reinterpret_cast<float*>(smem_epi + kEpiWarps * epi_warp_bytes);  // per warp [scale | bias]
     uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(smem_sb) + kEpiWarps * 2 * BLOCK_N * 4);
@@ -265,6 +283,56 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         bool m_valid = true;
         for (long long ti = 0; tile_at(ti, m_blk_raw, n_blk, m_valid); ++ti) {
             const int m_blk = m_valid ? m_blk_raw : p.m_tiles - 1;  // overhanging CTA: re-load a valid tile
+            if constexpr (ROW3) {
+                // start of this tile in the padded-flat walk: position q0 of row p0 of image img0
+                const int m0 = m_blk * kBlockM;
+                const int rest = m0 / p.row_pitch;
+                const int q0 = m0 - rest * p.row_pitch;
+                const int img0 = rest / p.H;
+                const int p0 = rest - img0 * p.H;
+                const int b_row3 = PAIR ? n_blk * BLOCK_N + cl_rank * (BLOCK_N / 2) : n_blk * BLOCK_N;
+                int tap_r3 = 0, cb3 = 0;
+                for (int it = 0; it < k_iters; ++it) {
+                    ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+                    if (ptx::elect_one()) {
+                        if (it == 0) stamp(ti, TR_PROD_FIRST);
+                        if (it == k_iters - 1) stamp(ti, TR_PROD_LAST);
+                        const bool load_b = !p.b_resident || ti == 0;  // resident B arrives with the CTA's first tile
+                        const uint32_t bytes = kATile + (load_b ? 3 * kBBytes : 0);
+                        uint8_t* a_dst = smem_a + stage * kATile;
+                        if (PAIR) {
+                            if (cl_rank == 0) ptx::mbar_expect_tx(&full_bar[stage], 2 * bytes);
+                            ptx::tma_load_im2col_4d_pair(a_dst, &tmap_a, &full_bar[stage], cb3 * kBlockK, q0 - 1, p0 - 1, img0, 0,
+                                                         static_cast<uint16_t>(tap_r3));
+                        } else {
+                            ptx::mbar_expect_tx(&full_bar[stage], bytes);
+                            ptx::tma_load_im2col_4d(a_dst, &tmap_a, &full_bar[stage], cb3 * kBlockK, q0 - 1, p0 - 1, img0, 0,
+                                                    static_cast<uint16_t>(tap_r3));
+                        }
+                        if (load_b) {
+#pragma unroll
+                            for (int s3 = 0; s3 < 3; ++s3) {
+                                const int kbi = (tap_r3 * 3 + s3) * p.c_blocks + cb3;  // k-block of tap (r, s), channels cb
+                                uint8_t* b_dst = smem_b + (p.b_resident ? kbi : stage * 3 + s3) * kBBytes;
+                                if (PAIR)
+                                    ptx::tma_load_2d_pair(b_dst, &tmap_b, &full_bar[stage], kbi * kBlockK, b_row3);
+                                else
+                                    ptx::tma_load_2d(b_dst, &tmap_b, &full_bar[stage], kbi * kBlockK, b_row3);
+                            }
+                        }
+                    }
+                    __syncwarp();
+                    if (++cb3 == p.c_blocks) {
+                        cb3 = 0;
+                        ++tap_r3;
+                    }
+                    if (++stage == kStages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+                continue;
+            }
             int img = 0, base_w = 0, base_h = 0;
             if (A_MODE == A_IM2COL) {
                 const int m0 = m_blk * kBlockM;
@@ -356,7 +424,56 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             ptx::tc_fence_after();
             if (lane == 0) stamp(tile_iter, TR_MMA_START);
             const uint32_t tmem_d = tmem_base + acc_stage * BLOCK_N;
-            for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+            if constexpr (ROW3) {
+                int tap_r3 = 0, cb3 = 0;
+                for (int it = 0; it < k_iters; ++it) {
+                    ptx::mbar_wait(&full_bar[stage], phase);
+                    ptx::tc_fence_after();
+                    if (it == 0 && lane == 0) stamp(tile_iter, TR_MMA_FIRST);
+                    if (ptx::elect_one()) {
+                        const uint32_t a_base = ptx::smem_u32(smem_a + stage * kATile);
+#pragma unroll
+                        for (int s3 = 0; s3 < 3; ++s3) {
+                            const int kbi = (tap_r3 * 3 + s3) * p.c_blocks + cb3;
+                            // tap s reads the same tile one pixel row (128 B) further on.  The 128-byte swizzle is a
+                            // function of the absolute shared-memory address (measured: a start shifted by whole
+                            // rows is read correctly with the descriptor's base-offset field left at 0, and wrongly
+                            // with the row phase written into it), so only the start address moves.
+                            const uint64_t a_desc = ptx::make_kmajor_sw128_desc(a_base + s3 * (kBlockK * 2));
+                            const uint64_t b_desc = ptx::make_kmajor_sw128_desc(
+                                ptx::smem_u32(smem_b + (p.b_resident ? kbi : stage * 3 + s3) * kBBytes));
+#pragma unroll
+                            for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+                                if (PAIR)
+                                    ptx::umma_bf16_ss_pair(tmem_d, a_desc + 2 * k, b_desc + 2 * k, idesc, (it | s3 | k) != 0 ? 1u : 0u);
+                                else
+                                    ptx::umma_bf16_ss(tmem_d, a_desc + 2 * k, b_desc + 2 * k, idesc, (it | s3 | k) != 0 ? 1u : 0u);
+                            }
+                        }
+                        if (PAIR)
+                            ptx::umma_commit_pair(&empty_bar[stage], kClusterMask);
+                        else
+                            ptx::umma_commit(&empty_bar[stage]);
+                        if (it == k_iters - 1) {
+                            if (PAIR)
+                                ptx::umma_commit_pair(&tmem_full_bar[acc_stage], kClusterMask);
+                            else
+                                ptx::umma_commit(&tmem_full_bar[acc_stage]);
+                            stamp(tile_iter, TR_MMA_DONE);
+                        }
+                    }
+                    __syncwarp();
+                    if (++cb3 == p.c_blocks) {
+                        cb3 = 0;
+                        ++tap_r3;
+                    }
+                    if (++stage == kStages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+            }
+            if constexpr (!ROW3) for (int kb = 0; kb < p.num_k_blocks; ++kb) {
                 ptx::mbar_wait(&full_bar[stage], phase);
                 ptx::tc_fence_after();
                 if (kb == 0 && lane == 0) stamp(tile_iter, TR_MMA_FIRST);
@@ -556,14 +673,35 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         }
                     } else {
                         // coalesced write-out: 8 lanes cover one 128-byte row segment, 4 rows per instruction
-                        __nv_bfloat16* gout = p.out_bf16 + static_cast<size_t>(m_row0) * p.N + n_tile0 + c * kEpiCols;
                         const int ch = lane & 7;
+                        if constexpr (ROW3) {
+                            // padded-flat position -> output pixel; the two overhang positions of every row are dropped
+                            __nv_bfloat16* gcol = p.out_bf16 + n_tile0 + c * kEpiCols + ch * 8;
+                            int m = m_row0 + (lane >> 3);
+                            int rest = m / p.row_pitch;
+                            int q = m - rest * p.row_pitch;
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            const int row = i * 4 + (lane >> 3);
-                            const uint4 val = ptx::lds128(slab + row * 128 + ((ch ^ (row & 7)) << 4));
-                            if (m_row0 + row < p.M)
-                                *reinterpret_cast<uint4*>(gout + static_cast<size_t>(row) * p.N + ch * 8) = val;
+                            for (int i = 0; i < 8; ++i) {
+                                const int row = i * 4 + (lane >> 3);
+                                const uint4 val = ptx::lds128(slab + row * 128 + ((ch ^ (row & 7)) << 4));
+                                if (m < p.M && q < p.row_valid)
+                                    *reinterpret_cast<uint4*>(gcol + (static_cast<size_t>(rest) * p.row_valid + q) * p.N) = val;
+                                m += 4;
+                                q += 4;
+                                if (q >= p.row_pitch) {
+                                    q -= p.row_pitch;
+                                    ++rest;
+                                }
+                            }
+                        } else {
+                            __nv_bfloat16* gout = p.out_bf16 + static_cast<size_t>(m_row0) * p.N + n_tile0 + c * kEpiCols;
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                const int row = i * 4 + (lane >> 3);
+                                const uint4 val = ptx::lds128(slab + row * 128 + ((ch ^ (row & 7)) << 4));
+                                if (m_row0 + row < p.M)
+                                    *reinterpret_cast<uint4*>(gout + static_cast<size_t>(row) * p.N + ch * 8) = val;
+                            }
                         }
                         __syncwarp();
                     }

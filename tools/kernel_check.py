@@ -73,8 +73,19 @@ CASES = {
         ("p_c3_7_b5", 5, 7, 7, 512, 512, 3, 1, 1, 1, 1, 0),
         ("p_s2_14", 16, 14, 14, 1024, 2048, 1, 2, 0, 0, 0, 0),
     ],
+    # row-reuse mode for 3x3 / stride 1 / pad 1 (A_ROW3): rows straddling tiles and images, partial last tiles
+    "row3": [
+        ("r3_56_c64", 2, 56, 56, 64, 64, 3, 1, 1, 0, 1, 0),
+        ("r3_28_c128", 3, 28, 28, 128, 128, 3, 1, 1, 0, 1, 0),
+        ("r3_14_c256", 5, 14, 14, 256, 256, 3, 1, 1, 0, 1, 0),
+        ("r3_7_c512", 5, 7, 7, 512, 512, 3, 1, 1, 0, 0, 0),
+        ("r3_56_b32", 32, 56, 56, 64, 64, 3, 1, 1, 0, 1, 0),
+        ("r3_28_b16", 16, 28, 28, 128, 128, 3, 1, 1, 0, 1, 0),
+        ("r3_rect", 3, 20, 36, 64, 128, 3, 1, 1, 0, 1, 0),
+        ("r3_b1", 1, 14, 14, 64, 64, 3, 1, 1, 0, 0, 0),
+    ],
 }
-MODE = {"tiled": 0, "im2col": 1, "gather": 2, "pair_tiled": 0, "pair_im2col": 1}
+MODE = {"tiled": 0, "im2col": 1, "gather": 2, "pair_tiled": 0, "pair_im2col": 1, "row3": 3}
 
 
 def run_group(group: str) -> int:
@@ -279,7 +290,7 @@ def main() -> int:
     if args.group:
         return run_group(args.group)
     rc_all = 0
-    groups = os.environ.get("KC_GROUPS", "tiled,im2col,gather,pair_tiled,pair_im2col,perf").split(",")
+    groups = os.environ.get("KC_GROUPS", "tiled,im2col,gather,pair_tiled,pair_im2col,row3,perf").split(",")
     for g in groups:
         t0 = time.time()
         p = subprocess.run([sys.executable, os.path.abspath(__file__), "--group", g], timeout=600)
