@@ -51,6 +51,13 @@ CONV_CASES = [
     (2, 224, 224, 8, 64, 7, 2, 3, False, True, 2),     # stem, channel-padded input
     (2, 20, 20, 24, 64, 3, 1, 1, True, True, 2),       # software gather, Cin not a multiple of 64
     (2, 14, 14, 64, 64, 3, 1, 1, False, True, 2),      # gather vs im2col on the same case
+    (3, 28, 28, 128, 128, 3, 1, 1, False, True, 3),    # row reuse (A_ROW3) on CTA pairs, rows straddle tiles
+    (6, 56, 56, 64, 64, 3, 1, 1, False, True, 3),      # row reuse, 64-wide tiles, resident B (> 148 tiles)
+    (5, 14, 14, 256, 256, 3, 1, 1, False, False, 3),   # row reuse on a narrow map, ragged last tile
+    (1, 7, 7, 512, 512, 3, 1, 1, False, True, 3),      # row reuse, one image smaller than a tile
+    (16, 14, 14, 256, 256, 3, 1, 1, False, True, -1),  # auto: tensor-bound 3x3 -> im2col on CTA pairs
+    (8, 28, 28, 128, 512, 1, 1, 0, True, True, -1),    # auto: 1x1 + residual, slabs used in place
+    (7, 56, 56, 256, 64, 1, 1, 0, False, True, -1),    # auto: single n-tile, resident B (172 tiles)
 ]
 
 
