@@ -333,8 +333,10 @@ int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const vo
     int bn = block_n_req > 0 ? block_n_req : (g_force_block_n > 0 ? g_force_block_n : 0);
     // 0: never, 1 (default): tensor-bound layers run on CTA pairs, 2: every eligible layer (tests)
     const int pair_env = env_int("ADAPT_PAIR", 1);
+    // (memory-bound class: pairs only pay where the operand ring is the shallow part -- residual layers with
+    // K >= 256, whose 24 KiB pair stages fit 5 deep next to the residual ring instead of 3: -5 % measured)
     const bool pair_ok = a_mode != adapt::A_GATHER && !out_f32 && env_int("ADAPT_EPI_MODE", 1) != 0 && p.m_tiles >= 2 &&
-                         (pair_env == 2 || (pair_env == 1 && !memory_bound));
+                         (pair_env == 2 || (pair_env == 1 && (!memory_bound || (residual != nullptr && K >= 256))));
     if (bn == 0) bn = memory_bound ? (g.Cout >= 128 ? 128 : 64) : pick_block_n(p.m_tiles, g.Cout, num_sms, pair_ok);
     if (row3) {
         // a row-reuse stage holds three B tiles: 128-wide tiles on CTA pairs (8 KiB per tile and CTA), or
@@ -455,7 +457,8 @@ int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const vo
     const bool has_res = residual != nullptr && p.epi_tma != 0;
     int stages, d_out, d_res;
     if (memory_bound) {
-        stages = p.num_k_blocks < 3 ? 3 : (p.num_k_blocks > 4 ? 4 : p.num_k_blocks);
+        stages = env_int("ADAPT_MB_STAGE_CAP", 0) ? (p.num_k_blocks < 3 ? 3 : (p.num_k_blocks > 4 ? 4 : p.num_k_blocks))
+                                                  : adapt::kMaxStages;  // whatever fits after the epilogue rings
         d_out = has_res ? 0 : 2;
         d_res = has_res ? 4 : 0;
     } else {

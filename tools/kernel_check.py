@@ -169,6 +169,7 @@ def run_perf() -> int:
         ("conv5_1x1_512_2048", 7, 7, 512, 2048, 1, 1, 0),
         ("conv3_s2_256_128", 56, 56, 256, 128, 1, 2, 0),
         ("stem_gather", 224, 224, 8, 64, 7, 2, 3),
+        ("stem_s2d", 115, 115, 16, 64, 4, 1, 0),
         ("conv2_3_res", 56, 56, 64, 256, 1, 1, 0, 1),
         ("conv3_3_res", 28, 28, 128, 512, 1, 1, 0, 1),
         ("conv4_3_res", 14, 14, 256, 1024, 1, 1, 0, 1),
