@@ -122,10 +122,17 @@ class ClockSampler:
         return {"sm_mhz": statistics.median(busy), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def part_at_for(model, n: int):
+def part_at_for(model, n: int, cuts: str = "balanced"):
+    """Cut points of the N-stage bench line.  "balanced" (default): the time-balanced partition the dispatcher
+    computes from its roofline cost model; "config": the split points BASELINE.json's configs 2 and 3 name for 2 and
+    4 stages (block-group boundaries, unbalanced -- they are parity-test cases, tests/test_defer_gpu.py)."""
     from adapt_b200.dispatcher import balanced_part_at
 
-    return CONFIG_PART_AT.get(n) if n in CONFIG_PART_AT else balanced_part_at(model, n)
+    if n == 1:
+        return []
+    if cuts == "config" and n in CONFIG_PART_AT:
+        return CONFIG_PART_AT[n]
+    return balanced_part_at(model, n)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -138,7 +145,7 @@ def run_reference(args) -> int:
 
     model = adapt_b200.ResNet50(weights=None)
     weights = {l.name: l.get_weights() for l in model.layers if l.get_weights()}
-    part_at = part_at_for(model, args.gpus)
+    part_at = part_at_for(model, args.gpus, args.cuts)
     sample = args.ref_batch
     r = time_cpu_pipeline(weights, part_at, sample, args.steps, args.warmup)
     line = {
@@ -208,7 +215,7 @@ def run_ours(args) -> int:
     n = args.gpus
     B = args.batch
     model = adapt_b200.ResNet50(weights=None)
-    part_at = part_at_for(model, n)
+    part_at = part_at_for(model, n, args.cuts)
 
     if world > 1 and rank > 0:
         Node(model, device=local_rank).run()      # worker role: blocks until the dispatcher shuts down
@@ -364,6 +371,8 @@ def main() -> int:
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=128, help="micro-batch (images per step)")
+    ap.add_argument("--cuts", choices=["balanced", "config"], default="balanced",
+                    help="N>1: time-balanced cut points (default) or the split points BASELINE.json names for N=2/4")
     ap.add_argument("--ref-batch", type=int, default=32, help="micro-batch of the CPU reference sample")
     ap.add_argument("--cpu-steps", type=int, default=48, help="micro-batches of the cpu_baseline sample (10-30 s of CPU work)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
