@@ -11,16 +11,20 @@
 //   acc: fp32 in TMEM (tcgen05.mma kind::f16), epilogue in fp32, output bf16 (or fp32)
 //
 // Structure: persistent CTAs (one per SM), warp-specialised:
-//   warp 0      TMA producer   (A tile: tiled 2-D box, or im2col box; B tile: tiled 2-D box)
-//   warp 1      MMA issuer     (one elected lane issues tcgen05.mma; owns the TMEM allocation)
-//   warps 2..5  epilogue       (tcgen05.ld -> scale/bias/residual/ReLU -> bf16 -> smem slab -> TMA store;
-//                               the residual arrives through a per-warp TMA ring that prefetches
-//                               across tile boundaries)
-//   warps 6..9  (A_GATHER only) software im2col producers for thin-channel inputs (the stem)
-// Three pipelines: smem full/empty ring (TMA <-> MMA), TMEM full/empty double buffer
-// (MMA <-> epilogue), and a static round-robin tile schedule.  The shared-memory budget is split
-// at launch time between operand stages and epilogue staging (ConvGemmParams::stages/d_out/d_res):
-// HBM-bound layers want many bytes of residual/output in flight, tensor-bound layers want stages.
+//   warp 0        TMA producer (A: tiled 2-D box, im2col box, or a padded-flat row segment that serves the three
+//                 horizontal taps of a 3x3 filter row (A_ROW3); B: tiled 2-D box, optionally resident)
+//   warp 1        MMA issuer   (one elected lane issues tcgen05.mma; owns the TMEM allocation; in CTA-pair mode
+//                 only the leader CTA issues, for both)
+//   warps 2..9    epilogue, two groups of four: group g drains TMEM accumulator stage g
+//                 (tcgen05.ld -> scale/bias(/residual) -> cvt[.relu].bf16x2 -> 4 KiB smem slab -> TMA store;
+//                 with a residual the slab is used in place, filled by a per-warp TMA prefetch that runs ahead
+//                 across tile boundaries)
+//   warps 10..13  (A_GATHER only) software im2col producers for thin-channel inputs (odd stem cuts)
+// Three pipelines: smem full/empty ring (TMA <-> MMA), TMEM full/empty double buffer (MMA <-> epilogue), and a
+// static round-robin tile schedule.  The shared-memory budget is split at launch time between operand stages and
+// epilogue slabs (ConvGemmParams::stages/d_out/d_res/b_resident).  Launched with programmatic stream
+// serialization: the prologue overlaps the previous layer's tail, griddepcontrol.wait precedes the first access
+// to activations.
 #pragma once
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>

@@ -1,5 +1,5 @@
 cd /root/repo
-for i in 1 2; do
-ADAPT_MB_STAGE_CAP=1 timeout 300 python tools/kernel_check.py --group perf > gpurun_out/cap1_$i.log 2>&1
-ADAPT_MB_STAGE_CAP=0 timeout 300 python tools/kernel_check.py --group perf > gpurun_out/cap0_$i.log 2>&1
-done
+for p in 1 2; do for bn in 128 256; do
+echo "== pair=$p bn=$bn"
+ADAPT_PAIR=$p KC_BN=$bn KC_ONLY=conv4_1x1 timeout 300 python tools/kernel_check.py --group trace 2>&1 | grep grid | cut -c1-400
+done; done
