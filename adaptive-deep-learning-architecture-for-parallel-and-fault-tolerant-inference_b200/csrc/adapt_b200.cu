@@ -641,7 +641,13 @@ struct adapt_stage {
     bool use_graph = true;
     std::vector<WeightDev> weights;
     std::vector<adapt_tensor_desc> tdesc;
-    std::vector<void*> tptr;
+    std::vector<void*> tptr;  // internal tensors: sub-ranges of `arena`
+    // One block for all internal activation tensors of the installed program.  It only ever grows, so a
+    // re-slice to a program that fits (every re-slice, when the stage was created with its largest program)
+    // allocates nothing: cudaMalloc / cudaFree synchronise the device and, with peer access enabled, re-map the
+    // block into every peer, which is what a fail-over must not wait for.
+    void* arena = nullptr;
+    size_t arena_bytes = 0;
     std::vector<adapt_op_desc> ops;
     void* io_in[2] = {nullptr, nullptr};
     void* io_out[2] = {nullptr, nullptr};
@@ -662,11 +668,14 @@ void drop_plans(adapt_stage* st) {
     st->plans.clear();
 }
 
-void free_tensors(adapt_stage* st) {
-    for (void* p : st->tptr)
-        if (p) cudaFree(p);
+void free_tensors(adapt_stage* st, bool release_arena) {
     st->tptr.clear();
     st->tdesc.clear();
+    if (release_arena && st->arena) {
+        cudaFree(st->arena);
+        st->arena = nullptr;
+        st->arena_bytes = 0;
+    }
 }
 
 int install_program(adapt_stage* st, const adapt_tensor_desc* tensors, int n_tensors, const adapt_op_desc* ops,
@@ -703,15 +712,26 @@ int install_program(adapt_stage* st, const adapt_tensor_desc* tensors, int n_ten
         }
     }
     drop_plans(st);
-    free_tensors(st);
-    st->tdesc.assign(tensors, tensors + n_tensors);
-    st->tptr.assign(n_tensors, nullptr);
-    st->ops.assign(ops, ops + n_ops);
+    free_tensors(st, false);
+    constexpr size_t kAlign = 1024;  // (TMA needs 16 B; whole swizzle atoms keep the boxes of different tensors apart)
+    size_t need = 0;
+    std::vector<size_t> offs(n_tensors, 0);
     for (int i = 0; i < n_tensors; ++i) {
         if (tensors[i].role != ADAPT_T_INTERNAL) continue;
         const size_t bytes = (size_t)tensors[i].elems_per_image * st->max_batch * elem_size(st, tensors[i].dtype);
-        CUDA_TRY(cudaMalloc(&st->tptr[i], bytes));
+        offs[i] = need;
+        need += (bytes + kAlign - 1) / kAlign * kAlign;
     }
+    if (need > st->arena_bytes) {
+        free_tensors(st, true);
+        CUDA_TRY(cudaMalloc(&st->arena, need));
+        st->arena_bytes = need;
+    }
+    st->tdesc.assign(tensors, tensors + n_tensors);
+    st->tptr.assign(n_tensors, nullptr);
+    st->ops.assign(ops, ops + n_ops);
+    for (int i = 0; i < n_tensors; ++i)
+        if (tensors[i].role == ADAPT_T_INTERNAL) st->tptr[i] = static_cast<uint8_t*>(st->arena) + offs[i];
     return ADAPT_OK;
 }
 
@@ -1106,7 +1126,7 @@ void adapt_stage_destroy(adapt_stage_t* st) {
     if (cudaSetDevice(st->device) == cudaSuccess) {
         cudaDeviceSynchronize();
         drop_plans(st);
-        free_tensors(st);
+        free_tensors(st, true);
         for (WeightDev& w : st->weights) {
             if (w.kernel) cudaFree(w.kernel);
             if (w.scale) cudaFree(w.scale);

@@ -150,7 +150,7 @@ class ResidentBatch:
 class DEFER:
     def __init__(self, computeNodes, mode: str = "bf16", max_batch: int = 128, heartbeat_timeout: float = 0.05,
                  max_inflight: Optional[int] = None, backend_factory=None, warm_batches: Sequence[int] = (),
-                 silent_kill: bool = True, handoff: str = "auto") -> None:
+                 silent_kill: bool = True, handoff: str = "auto", ingest_rails: str = "auto") -> None:
         self.computeNodes = computeNodes
         self.dispatchIP = self.get_local_ip()
         self.chunk_size = 512 * 1000
@@ -168,6 +168,12 @@ class DEFER:
         if handoff not in ("auto", "direct", "copy"):
             raise ValueError("handoff must be 'auto', 'direct' or 'copy'")
         self.handoff = handoff
+        # host -> first stage ingest: "auto" = pinned input batches are spread round-robin over the PCIe links
+        # of ALL the pipeline's GPUs (H2D into a staging buffer on GPU j, then one NVLink copy into the first
+        # stage's input slot), because one x16 link carries only ~91 k fp32 images/s; "off" = first stage's link only
+        if ingest_rails not in ("auto", "off"):
+            raise ValueError("ingest_rails must be 'auto' or 'off'")
+        self.ingest_rails = ingest_rails
         # -- runtime state
         self._shutdown_event = threading.Event()
         self.inflight_lock = threading.Lock()
@@ -253,7 +259,7 @@ class DEFER:
         h = self.health
         epoch = h.epoch + 1
         h.write_table({"epoch": epoch, "order": order, "part_at": part_at, "warm_batches": self.warm_batches,
-                       "handoff": self.handoff})
+                       "handoff": self.handoff, "ingest_rails": self.ingest_rails})
         h.g[G_EPOCH] = epoch
         active = list(order)
         t_start = time.perf_counter()

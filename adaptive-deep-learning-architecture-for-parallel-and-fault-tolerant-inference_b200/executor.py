@@ -25,7 +25,10 @@ def elem_bytes(dtype: int, mode: int) -> int:
 
 
 class StageExecutor:
-    def __init__(self, model: Model, part: PartModel, device: int = 0, mode: str = "bf16", max_batch: int = 128):
+    def __init__(self, model: Model, part: PartModel, device: int = 0, mode: str = "bf16", max_batch: int = 128,
+                 reserve_full: bool = False):
+        """`reserve_full`: size the stage's activation arena for the WHOLE model before installing `part`, so that
+        no later re-slice (a fail-over hands this stage more layers) has to allocate device memory."""
         N.require_gpu()
         self.lib = N.lib()
         self.model = model
@@ -34,8 +37,13 @@ class StageExecutor:
         self.max_batch = int(max_batch)
         self.entries, self.windex = build_weight_table(model)
         self._keepalive = self.entries  # host arrays must outlive adapt_stage_create
-        self.part = part
-        self.program: StageProgram = compile_part(part, self.windex, self.mode)
+        whole = None
+        if reserve_full and len(part.layer_names) < len(model.layers) - 1:
+            from .dag_util import construct_model
+
+            whole = construct_model(model, model.layers[0].name, model.layers[-1].name, "whole")
+        self.part = whole or part
+        self.program: StageProgram = compile_part(self.part, self.windex, self.mode)
         w = (N.WeightDesc * len(self.entries))()
         for i, e in enumerate(self.entries):
             kh, kw, cin, cout = e.geom
@@ -46,6 +54,8 @@ class StageExecutor:
         N.check(self.lib.adapt_stage_create(self.device, self.mode, self.max_batch, w, len(self.entries), t, len(t), o,
                                             len(o), C.byref(handle)))
         self.handle = handle
+        if whole is not None:
+            self.reslice(part)
 
     # ---- program / geometry ---------------------------------------------------------------------
     def reslice(self, part: PartModel) -> None:

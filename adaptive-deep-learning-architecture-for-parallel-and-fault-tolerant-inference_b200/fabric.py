@@ -325,7 +325,7 @@ class CudaBackend:
     def make_executor(self, model, part, mode: str, max_batch: int):
         from .executor import StageExecutor
 
-        return StageExecutor(model, part, device=self.device, mode=mode, max_batch=max_batch)
+        return StageExecutor(model, part, device=self.device, mode=mode, max_batch=max_batch, reserve_full=True)
 
     def close(self) -> None:
         for a in self._registered:

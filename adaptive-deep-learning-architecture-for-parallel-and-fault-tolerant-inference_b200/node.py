@@ -17,6 +17,7 @@ from __future__ import annotations
 
 import ctypes
 import os
+import sys
 import threading
 import time
 import traceback
@@ -114,6 +115,8 @@ class StageWorker:
         self._timing_events = None
         self._timing_armed = False
         self.handoff_copy = False
+        self.rails: List[dict] = []          # ingest rails ever created (other GPUs' PCIe links)
+        self._active_rails: List[dict] = []  # ... of the GPUs in the current stage order
         self.on_kill: Optional[Callable[[], None]] = None
         if hasattr(self.backend, "abort_check"):  # synchronous test backends must be able to give up a wait
             self.backend.abort_check = lambda: (self.health.phase != PHASE_RUN or bool(self.health.w[self.wid, W_KILL])
@@ -182,7 +185,8 @@ class StageWorker:
         while True:
             self._write_own_flags(POISON)
             if not (self.backend.busy(self.copy_stream) or self.backend.busy(self.stream)
-                    or self.backend.busy(self.xfer_stream)):
+                    or self.backend.busy(self.xfer_stream)
+                    or any(r["backend"].busy(r["stream"]) for r in getattr(self, "rails", []))):
                 return
             if time.monotonic() - t0 > 20:
                 raise TimeoutError("stage streams did not drain")
@@ -225,8 +229,37 @@ class StageWorker:
                 self.executor.bind_io(s, self.in_buf(self.wid, s), out_ptr)
             if table.get("warm_batches"):
                 self._warm(table["warm_batches"])
+        self._setup_rails(order, table)
         self.epoch = epoch
         self.health.w[self.wid, W_ACK_READY] = epoch
+
+    def _setup_rails(self, order: List[int], table: dict) -> None:
+        """Ingest rails of the first stage: one (context, stream, 2 staging buffers) per OTHER GPU of the
+        pipeline.  A pinned input batch k goes host -> GPU j over GPU j's own PCIe link, then over NVLink into
+        this stage's input slot; rail 0 is this GPU's own link.  Rails are created once and re-used across
+        reconfigurations; only the GPUs of the current stage order are active."""
+        self._active_rails = []
+        if (table.get("ingest_rails", "auto") != "auto" or getattr(self.backend, "name", "") != "cuda"
+                or self.stage_index != 0 or len(order) < 2):
+            return
+        have = {r["device"]: r for r in self.rails}
+        nbytes = self.max_batch * self.session["in_row_bytes"]
+        for w in order:
+            d = int(self.health.w[w, W_DEVICE])
+            if w == self.wid or d == self.device or any(r["device"] == d for r in self._active_rails):
+                continue
+            r = have.get(d)
+            if r is None:
+                try:
+                    rb = CudaBackend(d)
+                    rb.peer_enable(self.device)
+                    r = {"device": d, "backend": rb, "stream": rb.new_stream(),
+                         "staging": [rb.alloc(nbytes), rb.alloc(nbytes)], "count": 0}
+                except Exception as e:  # noqa: BLE001  (no peer access / no memory: that GPU is simply not a rail)
+                    print(f"[adapt] worker {self.wid}: GPU {d} not usable as an ingest rail: {e}", file=sys.stderr)
+                    continue
+                self.rails.append(r)
+            self._active_rails.append(r)
 
     def _warm(self, batches) -> None:
         """Build launch records + graphs for the batch sizes the dispatcher announces, so the
@@ -268,10 +301,25 @@ class StageWorker:
                     time.sleep(20e-6)
                 ctypes.memmove(self.stage_addr[s], aux, nbytes)
                 src = self.stage_addr[s]
-            if k >= 2:
-                b.wait_flag(self.copy_stream, self.flag(self.wid, F_IN_CONSUMED + s), k - 1)
-            b.h2d(self.in_buf(self.wid, s), src, nbytes, self.copy_stream)
-            b.write_flag(self.copy_stream, self.flag(self.wid, F_H2D_DONE + s), k + 1)
+            rails = self._active_rails if (kind & KIND_PINNED) else []
+            lane = k % (len(rails) + 1)
+            if lane == 0:
+                if k >= 2:
+                    b.wait_flag(self.copy_stream, self.flag(self.wid, F_IN_CONSUMED + s), k - 1)
+                b.h2d(self.in_buf(self.wid, s), src, nbytes, self.copy_stream)
+                b.write_flag(self.copy_stream, self.flag(self.wid, F_H2D_DONE + s), k + 1)
+            else:
+                # over GPU j's PCIe link into its staging buffer (no dependency: runs ahead), then -- once this
+                # stage has consumed what the slot held -- one NVLink copy into the input slot
+                rail = rails[lane - 1]
+                rb, rs = rail["backend"], rail["stream"]
+                stg = rail["staging"][rail["count"] & 1]
+                rail["count"] += 1
+                rb.h2d(stg, src, nbytes, rs)
+                if k >= 2:
+                    rb.wait_flag(rs, self.flag(self.wid, F_IN_CONSUMED + s), k - 1)
+                rb.d2d(self.in_buf(self.wid, s), stg, nbytes, rs)
+                rb.write_flag(rs, self.flag(self.wid, F_H2D_DONE + s), k + 1)
             b.wait_flag(self.stream, self.flag(self.wid, F_H2D_DONE + s), k + 1)
         else:
             b.wait_flag(self.stream, self.flag(self.wid, F_IN_READY + s), k + 1)

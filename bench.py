@@ -172,6 +172,29 @@ def workload_name(n: int, batch: int, part_at) -> str:
 
 
 # ---------------------------------------------------------------------------------------------
+def drive_steady(defer, in_q, out_q, items, warm, timeout=60.0):
+    """Feed `items` back to back; returns (results, seconds between the arrival of result `warm` - 1 and the last
+    one), i.e. the steady-state time of the last len(items) - warm steps with the pipeline kept full -- every one of
+    those steps has its host->device copy and its device->host result read inside the region -- and the wall time
+    of the whole drive (fill and drain included) for reference."""
+    timeout = float(os.environ.get("ADAPT_BENCH_DRIVE_TIMEOUT_S", timeout))
+    t = threading.Thread(target=lambda: [in_q.put(x) for x in items], daemon=True)
+    t0 = time.perf_counter()
+    t.start()
+    outs, stamps = [], []
+    while len(outs) < len(items):
+        try:
+            outs.append(out_q.get(timeout=0.5))
+            stamps.append(time.perf_counter())
+        except queue.Empty:
+            if defer.error:
+                raise RuntimeError(defer.error)
+            if time.perf_counter() - t0 > timeout:
+                raise TimeoutError(f"bench: {len(outs)}/{len(items)} results; {defer.debug_state()}")
+    t.join()
+    return outs, stamps[-1] - stamps[warm - 1], stamps[-1] - t0
+
+
 def drive(defer, in_q, out_q, items, timeout=60.0):
     """Feed `items` and collect as many results; returns (results, wall seconds)."""
     timeout = float(os.environ.get("ADAPT_BENCH_DRIVE_TIMEOUT_S", timeout))  # (profiler runs need minutes per step)
@@ -228,7 +251,7 @@ def run_ours(args) -> int:
     # window: profiling runs widen it with ADAPT_HEARTBEAT_TIMEOUT_S; numbers are never taken from those runs)
     defer = DEFER(devices, mode="bf16", max_batch=B, warm_batches=[B],
                   heartbeat_timeout=float(os.environ.get("ADAPT_HEARTBEAT_TIMEOUT_S", "0.05")),
-                  max_inflight=max(2 * n + 4, 12))
+                  max_inflight=max(2 * n + 4, 12), ingest_rails=args.ingest_rails)
     in_q, out_q = queue.Queue(2 * n + 8), queue.Queue()
     th = threading.Thread(target=defer.run_defer, args=(model, part_at, in_q, out_q), daemon=True)
     th.start()
@@ -258,9 +281,10 @@ def run_ours(args) -> int:
 
     # ---------------- leg 2: end to end through the public API, pinned host inputs ----------------
     pinned = [torch.from_numpy(x).pin_memory() for _ in range(3)]
-    drive(defer, in_q, out_q, [pinned[i % 3] for i in range(W)])
+    # W warm-up items and K timed items flow back to back: the timed region starts when the last warm-up result
+    # arrives (pipeline full) and ends with the K-th timed result
     defer.latencies_ms.clear()
-    e2e_outs, e2e_wall = drive(defer, in_q, out_q, [pinned[i % 3] for i in range(K)])
+    e2e_outs, e2e_wall, e2e_wall_all = drive_steady(defer, in_q, out_q, [pinned[i % 3] for i in range(W + K)], W)
     e2e_value = K * B / e2e_wall
     clock_info = clocks.stop()
     lat = sorted(defer.latencies_ms)
@@ -301,15 +325,18 @@ def run_ours(args) -> int:
     # ---------------- fail-over leg (needs a stage to lose) ----------------
     failover = None
     if n >= 2 and not args.no_failover:
-        pre = [pinned[i % 3] for i in range(3 * n)]
-        t = threading.Thread(target=lambda: [in_q.put(p) for p in pre + pre], daemon=True)
+        # BASELINE config 5: the kill lands mid-stream, after >= 100 micro-batches, with more queued behind it than
+        # the pipeline can hold in flight (otherwise every result may already be out when the stage dies)
+        n_before, n_after = 100, 6 * n + 40
+        items = [pinned[i % 3] for i in range(n_before + n_after)]
+        t = threading.Thread(target=lambda: [in_q.put(p) for p in items], daemon=True)
         t.start()
         got = 0
         t_kill = None
-        while got < 2 * len(pre):
+        while got < len(items):
             out_q.get(timeout=120)
             got += 1
-            if got == len(pre) // 2 and t_kill is None:
+            if got == n_before and t_kill is None:
                 defer.inject_kill(n // 2)
                 t_kill = time.perf_counter()
         t.join()
@@ -318,7 +345,8 @@ def run_ours(args) -> int:
                     "detect_ms": defer.stats.get("detect_ms", [None])[-1],
                     "phases_ms": defer.stats.get("reconfig_phases_ms", [None])[-1],
                     "reconfig_ms": defer.stats.get("reconfig_ms", [None])[-1], "replayed": defer.stats["replayed"],
-                    "delivered_exactly_once": got == 2 * len(pre) and out_q.empty(), "stages_after": len(defer.order)}
+                    "delivered_exactly_once": got == len(items) and out_q.empty(), "stages_after": len(defer.order),
+                    "killed_after_micro_batches": n_before}
 
     from adapt_b200.dag_util import build_weight_table, compile_part
 
@@ -350,7 +378,12 @@ def run_ours(args) -> int:
         "clocks": clock_info,
         "e2e": {"value": round(e2e_value, 1), "unit": "img/s", "h2d_bytes_per_step": int(x.nbytes),
                 "d2h_bytes_per_step": B * 1000 * 4, "p50_latency_ms": p50_unloaded, "p50_latency_ms_saturated": p50, "p99_latency_ms_saturated": p99,
-                "timing": "wall clock around K queue items"},
+                "value_incl_fill_and_drain": round((W + K) * B / e2e_wall_all, 1),
+                "ingest": ("round-robin over the PCIe links of all %d GPUs, then NVLink into stage 1" % n)
+                          if n > 1 and args.ingest_rails == "auto" else "the first stage's own PCIe link",
+                "timing": "wall clock from the arrival of the last warm-up result to the arrival of the K-th timed "
+                          "result, W + K pinned host batches fed back to back (pipeline full); "
+                          "value_incl_fill_and_drain = (W + K) batches over the whole drive"},
         "gpu_launches": int(launches_per_step * K),
         "roofline": roofline,
         "cpu_baseline": cpu,
@@ -375,6 +408,8 @@ def main() -> int:
                     help="N>1: time-balanced cut points (default) or the split points BASELINE.json names for N=2/4")
     ap.add_argument("--ref-batch", type=int, default=32, help="micro-batch of the CPU reference sample")
     ap.add_argument("--cpu-steps", type=int, default=48, help="micro-batches of the cpu_baseline sample (10-30 s of CPU work)")
+    ap.add_argument("--ingest-rails", choices=["auto", "off"], default="auto",
+                    help="N>1: spread pinned input batches over every GPU's PCIe link (auto) or use the first stage's only")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-failover", action="store_true")
     ap.add_argument("--dump-ops", default=None, help="write the per-launch timing table (JSON) here")

@@ -1,5 +1,9 @@
 cd /root/repo
-python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/smoke.log
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/gpu_tests.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/gpu_tests.log
-KC_GROUPS=row3 timeout 600 compute-sanitizer --tool memcheck --error-exitcode 7 python tools/kernel_check.py --group row3 > gpurun_out/san_row3.log 2>&1; echo "memcheck row3 rc=$?"; tail -4 gpurun_out/san_row3.log
-timeout 600 compute-sanitizer --tool memcheck --error-exitcode 7 python tools/kernel_check.py --group pair_im2col > gpurun_out/san_pair.log 2>&1; echo "memcheck pair rc=$?"; tail -4 gpurun_out/san_pair.log
+for m in off auto auto; do
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 30 --warmup 5 --no-cpu-baseline --ingest-rails $m > gpurun_out/b2_$m.json 2> gpurun_out/b2_$m.err
+python - <<PY
+import json
+d=json.loads(open("gpurun_out/b2_$m.json").read().strip().splitlines()[-1])
+print("$m", d["value"], d["e2e"]["value"], d["failover"])
+PY
+done
