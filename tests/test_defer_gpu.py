@@ -109,6 +109,25 @@ def test_pinned_torch_inputs(pkg, model50):
     _check(model50, xs, outs)
 
 
+def test_ingest_rails_across_gpus(pkg, model50):
+    """Pinned inputs spread over every GPU's PCIe link (node.StageWorker._setup_rails): every batch distinct, so a
+    batch landing in the wrong slot or overtaking another shows up as a wrong row; a stage dies mid-stream."""
+    torch = pytest.importorskip("torch")
+    if _ngpu() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    from adapt_b200.dispatcher import DEFER, balanced_part_at
+
+    n = min(_ngpu(), 4)
+    xs = [KO.synthetic_images(3, seed=700 + i, kind="normal") for i in range(30)]
+    pinned = [torch.from_numpy(x).pin_memory() for x in xs]
+    defer = DEFER([f"cuda:{i}" for i in range(n)], max_batch=3, heartbeat_timeout=0.05, ingest_rails="auto")
+    outs, stats, _ = _run(defer, model50, balanced_part_at(model50, n), pinned, kill_after=12, kill_stage=n - 1)
+    assert stats["failovers"] == 1 and stats["delivered"] == 30
+    _check(model50, xs, outs)
+    with pytest.raises(ValueError):
+        DEFER(["cuda:0"], ingest_rails="sometimes")
+
+
 def test_failover_resliced_and_replayed(pkg, model50):
     from adapt_b200.dispatcher import DEFER
 
