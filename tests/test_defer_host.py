@@ -143,3 +143,54 @@ def test_too_few_compute_nodes(pkg, model50):
     d = DEFER([0], backend_factory=HostBackend)
     with pytest.raises(ValueError):
         d.run_defer(model50, ["conv3_block4_out"], queue.Queue(), queue.Queue())
+
+
+def test_constructor_options_are_validated_and_published(pkg, model50):
+    """Build-specific DEFER options: bad values fail loudly; the hand-off / ingest choices reach the workers through
+    the partition table (host backends have no PCIe rails: the option must be harmless there)."""
+    from adapt_b200.dispatcher import DEFER
+
+    with pytest.raises(ValueError):
+        DEFER([0], handoff="teleport", backend_factory=HostBackend)
+    with pytest.raises(ValueError):
+        DEFER([0], ingest_rails="sometimes", backend_factory=HostBackend)
+    d = DEFER([0, 1], mode="fp32", max_batch=1, backend_factory=HostBackend, heartbeat_timeout=5.0, handoff="copy",
+              ingest_rails="auto")
+    inputs = [KO.synthetic_images(1, seed=900 + i, kind="normal") for i in range(3)]
+    in_q, out_q = queue.Queue(10), queue.Queue()
+    import threading
+
+    t = threading.Thread(target=d.run_defer, args=(model50, ["conv3_block4_out"], in_q, out_q), daemon=True)
+    t.start()
+    d.wait_ready(60)
+    table = d.health.read_table()
+    assert table["handoff"] == "copy" and table["ingest_rails"] == "auto" and table["part_at"] == ["conv3_block4_out"]
+    assert all(not getattr(w, "_active_rails", []) for w in d.workers)
+    for x in inputs:
+        in_q.put(x)
+    outs = [out_q.get(timeout=60) for _ in inputs]
+    d.shutdown()
+    t.join(30)
+    o = oracle_for(model50)
+    for x, y in zip(inputs, outs):
+        np.testing.assert_allclose(y, o.predict(x)[0], rtol=1e-5, atol=1e-7)
+
+
+def test_bench_cut_selection(pkg, model50):
+    """bench.py: N = 1 is the single chunk; N > 1 defaults to the time-balanced cuts, `--cuts config` to the split
+    points BASELINE.json names for 2 and 4 stages; every choice is a valid partition."""
+    import importlib.util
+    import os
+
+    from adapt_b200.dag_util import valid_cut_points
+
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(os.path.dirname(os.path.dirname(__file__)), "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    assert bench.part_at_for(model50, 1) == [] and bench.part_at_for(model50, 1, "config") == []
+    assert bench.part_at_for(model50, 2, "config") == ["conv3_block4_out"]
+    assert bench.part_at_for(model50, 4, "config") == ["conv2_block3_out", "conv3_block4_out", "conv4_block6_out"]
+    valid = set(valid_cut_points(model50))
+    for n in (2, 3, 4, 8):
+        cuts = bench.part_at_for(model50, n)
+        assert len(cuts) == n - 1 and all(c in valid for c in cuts), cuts
