@@ -225,25 +225,29 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     };
     if (threadIdx.x == 0) stamp(0, TR_CTA_START);
 
-    if (warp_idx == 0 && lane == 0) {
+    if (warp_idx == 0) {
+        // 84 mbarriers, initialised by the 32 lanes in parallel
+        constexpr uint32_t full_count = (A_MODE == A_GATHER) ? (1 + 128) : 1;
+        constexpr int kNumBars = 2 * kMaxStages + 4 + kEpiWarps * kMaxRes;
+        for (int i = lane; i < kNumBars; i += 32) {
+            uint32_t count = 1;  // tmem_full, residual slots
+            if (i < kMaxStages)
+                count = full_count;
+            else if (i < 2 * kMaxStages)
+                count = PAIR ? 1 : CL;  // multicast: every CTA of the cluster must have drained the stage; pair: the leader's MMA commit
+            else if (i >= 2 * kMaxStages + 2 && i < 2 * kMaxStages + 4)
+                count = PAIR ? 8 : 4;  // tmem_empty: one arrive per epilogue warp (of both CTAs of a pair)
+            ptx::mbar_init(&bars[i], count);
+        }
+        ptx::fence_mbar_init();
+    } else if (warp_idx == 2 && lane == 0) {
+        // descriptor fetches start at once, on a warp that has nothing else to do yet
         if (A_MODE != A_GATHER) ptx::prefetch_tmap(&tmap_a);
         ptx::prefetch_tmap(&tmap_b);
-        constexpr uint32_t full_count = (A_MODE == A_GATHER) ? (1 + 128) : 1;
-        for (int i = 0; i < kMaxStages; ++i) {
-            ptx::mbar_init(&full_bar[i], full_count);
-            // multicast: every CTA of the cluster must have drained the stage; pair: the leader's MMA commit
-            ptx::mbar_init(&empty_bar[i], PAIR ? 1 : CL);
-        }
-        for (int i = 0; i < 2; ++i) {
-            ptx::mbar_init(&tmem_full_bar[i], 1);
-            ptx::mbar_init(&tmem_empty_bar[i], PAIR ? 8 : 4);  // one arrive per epilogue warp (of both CTAs of a pair)
-        }
-        for (int i = 0; i < kEpiWarps * kMaxRes; ++i) ptx::mbar_init(&res_bar[i], 1);
         if (p.epi_tma) {
             ptx::prefetch_tmap(&tmap_out);
             if (p.residual != nullptr) ptx::prefetch_tmap(&tmap_res);
         }
-        ptx::fence_mbar_init();
     }
     if (warp_idx == 1) {
         if (PAIR) {

@@ -1,9 +1,8 @@
 cd /root/repo
-for m in off auto auto; do
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 30 --warmup 5 --no-cpu-baseline --ingest-rails $m > gpurun_out/b2_$m.json 2> gpurun_out/b2_$m.err
-python - <<PY
+KC_GROUPS=tiled,im2col,pair_im2col,row3 timeout 600 python tools/kernel_check.py 2>&1 | grep -E "group|error|\"bad\": [1-9]"
+KC_BN=128 KC_ONLY=conv3 timeout 300 python tools/kernel_check.py --group trace 2>&1 | grep grid | cut -c1-330
+timeout 600 python bench.py --no-cpu-baseline > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err
+python - <<'PY'
 import json
-d=json.loads(open("gpurun_out/b2_$m.json").read().strip().splitlines()[-1])
-print("$m", d["value"], d["e2e"]["value"], d["failover"])
+d=json.loads(open("gpurun_out/bench_n1.json").read().strip().splitlines()[-1]); print(d["value"], d["ms_per_step"], d["e2e"]["value"])
 PY
-done
