@@ -52,8 +52,12 @@ class LayerSpec:
     out_shape: Tuple[int, ...] = ()  # per-image (H, W, C) or (C,)
 
 
-def build_resnet50_layers() -> List[LayerSpec]:
-    """Layer list in the order Keras reports for ResNet50(include_top=True) (`model.layers`)."""
+RESNET_BLOCKS = {"resnet50": (3, 4, 6, 3), "resnet101": (3, 4, 23, 3), "resnet152": (3, 8, 36, 3)}
+
+
+def build_resnet50_layers(blocks_per_stack: Tuple[int, int, int, int] = (3, 4, 6, 3)) -> List[LayerSpec]:
+    """Layer list in the order Keras reports for ResNet50(include_top=True) (`model.layers`).  The same v1 builder
+    with other stack depths gives Keras' ResNet101 (3, 4, 23, 3) and ResNet152 (3, 8, 36, 3)."""
     L: List[LayerSpec] = []
     L.append(LayerSpec("input_1", "InputLayer", [], out_shape=(224, 224, 3)))
     L.append(LayerSpec("conv1_pad", "ZeroPadding2D", ["input_1"], pad=3))
@@ -63,8 +67,9 @@ def build_resnet50_layers() -> List[LayerSpec]:
     L.append(LayerSpec("pool1_pad", "ZeroPadding2D", ["conv1_relu"], pad=1))
     L.append(LayerSpec("pool1_pool", "MaxPooling2D", ["pool1_pad"], kernel=3, stride=2))
     prev = "pool1_pool"
-    for stack, filters, blocks, stride1 in (("conv2", 64, 3, 1), ("conv3", 128, 4, 2), ("conv4", 256, 6, 2),
-                                            ("conv5", 512, 3, 2)):
+    b2, b3, b4, b5 = blocks_per_stack
+    for stack, filters, blocks, stride1 in (("conv2", 64, b2, 1), ("conv3", 128, b3, 2), ("conv4", 256, b4, 2),
+                                            ("conv5", 512, b5, 2)):
         for b in range(1, blocks + 1):
             n = f"{stack}_block{b}"
             s = stride1 if b == 1 else 1
@@ -232,8 +237,21 @@ def bf16_round(x: np.ndarray) -> np.ndarray:
 
 # ------------------------------------------------------------------------------------ evaluation
 class ResNet50Oracle:
-    def __init__(self, weights: Optional[Dict[str, List[np.ndarray]]] = None, seed: int = 1234):
-        self.layers = build_resnet50_layers()
+    def __init__(self, weights: Optional[Dict[str, List[np.ndarray]]] = None, seed: int = 1234,
+                 blocks_per_stack: Optional[Tuple[int, int, int, int]] = None):
+        if blocks_per_stack is None:
+            # infer the depth from the weight names when weights are given (conv4_block23_1_conv => ResNet-101)
+            blocks_per_stack = (3, 4, 6, 3)
+            if weights is not None:
+                depth = [0, 0, 0, 0]
+                for name in weights:
+                    if name.startswith("conv") and "_block" in name:
+                        stack = int(name[4]) - 2
+                        if 0 <= stack < 4:
+                            depth[stack] = max(depth[stack], int(name.split("_block")[1].split("_")[0]))
+                if all(depth):
+                    blocks_per_stack = tuple(depth)
+        self.layers = build_resnet50_layers(blocks_per_stack)
         self.by_name = {l.name: l for l in self.layers}
         self.weights = weights if weights is not None else init_weights(self.layers, seed)
         self.logits: Optional[np.ndarray] = None  # pre-softmax tap of the last evaluated `predictions`

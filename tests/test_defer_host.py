@@ -194,3 +194,31 @@ def test_bench_cut_selection(pkg, model50):
     for n in (2, 3, 4, 8):
         cuts = bench.part_at_for(model50, n)
         assert len(cuts) == n - 1 and all(c in valid for c in cuts), cuts
+
+
+@pytest.mark.parametrize("ctor_name,n_params,n_layers", [("ResNet101", 44707176, 347), ("ResNet152", 60419944, 517)])
+def test_deeper_resnets_share_the_front_end(pkg, ctor_name, n_params, n_layers):
+    """`construct_model` is model-agnostic.  The Keras-compatible ResNet-101 / -152 graphs have
+    the published parameter counts, partition at the same kind of articulation points, compile to stage programs
+    and run through the DEFER pipeline (host executor) with the oracle's values."""
+    import adapt_b200
+    from adapt_b200.dag_util import build_weight_table, compile_part, construct_model, valid_cut_points
+    from adapt_b200.dispatcher import DEFER, balanced_part_at
+
+    m = getattr(adapt_b200, ctor_name)(weights=None)
+    assert len(m.layers) == n_layers and sum(int(w.size) for w in m.get_weights()) == n_params
+    cuts = valid_cut_points(m)
+    assert "conv4_block23_out" in cuts and "conv4_block23_2_relu" not in cuts
+    part_at = balanced_part_at(m, 3)
+    assert len(part_at) == 2 and all(c in cuts for c in part_at)
+    _, windex = build_weight_table(m)
+    whole = construct_model(m, m.layers[0].name, m.layers[-1].name, "whole")
+    assert len(compile_part(whole, windex, 0).ops) > 100
+    with pytest.raises(RuntimeError):
+        construct_model(m, "conv4_block23_2_relu", m.layers[-1].name, "bad")
+    if ctor_name == "ResNet152":
+        return  # (the pipeline run below is the same code path; one model keeps the CPU suite short)
+    x = KO.synthetic_images(1, seed=77, kind="normal")
+    d = DEFER([0, 1, 2], mode="fp32", max_batch=1, backend_factory=HostBackend, heartbeat_timeout=5.0)
+    outs, stats = _run(d, m, part_at, [x])
+    np.testing.assert_allclose(outs[0], oracle_for(m).predict(x)[0], rtol=1e-5, atol=1e-7)

@@ -41,6 +41,22 @@ def test_product_layer_table_agrees_with_oracle(model50):
     assert [tuple(w.shape) for w in model50.get_weights()] == [s for _, _, s in ws]
 
 
+@pytest.mark.parametrize("name,depths,n_layers,n_params", [("ResNet101", (3, 4, 23, 3), 347, 44_707_176),
+                                                           ("ResNet152", (3, 8, 36, 3), 517, 60_419_944)])
+def test_deeper_variants_agree_with_oracle_topology(pkg, name, depths, n_layers, n_params):
+    """Keras' ResNet101 / ResNet152 (v1) are the same builder with other stack depths: published layer and
+    parameter counts, and the product's stand-in lists the same layers, shapes and edges as the oracle."""
+    import adapt_b200
+
+    L = KO.build_resnet50_layers(depths)
+    assert len(L) == n_layers and KO.total_params(L) == n_params
+    m = getattr(adapt_b200, name)(weights=None)
+    assert [l.name for l in m.layers] == [l.name for l in L]
+    for a, b in zip(m.layers, L):
+        assert a.class_name == b.kind and tuple(a.output_shape[1:]) == tuple(b.out_shape) and a.inbound_names == b.inbound
+    assert len(oracle_for(m).layers) == n_layers       # depth inferred from the weight names
+
+
 def test_conv_against_independent_formulation():
     torch = pytest.importorskip("torch")
     F = torch.nn.functional

@@ -219,3 +219,18 @@ def test_bad_arguments_fail_loudly(model50, nat):
     with pytest.raises(nat.AdaptError):
         p.ex.enqueue(1, 1, 0)            # slot 1 never bound
     p.close()
+
+
+def test_resnet101_shares_every_kernel(pkg):
+    """a deeper graph from the same builder runs on the same kernels (23 conv4 blocks)."""
+    import adapt_b200
+
+    m = adapt_b200.ResNet101(weights=None)
+    o = oracle_for(m)
+    x = KO.synthetic_images(2, seed=31, kind="normal")
+    ref = o.predict(x)[0]
+    got = _predictor(m, mode="bf16", max_batch=2).predict(x)
+    assert np.abs(got - ref).max() <= PROB_TOL_BF16
+    assert got.argmax(-1).tolist() == ref.argmax(-1).tolist()
+    got32 = _predictor(m, mode="fp32", max_batch=2).predict(x)
+    assert np.abs(got32 - ref).max() <= PROB_TOL_FP32
