@@ -183,7 +183,7 @@ class DEFER:
         self.workers: List[StageWorker] = []
         self.models_to_dispatch: List[PartModel] = []
         self.part_at: List[str] = []
-        self.stats = {"delivered": 0, "replayed": 0, "failovers": 0, "failover_ms": [], "dropped_stale": 0}
+        self.stats = {"delivered": 0, "replayed": 0, "failovers": 0, "failover_ms": [], "dropped_stale": 0, "rejoins": 0}
         self.latencies_ms: List[float] = []
         self._feed_lock = threading.Lock()
         self._collect_lock = threading.Lock()
@@ -417,6 +417,14 @@ class DEFER:
             alive = set(self._get_available_workers())
             dead = [w for w in self.order if w not in alive]
             if not dead:
+                # elastic re-join: a worker that is healthy again but holds no stage is given one
+                joiners = sorted(w for w in alive if w not in self.order and not int(self.health.w[w, W_KILL]))
+                if joiners:
+                    try:
+                        self._rejoin(joiners)
+                    except Exception as e:  # noqa: BLE001
+                        self.error = f"re-join failed: {type(e).__name__}: {e}; joiners: {joiners}; {self.debug_state()}"
+                        self._shutdown_event.set()
                 continue
             causes = {w: (self._worker_error(w) if int(self.health.w[w, W_STATE]) == StateEnum.ERROR
                           else f"heartbeat {self.health.age_ms(w):.0f} ms old, state {int(self.health.w[w, W_STATE])}")
@@ -447,6 +455,30 @@ class DEFER:
                 self.stats["replayed"] += 1
         self.stats["failovers"] += 1
         self.stats.setdefault("reconfig_ms", []).append((time.perf_counter() - t0) * 1e3)
+
+    def _rejoin(self, joiners: List[int]) -> None:
+        """Widen the pipeline again: the same two-phase reconfiguration as a fail-over, over the current stages
+        plus the returning workers (kept in worker order, so the dispatcher-local stage stays first), with the
+        time-balanced cuts for the new stage count; every retained, undelivered input is replayed in order."""
+        t0 = time.perf_counter()
+        with self._feed_lock:  # feeder paused
+            order = sorted(set(self.order) | set(joiners))
+            part_at = balanced_part_at(self.model, len(order))
+            self._reconfigure(order, part_at)
+            with self.inflight_lock:
+                pending = sorted(self.inflight_tasks.items())
+            for seq, task in pending:
+                self._feed_one(seq, task["data"])
+                self.stats["replayed"] += 1
+        self.stats["rejoins"] += 1
+        self.stats.setdefault("rejoin_ms", []).append((time.perf_counter() - t0) * 1e3)
+
+    def revive(self, worker_id: int) -> None:
+        """Undo an injected kill: the worker resumes its heartbeat and, once the watchdog sees it healthy, gets
+        a stage again (`stats["rejoins"]`)."""
+        if worker_id in self.order:
+            raise RuntimeError(f"worker {worker_id} still holds a stage: the fail-over that drops it has not run yet")
+        self.health.w[worker_id, W_KILL] = 0
 
     # ------------------------------------------------------------------ measurement aids
     def preload_input(self, x) -> None:

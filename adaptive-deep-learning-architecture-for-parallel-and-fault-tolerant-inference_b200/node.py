@@ -432,7 +432,17 @@ class StageWorker:
                     break
                 if int(h.w[self.wid, W_KILL]):
                     self._die()
-                    break
+                    # silent until shut down -- or revived (DEFER.revive clears the kill word): then the heartbeat
+                    # resumes and the worker idles without a stage until the dispatcher re-slices it back in
+                    while int(h.w[self.wid, W_KILL]) and not self._stop.is_set() and h.phase != PHASE_SHUTDOWN:
+                        time.sleep(1e-3)
+                    if self._stop.is_set() or h.phase == PHASE_SHUTDOWN:
+                        break
+                    self.dead = False
+                    self.stage_index, self.epoch = -1, -1
+                    self.state.state = StateEnum.IDLE
+                    self._start_heartbeat()
+                    continue
                 if phase == PHASE_QUIESCE and int(h.w[self.wid, W_ACK_QUIESCE]) != epoch:
                     self.state.state = StateEnum.IDLE
                     self._quiesce(epoch)

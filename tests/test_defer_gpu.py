@@ -141,6 +141,45 @@ def test_failover_resliced_and_replayed(pkg, model50):
     assert stats["failover_ms"] and stats["failover_ms"][0] < 1000.0   # sub-second recovery (north_star)
 
 
+def test_elastic_rejoin_after_failover_gpu(pkg, model50):
+    """Kill a stage mid-stream (3 -> 2 stages), revive it, and the watchdog re-slices it back in (2 -> 3) while
+    inputs keep flowing: FIFO and exactly once across both reconfigurations, values against the oracle."""
+    from adapt_b200.dispatcher import DEFER
+
+    devs = [f"cuda:{i % max(1, _ngpu())}" for i in range(3)]
+    inputs = [KO.synthetic_images(2, seed=800 + i, kind="normal") for i in range(60)]
+    defer = DEFER(devs, max_batch=2, heartbeat_timeout=0.05)
+    in_q, out_q = queue.Queue(10), queue.Queue()
+    t = threading.Thread(target=defer.run_defer, args=(model50, ["conv2_block3_out", "conv4_block1_out"], in_q, out_q),
+                         daemon=True)
+    t.start()
+    defer.wait_ready(120)
+    threading.Thread(target=lambda: [in_q.put(x) for x in inputs], daemon=True).start()
+    outs, victim, revived, t0 = [], None, False, time.time()
+    while len(outs) < len(inputs):
+        try:
+            outs.append(out_q.get(timeout=0.2))
+        except queue.Empty:
+            assert defer.error is None, defer.error
+            assert time.time() - t0 < 60, f"timed out with {len(outs)}/{len(inputs)}: {defer.debug_state()}"
+        if victim is None and len(outs) >= 10:
+            victim = defer.inject_kill(1)
+        if victim is not None and not revived and defer.stats["failovers"] == 1 and len(outs) >= 25:
+            defer.revive(victim)
+            revived = True
+    t1 = time.time()
+    while defer.stats["rejoins"] == 0 and time.time() - t1 < 10:   # (the stream may end before the watchdog's next look)
+        time.sleep(0.01)
+    time.sleep(0.05)
+    assert out_q.empty(), "duplicate delivery"
+    stats, order = dict(defer.stats), list(defer.order)
+    defer.shutdown()
+    t.join(30)
+    assert stats["failovers"] == 1 and stats["rejoins"] == 1 and stats["delivered"] == len(inputs)
+    assert len(order) == 3 and victim in order
+    _check(model50, inputs, outs)
+
+
 def test_fp32_check_mode_through_defer(pkg, model50):
     from adapt_b200.dispatcher import DEFER
 

@@ -222,3 +222,45 @@ def test_deeper_resnets_share_the_front_end(pkg, ctor_name, n_params, n_layers):
     d = DEFER([0, 1, 2], mode="fp32", max_batch=1, backend_factory=HostBackend, heartbeat_timeout=5.0)
     outs, stats = _run(d, m, part_at, [x])
     np.testing.assert_allclose(outs[0], oracle_for(m).predict(x)[0], rtol=1e-5, atol=1e-7)
+
+
+def test_elastic_rejoin_after_failover(pkg, model50):
+    """a stage is killed (3 -> 2 stages), later revived; the watchdog hands it a stage again
+    (2 -> 3) and the stream continues -- FIFO, nothing lost, nothing duplicated across both reconfigurations."""
+    import threading
+
+    from adapt_b200.dispatcher import DEFER
+
+    o = oracle_for(model50)
+    inputs = [KO.synthetic_images(1, seed=300 + i, kind="normal") for i in range(12)]
+    d = DEFER([0, 1, 2], mode="fp32", max_batch=1, backend_factory=lambda dev: HostBackend(dev, delay=0.01),
+              heartbeat_timeout=1.0)   # (host executors hold the GIL for long stretches: a generous liveness window)
+    in_q, out_q = queue.Queue(4), queue.Queue()
+    t = threading.Thread(target=d.run_defer, args=(model50, ["conv2_block3_out", "conv4_block1_out"], in_q, out_q), daemon=True)
+    t.start()
+    d.wait_ready(60)
+    outs = []
+
+    def pump(items):
+        for x in items:
+            in_q.put(x)
+            outs.append(out_q.get(timeout=60))
+
+    pump(inputs[:3])
+    victim = d.inject_kill(1)
+    with pytest.raises(RuntimeError):
+        d.revive(victim)                      # still holds a stage: the fail-over has not happened yet
+    pump(inputs[3:7])                         # stalls until the fail-over, then flows through 2 stages
+    assert d.stats["failovers"] == 1 and len(d.order) == 2 and victim not in d.order, (d.stats, d.order)
+    d.revive(victim)
+    t0 = time.time()
+    while d.stats["rejoins"] == 0 and time.time() - t0 < 20:
+        time.sleep(0.01)
+    assert d.stats["rejoins"] == 1 and len(d.order) == 3 and victim in d.order and len(d.part_at) == 2
+    pump(inputs[7:])
+    assert d.error is None and out_q.empty()
+    d.shutdown()
+    t.join(30)
+    assert d.stats["delivered"] == len(inputs)
+    for x, y in zip(inputs, outs):
+        np.testing.assert_allclose(y, o.predict(x)[0], rtol=1e-5, atol=1e-7)
