@@ -264,3 +264,39 @@ def test_elastic_rejoin_after_failover(pkg, model50):
     assert d.stats["delivered"] == len(inputs)
     for x, y in zip(inputs, outs):
         np.testing.assert_allclose(y, o.predict(x)[0], rtol=1e-5, atol=1e-7)
+
+
+def test_cascading_kills(pkg, model50):
+    """Two stages die one after the other (3 -> 2 -> 1 stages): each death is detected and re-sliced on its own,
+    the stream stays FIFO and exactly-once, and the last survivor runs the whole model."""
+    import threading
+
+    from adapt_b200.dispatcher import DEFER
+
+    o = oracle_for(model50)
+    inputs = [KO.synthetic_images(1, seed=350 + i, kind="normal") for i in range(9)]
+    d = DEFER([0, 1, 2], mode="fp32", max_batch=1, backend_factory=lambda dev: HostBackend(dev, delay=0.01),
+              heartbeat_timeout=1.0)
+    in_q, out_q = queue.Queue(4), queue.Queue()
+    t = threading.Thread(target=d.run_defer, args=(model50, ["conv2_block3_out", "conv4_block1_out"], in_q, out_q), daemon=True)
+    t.start()
+    d.wait_ready(60)
+    outs = []
+
+    def pump(items):
+        for x in items:
+            in_q.put(x)
+            outs.append(out_q.get(timeout=60))
+
+    pump(inputs[:2])
+    d.inject_kill(2)
+    pump(inputs[2:5])
+    assert d.stats["failovers"] == 1 and len(d.order) == 2
+    d.inject_kill(1)
+    pump(inputs[5:])
+    assert d.stats["failovers"] == 2 and len(d.order) == 1 and d.part_at == []
+    assert d.error is None and out_q.empty()
+    d.shutdown()
+    t.join(30)
+    for x, y in zip(inputs, outs):
+        np.testing.assert_allclose(y, o.predict(x)[0], rtol=1e-5, atol=1e-7)
