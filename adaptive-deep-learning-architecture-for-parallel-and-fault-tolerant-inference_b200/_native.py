@@ -18,7 +18,9 @@ OK, EINVAL, ECUDA, ENODEV, ENOMEM, ESTATE = 0, -1, -2, -3, -4, -5
 MODE_BF16, MODE_FP32_CHECK = 0, 1
 OP_INGEST, OP_CONV, OP_MAXPOOL, OP_GAP, OP_SOFTMAX, OP_AFFINE, OP_ZEROPAD = 0, 1, 2, 3, 4, 5, 6
 T_INTERNAL, T_INPUT, T_OUTPUT = 0, 1, 2
-DT_WORK, DT_F32 = 0, 1
+DT_WORK, DT_F32, DT_U8 = 0, 1, 2
+IN_F32, IN_U8_RGB_CAFFE = 0, 1  # INGEST input formats (include/adapt_b200.h)
+INPUT_FORMATS = {"float32": IN_F32, "uint8": IN_U8_RGB_CAFFE}
 NOALLOC_MAX_LOGITS = 256 * 1024  # ADAPT_NOALLOC_MAX_LOGITS
 
 
@@ -57,7 +59,7 @@ class OpDesc(C.Structure):
         ("relu", C.c_int32),
         ("weight", C.c_int32),
         ("out_f32", C.c_int32),
-        ("reserved", C.c_int32),
+        ("in_format", C.c_int32),
     ]
 
 

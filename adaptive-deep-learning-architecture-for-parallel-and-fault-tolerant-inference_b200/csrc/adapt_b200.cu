@@ -658,6 +658,7 @@ namespace {
 
 size_t elem_size(const adapt_stage* st, int dtype) {
     if (dtype == ADAPT_DT_F32) return 4;
+    if (dtype == ADAPT_DT_U8) return 1;
     return st->mode == ADAPT_MODE_BF16 ? 2 : 4;
 }
 
@@ -776,21 +777,36 @@ int run_steps(adapt_stage* st, const std::vector<Step>& steps, cudaStream_t stre
         switch (s.kind) {
             case ADAPT_OP_INGEST: {
                 const long long pixels = (long long)B * o.H * o.W;
+                const bool u8 = o.in_format == ADAPT_IN_U8_RGB_CAFFE;  // raw uint8 RGB, preprocessing fused
+                if (o.in_format != ADAPT_IN_F32 && !u8) return fail(ADAPT_EINVAL, "ingest: unknown input format %d", o.in_format);
+                if (u8 && o.Cin != 3) return fail(ADAPT_EINVAL, "ingest: uint8 input needs 3 channels");
+                const int threads = 256;
                 if (st->mode == ADAPT_MODE_BF16 && o.Cout == 16) {
                     // space-to-depth ingest for the stem: (H, W, 3) -> (Ho, Wo, 16) with `pad` folded in
                     if (o.Cin != 3 || o.Ho * 2 != o.H + 2 * o.pad || o.Wo * 2 != o.W + 2 * o.pad)
                         return fail(ADAPT_EINVAL, "ingest(s2d): expects 3 channels and Ho = (H + 2*pad) / 2");
                     const long long outs = (long long)B * o.Ho * o.Wo;
-                    const int threads = 256;
-                    adapt::ingest_s2d_kernel<<<(unsigned)((outs + threads - 1) / threads), threads, 0, stream>>>(
-                        reinterpret_cast<const float*>(s.in), reinterpret_cast<__nv_bfloat16*>(s.out), B, o.H, o.W, o.Ho, o.Wo,
-                        o.pad);
+                    const unsigned blocks = (unsigned)((outs + threads - 1) / threads);
+                    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(s.out);
+                    if (u8)
+                        adapt::ingest_s2d_kernel<adapt::SrcU8Caffe><<<blocks, threads, 0, stream>>>(
+                            reinterpret_cast<const uint8_t*>(s.in), dst, B, o.H, o.W, o.Ho, o.Wo, o.pad);
+                    else
+                        adapt::ingest_s2d_kernel<adapt::SrcF32><<<blocks, threads, 0, stream>>>(
+                            reinterpret_cast<const float*>(s.in), dst, B, o.H, o.W, o.Ho, o.Wo, o.pad);
                 } else if (st->mode == ADAPT_MODE_BF16) {
                     if (o.Cout != 8 || o.Cin > 8) return fail(ADAPT_EINVAL, "ingest: expects Cin<=8 -> 8 channels");
-                    const int threads = 256;
-                    const long long blocks = (pixels + threads - 1) / threads;
-                    adapt::ingest_f32_to_bf16_pad8_kernel<<<(unsigned)blocks, threads, 0, stream>>>(
-                        reinterpret_cast<const float*>(s.in), reinterpret_cast<__nv_bfloat16*>(s.out), pixels, o.Cin);
+                    const unsigned blocks = (unsigned)((pixels + threads - 1) / threads);
+                    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(s.out);
+                    if (u8)
+                        adapt::ingest_pad8_kernel<adapt::SrcU8Caffe><<<blocks, threads, 0, stream>>>(
+                            reinterpret_cast<const uint8_t*>(s.in), dst, pixels, o.Cin);
+                    else
+                        adapt::ingest_pad8_kernel<adapt::SrcF32><<<blocks, threads, 0, stream>>>(
+                            reinterpret_cast<const float*>(s.in), dst, pixels, o.Cin);
+                } else if (u8) {
+                    adapt::ingest_u8_to_f32_kernel<<<(unsigned)((pixels + threads - 1) / threads), threads, 0, stream>>>(
+                        reinterpret_cast<const uint8_t*>(s.in), reinterpret_cast<float*>(s.out), pixels);
                 } else {
                     CUDA_TRY(cudaMemcpyAsync(s.out, s.in, (size_t)pixels * o.Cin * 4, cudaMemcpyDeviceToDevice,
                                              stream));

@@ -12,15 +12,34 @@
 namespace adapt {
 
 // ---------------------------------------------------------------------------------------------
-// fp32 NHWC (B,H,W,Cin) -> bf16 NHWC (B,H,W,Cpad) with zero channel padding (Cpad = 8 for the stem)
-// One thread per output pixel: reads Cin floats, writes one 16-byte vector.
-__global__ void ingest_f32_to_bf16_pad8_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out,
-                                               long long num_pixels, int Cin) {
+// Image sources of the ingest kernels.  SrcF32: the reference's queue contract, an already preprocessed fp32
+// image.  SrcU8Caffe: a raw uint8 RGB image with Keras' caffe-mode `preprocess_input` (RGB -> BGR, minus the
+// ImageNet channel means, no scaling; reference test/test.py:20-23) applied on the fly -- 4x fewer bytes over PCIe.
+struct SrcF32 {
+    using T = float;
+    static __device__ __forceinline__ float get(const float* img, long long pixel, int c, int Cin) {
+        return __ldg(img + pixel * Cin + c);
+    }
+};
+struct SrcU8Caffe {
+    using T = uint8_t;
+    static __device__ __forceinline__ float get(const uint8_t* img, long long pixel, int c, int /*Cin == 3*/) {
+        const float mean = c == 0 ? 103.939f : (c == 1 ? 116.779f : 123.68f);
+        return static_cast<float>(__ldg(img + pixel * 3 + (2 - c))) - mean;
+    }
+};
+
+// ---------------------------------------------------------------------------------------------
+// NHWC (B,H,W,Cin) image -> bf16 NHWC (B,H,W,Cpad) with zero channel padding (Cpad = 8 for the stem)
+// One thread per output pixel: reads Cin values, writes one 16-byte vector.
+template <typename Src>
+__global__ void ingest_pad8_kernel(const typename Src::T* __restrict__ in, __nv_bfloat16* __restrict__ out,
+                                   long long num_pixels, int Cin) {
     const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
     if (i >= num_pixels) return;
     float v[8];
 #pragma unroll
-    for (int c = 0; c < 8; ++c) v[c] = (c < Cin) ? __ldg(in + i * Cin + c) : 0.0f;
+    for (int c = 0; c < 8; ++c) v[c] = (c < Cin) ? Src::get(in, i, c, Cin) : 0.0f;
     uint4 o;
     __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&o);
 #pragma unroll
@@ -28,15 +47,24 @@ __global__ void ingest_f32_to_bf16_pad8_kernel(const float* __restrict__ in, __n
     reinterpret_cast<uint4*>(out)[i] = o;
 }
 
+// uint8 RGB -> preprocessed fp32 (fp32 check mode), one thread per pixel
+__global__ void ingest_u8_to_f32_kernel(const uint8_t* __restrict__ in, float* __restrict__ out, long long num_pixels) {
+    const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+    if (i >= num_pixels) return;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) out[i * 3 + c] = SrcU8Caffe::get(in, i, c, 3);
+}
+
 // ---------------------------------------------------------------------------------------------
-// Stem ingest with space-to-depth: fp32 NHWC (B,H,W,3) -> bf16 (B, Hs, Ws, 16) where
+// Stem ingest with space-to-depth: NHWC (B,H,W,3) image -> bf16 (B, Hs, Ws, 16) where
 //   X[b, hh, ww, (py*2+px)*3 + c] = in_padded[b, 2*hh+py, 2*ww+px, c]      (channels 12..15 = 0)
-// and in_padded is the image zero-padded by `pad` (3) on every side (conv1_pad folded in).  The
+// and in_padded is the (preprocessed) image zero-padded by `pad` (3) on every side (conv1_pad folded in).  The
 // 7x7 stride-2 convolution of the stem becomes a 4x4 stride-1 convolution over X with 16 stored
 // channels, whose four horizontally adjacent pixels are one contiguous 128-byte K-slab -- exactly
 // what the implicit-GEMM kernel's 64-element k-block wants.  One thread per X pixel (32 bytes out).
-__global__ void ingest_s2d_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, int B, int H, int W,
-                                  int Hs, int Ws, int pad) {
+template <typename Src>
+__global__ void ingest_s2d_kernel(const typename Src::T* __restrict__ in, __nv_bfloat16* __restrict__ out, int B, int H,
+                                  int W, int Hs, int Ws, int pad) {
     const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
     const long long total = static_cast<long long>(B) * Hs * Ws;
     if (i >= total) return;
@@ -54,9 +82,9 @@ __global__ void ingest_s2d_kernel(const float* __restrict__ in, __nv_bfloat16* _
         for (int px = 0; px < 2; ++px) {
             const int wi = 2 * ww + px - pad;
             if (hi >= 0 && hi < H && wi >= 0 && wi < W) {
-                const float* src = in + ((static_cast<long long>(b) * H + hi) * W + wi) * 3;
+                const long long pixel = (static_cast<long long>(b) * H + hi) * W + wi;
 #pragma unroll
-                for (int c = 0; c < 3; ++c) v[(py * 2 + px) * 3 + c] = __ldg(src + c);
+                for (int c = 0; c < 3; ++c) v[(py * 2 + px) * 3 + c] = Src::get(in, pixel, c, 3);
             }
         }
     }

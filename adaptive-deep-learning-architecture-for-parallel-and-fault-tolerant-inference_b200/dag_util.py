@@ -253,6 +253,7 @@ class Op:
     relu: int = 0
     weight: int = -1
     out_f32: int = 0
+    in_format: int = 0  # INGEST: N.IN_*
     layers: List[str] = field(default_factory=list)  # Keras layers this op covers
 
 
@@ -274,7 +275,7 @@ class StageProgram:
         o = (N.OpDesc * len(self.ops))()
         for i, p in enumerate(self.ops):
             o[i] = N.OpDesc(p.kind, p.inp, p.res, p.out, p.H, p.W, p.Cin, p.Ho, p.Wo, p.Cout, p.kh, p.kw, p.stride,
-                            p.pad, p.relu, p.weight, p.out_f32, 0)
+                            p.pad, p.relu, p.weight, p.out_f32, p.in_format)
         return t, o
 
 
@@ -289,8 +290,11 @@ def cut_tensor_elems(model: Model, layer_name: str, mode: int) -> int:
     return _stored_c(shp[0], mode)
 
 
-def compile_part(part: PartModel, windex: Dict[str, int], mode: int = N.MODE_BF16) -> StageProgram:
-    """Fuse the Keras layers of `part` into stage ops and assign activation buffers."""
+def compile_part(part: PartModel, windex: Dict[str, int], mode: int = N.MODE_BF16,
+                 input_format: int = N.IN_F32) -> StageProgram:
+    """Fuse the Keras layers of `part` into stage ops and assign activation buffers.  `input_format` (N.IN_*) only
+    matters for the part that takes the model input: fp32 preprocessed images (the reference's contract) or raw
+    uint8 RGB images preprocessed inside the ingest kernel."""
     model = part.model
     cons = _consumers(model)
     in_part = set(part.layer_names)
@@ -317,7 +321,9 @@ def compile_part(part: PartModel, windex: Dict[str, int], mode: int = N.MODE_BF1
     s2d_pad: Optional[str] = None  # ZeroPadding2D layer absorbed by the space-to-depth ingest
     if part.takes_model_input:
         h, w, c = shape_of(part.start)
-        t_in = new_t(h * w * c, N.DT_F32, part.start)
+        if input_format == N.IN_U8_RGB_CAFFE and c != 3:
+            raise ValueError("uint8 input needs a 3-channel image")
+        t_in = new_t(h * w * c, N.DT_U8 if input_format == N.IN_U8_RGB_CAFFE else N.DT_F32, part.start)
         vt[t_in].role = N.T_INPUT
         # bf16 stem fast path: pad -> 7x7/2 conv -> BN all inside this part => space-to-depth ingest
         if mode == N.MODE_BF16 and len(part.layer_names) >= 3:
@@ -329,12 +335,13 @@ def compile_part(part: PartModel, windex: Dict[str, int], mode: int = N.MODE_BF1
             hp, wp = h + 6, w + 6
             t0 = new_t((hp // 2) * (wp // 2) * 16, N.DT_WORK, part.start + ":s2d")
             ops.append(Op(N.OP_INGEST, t_in, t0, H=h, W=w, Cin=c, Ho=hp // 2, Wo=wp // 2, Cout=16, pad=3,
-                          layers=[part.start, s2d_pad]))
+                          in_format=input_format, layers=[part.start, s2d_pad]))
             done.add(s2d_pad)
             val[s2d_pad] = t0
         else:
             t0 = new_t(h * w * _stored_c(c, mode), N.DT_WORK, part.start + ":ingest")
-            ops.append(Op(N.OP_INGEST, t_in, t0, H=h, W=w, Cin=c, Ho=h, Wo=w, Cout=_stored_c(c, mode), layers=[part.start]))
+            ops.append(Op(N.OP_INGEST, t_in, t0, H=h, W=w, Cin=c, Ho=h, Wo=w, Cout=_stored_c(c, mode),
+                          in_format=input_format, layers=[part.start]))
         val[part.start] = t0
     else:
         t_in = new_t(cut_tensor_elems(model, part.start, mode), N.DT_WORK, part.start)

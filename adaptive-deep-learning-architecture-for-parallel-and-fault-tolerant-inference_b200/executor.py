@@ -21,12 +21,14 @@ MODES = {"bf16": N.MODE_BF16, "fp32": N.MODE_FP32_CHECK, "fp32-check": N.MODE_FP
 def elem_bytes(dtype: int, mode: int) -> int:
     if dtype == N.DT_F32:
         return 4
+    if dtype == N.DT_U8:
+        return 1
     return 2 if mode == N.MODE_BF16 else 4
 
 
 class StageExecutor:
     def __init__(self, model: Model, part: PartModel, device: int = 0, mode: str = "bf16", max_batch: int = 128,
-                 reserve_full: bool = False):
+                 reserve_full: bool = False, input_format: str = "float32"):
         """`reserve_full`: size the stage's activation arena for the WHOLE model before installing `part`, so that
         no later re-slice (a fail-over hands this stage more layers) has to allocate device memory."""
         N.require_gpu()
@@ -35,6 +37,9 @@ class StageExecutor:
         self.device = int(device)
         self.mode = MODES[mode] if isinstance(mode, str) else int(mode)
         self.max_batch = int(max_batch)
+        if input_format not in N.INPUT_FORMATS:
+            raise ValueError(f"input_format must be one of {sorted(N.INPUT_FORMATS)}")
+        self.input_format = N.INPUT_FORMATS[input_format]  # of the model input, when this stage takes it
         self.entries, self.windex = build_weight_table(model)
         self._keepalive = self.entries  # host arrays must outlive adapt_stage_create
         whole = None
@@ -43,7 +48,7 @@ class StageExecutor:
 
             whole = construct_model(model, model.layers[0].name, model.layers[-1].name, "whole")
         self.part = whole or part
-        self.program: StageProgram = compile_part(self.part, self.windex, self.mode)
+        self.program: StageProgram = compile_part(self.part, self.windex, self.mode, self.input_format)
         w = (N.WeightDesc * len(self.entries))()
         for i, e in enumerate(self.entries):
             kh, kw, cin, cout = e.geom
@@ -60,7 +65,7 @@ class StageExecutor:
     # ---- program / geometry ---------------------------------------------------------------------
     def reslice(self, part: PartModel) -> None:
         """Install another layer range; weights stay resident (metadata-only re-slice)."""
-        program = compile_part(part, self.windex, self.mode)
+        program = compile_part(part, self.windex, self.mode, self.input_format)
         t, o = program.c_arrays()
         N.check(self.lib.adapt_stage_reslice(self.handle, t, len(t), o, len(o)))
         self.part, self.program = part, program
@@ -173,13 +178,14 @@ class LocalPredictor:
     arrays.  With the full range it is `model.predict` of reference test/local_infer.py:22."""
 
     def __init__(self, model: Model, mode: str = "bf16", device: int = 0, max_batch: int = 32,
-                 start: Optional[str] = None, end: Optional[str] = None):
+                 start: Optional[str] = None, end: Optional[str] = None, input_format: str = "float32"):
         self.key = (mode, device, model._version)
         self.model = model
         start = start or model.layers[0].name
         end = end or model.layers[-1].name
         self.part = construct_model(model, start, end, "part1")
-        self.ex = StageExecutor(model, self.part, device=device, mode=mode, max_batch=max_batch)
+        self.ex = StageExecutor(model, self.part, device=device, mode=mode, max_batch=max_batch, input_format=input_format)
+        self.input_u8 = self.part.takes_model_input and input_format == "uint8"
         self.mode = self.ex.mode
         self.device = device
         self.max_batch = max_batch
@@ -201,8 +207,9 @@ class LocalPredictor:
         return out
 
     def run(self, x: np.ndarray) -> np.ndarray:
-        """float32 in (model input or cut tensor, logical NHWC shape) -> float32 out (logical shape)."""
-        x = np.asarray(x, dtype=np.float32)
+        """float32 in (model input or cut tensor, logical NHWC shape; raw uint8 RGB images with input_format="uint8")
+        -> float32 out (logical shape)."""
+        x = np.asarray(x, dtype=np.uint8 if self.input_u8 else np.float32)
         outs = []
         out_shape = self.part.output_shape[1:]
         for i in range(0, x.shape[0], self.max_batch):

@@ -322,10 +322,11 @@ class CudaBackend:
         self.lib.adapt_heartbeat_stop(handle)
 
     # compute
-    def make_executor(self, model, part, mode: str, max_batch: int):
+    def make_executor(self, model, part, mode: str, max_batch: int, input_format: str = "float32"):
         from .executor import StageExecutor
 
-        return StageExecutor(model, part, device=self.device, mode=mode, max_batch=max_batch, reserve_full=True)
+        return StageExecutor(model, part, device=self.device, mode=mode, max_batch=max_batch, reserve_full=True,
+                             input_format=input_format)
 
     def close(self) -> None:
         for a in self._registered:

@@ -210,7 +210,11 @@ class StageWorker:
             bounds = [self.model.layers[0].name] + list(table["part_at"]) + [self.model.layers[-1].name]
             part = construct_model(self.model, bounds[i], bounds[i + 1], f"part{i + 1}")
             if self.executor is None:
-                self.executor = self.backend.make_executor(self.model, part, self.mode, self.max_batch)
+                fmt = self.session.get("input_format", "float32")
+                if fmt == "float32":
+                    self.executor = self.backend.make_executor(self.model, part, self.mode, self.max_batch)
+                else:
+                    self.executor = self.backend.make_executor(self.model, part, self.mode, self.max_batch, input_format=fmt)
             else:
                 self.executor.reslice(part)
             self.stage_index, self.n_stages = i, len(order)

@@ -356,6 +356,27 @@ def run_ours(args) -> int:
     defer.shutdown()
     th.join(60)
 
+    # ---------------- extra leg: raw uint8 inputs, preprocessing fused into the ingest kernel ----------------
+    # (not the reference's queue contract, hence not `e2e`: reported beside it.  Single-process runs
+    # only: under torchrun the worker ranks leave with the session above.)
+    e2e_u8 = None
+    if world == 1 and not args.no_uint8_leg:
+        d8 = DEFER(devices, mode="bf16", max_batch=B, warm_batches=[B], max_inflight=max(2 * n + 4, 12),
+                   heartbeat_timeout=float(os.environ.get("ADAPT_HEARTBEAT_TIMEOUT_S", "0.05")), input_format="uint8",
+                   ingest_rails=args.ingest_rails)
+        q_in, q_out = queue.Queue(2 * n + 8), queue.Queue()
+        th8 = threading.Thread(target=d8.run_defer, args=(model, part_at, q_in, q_out), daemon=True)
+        th8.start()
+        d8.wait_ready(600)
+        rng8 = np.random.default_rng(0)
+        raw = [torch.from_numpy(rng8.integers(0, 256, (B, 224, 224, 3), dtype=np.uint8)).pin_memory() for _ in range(3)]
+        o8, wall8, _ = drive_steady(d8, q_in, q_out, [raw[i % 3] for i in range(W + K)], W)
+        e2e_u8 = {"value": round(K * B / wall8, 1), "unit": "img/s", "h2d_bytes_per_step": int(raw[0].numel()),
+                  "d2h_bytes_per_step": B * 1000 * 4, "probs_row_sum": float(np.float64(o8[-1]).sum() / B),
+                  "input": "raw uint8 RGB (B,224,224,3), caffe preprocess_input fused into the ingest kernel"}
+        d8.shutdown()
+        th8.join(60)
+
     # ---------------- CPU baseline on a bounded sample (N=1 only) ----------------
     cpu = None
     if n == 1 and not args.no_cpu_baseline:
@@ -384,6 +405,7 @@ def run_ours(args) -> int:
                 "timing": "wall clock from the arrival of the last warm-up result to the arrival of the K-th timed "
                           "result, W + K pinned host batches fed back to back (pipeline full); "
                           "value_incl_fill_and_drain = (W + K) batches over the whole drive"},
+        "e2e_uint8": e2e_u8,
         "gpu_launches": int(launches_per_step * K),
         "roofline": roofline,
         "cpu_baseline": cpu,
@@ -412,6 +434,7 @@ def main() -> int:
                     help="N>1: spread pinned input batches over every GPU's PCIe link (auto) or use the first stage's only")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-failover", action="store_true")
+    ap.add_argument("--no-uint8-leg", action="store_true", help="skip the extra end-to-end leg with raw uint8 inputs")
     ap.add_argument("--dump-ops", default=None, help="write the per-launch timing table (JSON) here")
     args = ap.parse_args()
     if args.warmup < 3:

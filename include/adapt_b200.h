@@ -56,6 +56,7 @@ extern "C" {
 /* tensor element types */
 #define ADAPT_DT_WORK 0     /* bf16 in ADAPT_MODE_BF16, fp32 in ADAPT_MODE_FP32_CHECK */
 #define ADAPT_DT_F32 1
+#define ADAPT_DT_U8 2       /* stage INPUT only: raw uint8 image (see ADAPT_IN_U8_RGB_CAFFE)  */
 
 /* One Conv2D/Dense layer's parameters in Keras layout (what `get_weights()` returns,
  * reference src/dispatcher.py:243) with BatchNormalization already folded on the host into
@@ -85,8 +86,16 @@ typedef struct adapt_op_desc {
     int32_t relu;                    /* apply ReLU in the epilogue                             */
     int32_t weight;                  /* index into the weight table (CONV) or -1               */
     int32_t out_f32;                 /* CONV: write fp32 instead of the working dtype (logits) */
-    int32_t reserved;
+    int32_t in_format;               /* INGEST: ADAPT_IN_* (0 elsewhere)                       */
 } adapt_op_desc;
+
+/* INGEST input formats.  ADAPT_IN_F32 is the reference's queue contract: an fp32 NHWC image that already went
+ * through `preprocess_input` (reference test/test.py:20-23).  ADAPT_IN_U8_RGB_CAFFE (no counterpart in the
+ * reference) takes the raw uint8 RGB image and applies Keras' caffe-mode preprocessing -- RGB -> BGR,
+ * minus the ImageNet channel means (103.939, 116.779, 123.68), no scaling -- inside the ingest kernel, so an input
+ * costs 150,528 bytes of PCIe instead of 602,112. */
+#define ADAPT_IN_F32 0
+#define ADAPT_IN_U8_RGB_CAFFE 1
 
 typedef struct adapt_stage adapt_stage_t;
 

@@ -17,7 +17,8 @@ def _u32(addr):
 
 
 class HostExecutor:
-    def __init__(self, model, part, max_batch, delay=0.0):
+    def __init__(self, model, part, max_batch, delay=0.0, input_format="float32"):
+        self.input_format = input_format
         self.oracle = oracle_for(model)
         self.model = model
         self.max_batch = max_batch
@@ -47,7 +48,12 @@ class HostExecutor:
         in_ptr, out_ptr = self.io[slot]
         n_in = batch * int(np.prod(self.in_shape))
         n_out = batch * int(np.prod(self.out_shape))
-        x = np.ctypeslib.as_array((ctypes.c_float * n_in).from_address(in_ptr)).reshape((batch,) + self.in_shape).copy()
+        if self.input_format == "uint8" and self.part.takes_model_input:
+            # raw RGB uint8 image: Keras caffe-mode preprocess_input, then the same oracle
+            raw = np.ctypeslib.as_array((ctypes.c_uint8 * n_in).from_address(in_ptr)).reshape((batch,) + self.in_shape)
+            x = raw.astype(np.float32)[..., ::-1] - np.array([103.939, 116.779, 123.68], dtype=np.float32)
+        else:
+            x = np.ctypeslib.as_array((ctypes.c_float * n_in).from_address(in_ptr)).reshape((batch,) + self.in_shape).copy()
         y, _ = self.oracle.run_range(x, self.part.start, self.part.end)
         if self.delay:
             time.sleep(self.delay)
@@ -116,8 +122,8 @@ class HostBackend:
     def memset(self, dst, value, nbytes, stream):
         ctypes.memset(dst, value, int(nbytes))
 
-    def make_executor(self, model, part, mode, max_batch):
-        return HostExecutor(model, part, max_batch, self.delay)
+    def make_executor(self, model, part, mode, max_batch, input_format="float32"):
+        return HostExecutor(model, part, max_batch, self.delay, input_format)
 
     def close(self):
         pass

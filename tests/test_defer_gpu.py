@@ -180,6 +180,22 @@ def test_elastic_rejoin_after_failover_gpu(pkg, model50):
     _check(model50, inputs, outs)
 
 
+def test_uint8_inputs_through_defer(pkg, model50):
+    """input_format="uint8": pinned and pageable raw RGB batches through a 2-stage pipeline, values against the
+    oracle on host-preprocessed images."""
+    torch = pytest.importorskip("torch")
+    from adapt_b200 import preprocess_input
+    from adapt_b200.dispatcher import DEFER
+
+    rng = np.random.default_rng(21)
+    xs = [rng.integers(0, 256, (2, 224, 224, 3), dtype=np.uint8) for _ in range(6)]
+    items = [torch.from_numpy(x).pin_memory() if i % 2 else x for i, x in enumerate(xs)]
+    devs = [f"cuda:{i % max(1, _ngpu())}" for i in range(2)]
+    defer = DEFER(devs, max_batch=2, input_format="uint8")
+    outs, _, _ = _run(defer, model50, ["conv3_block4_out"], items)
+    _check(model50, [preprocess_input(x) for x in xs], outs)
+
+
 def test_fp32_check_mode_through_defer(pkg, model50):
     from adapt_b200.dispatcher import DEFER
 

@@ -300,3 +300,32 @@ def test_cascading_kills(pkg, model50):
     t.join(30)
     for x, y in zip(inputs, outs):
         np.testing.assert_allclose(y, o.predict(x)[0], rtol=1e-5, atol=1e-7)
+
+
+def test_uint8_input_format(pkg, model50):
+    """SURVEY 8(f) rank 4: `input_format="uint8"` -- queue items are raw RGB uint8 images, a quarter of the bytes;
+    preprocessing (RGB -> BGR, ImageNet means) moves behind the queue.  Same values as preprocessing on the host."""
+    from adapt_b200 import preprocess_input
+    from adapt_b200._native import DT_U8, IN_U8_RGB_CAFFE, OP_INGEST
+    from adapt_b200.dag_util import build_weight_table, compile_part, construct_model
+    from adapt_b200.dispatcher import DEFER
+
+    with pytest.raises(ValueError):
+        DEFER([0], input_format="jpeg", backend_factory=HostBackend)
+    # the stage program: only the part that takes the model input changes (1-byte input elements, flagged ingest)
+    _, windex = build_weight_table(model50)
+    first = construct_model(model50, model50.layers[0].name, "conv3_block4_out", "part1")
+    second = construct_model(model50, "conv3_block4_out", model50.layers[-1].name, "part2")
+    for mode in (0, 1):
+        p8, p32 = compile_part(first, windex, mode, IN_U8_RGB_CAFFE), compile_part(first, windex, mode)
+        assert p8.in_dtype == DT_U8 and p8.in_elems == 224 * 224 * 3
+        assert [o.in_format for o in p8.ops if o.kind == OP_INGEST] == [IN_U8_RGB_CAFFE]
+        assert [o.in_format for o in p32.ops if o.kind == OP_INGEST] == [0] and len(p8.ops) == len(p32.ops)
+        assert not any(o.kind == OP_INGEST for o in compile_part(second, windex, mode, IN_U8_RGB_CAFFE).ops)
+    rng = np.random.default_rng(5)
+    imgs = [rng.integers(0, 256, (b, 224, 224, 3), dtype=np.uint8) for b in (1, 2)]
+    d = DEFER([0, 1], mode="fp32", max_batch=2, backend_factory=HostBackend, heartbeat_timeout=5.0, input_format="uint8")
+    outs, stats = _run(d, model50, ["conv3_block4_out"], imgs)
+    o = oracle_for(model50)
+    for x, y in zip(imgs, outs):
+        np.testing.assert_allclose(y, o.predict(preprocess_input(x))[0], rtol=1e-5, atol=1e-7)

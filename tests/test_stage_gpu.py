@@ -234,3 +234,26 @@ def test_resnet101_shares_every_kernel(pkg):
     assert got.argmax(-1).tolist() == ref.argmax(-1).tolist()
     got32 = _predictor(m, mode="fp32", max_batch=2).predict(x)
     assert np.abs(got32 - ref).max() <= PROB_TOL_FP32
+
+
+@pytest.mark.parametrize("end", [None, "conv1_relu", "conv1_pad"])
+def test_uint8_ingest_matches_host_preprocessing(pkg, model50, oracle, end):
+    """Raw uint8 RGB images with the caffe preprocessing fused into the ingest kernels (space-to-depth stem,
+    plain 3 -> 8 channel ingest when a cut separates the stem, fp32 check mode) against the oracle fed with
+    host-preprocessed fp32 images -- and bit-identical to the fp32 input path, which sees the same fp32 values."""
+    from adapt_b200 import preprocess_input
+
+    rng = np.random.default_rng(11)
+    x8 = rng.integers(0, 256, (3, 224, 224, 3), dtype=np.uint8)
+    xf = preprocess_input(x8)
+    for mode, tol in (("bf16", PROB_TOL_BF16), ("fp32", PROB_TOL_FP32)):
+        p8 = _predictor(model50, mode=mode, max_batch=3, end=end, input_format="uint8")
+        pf = _predictor(model50, mode=mode, max_batch=3, end=end)
+        got8, gotf = p8.run(x8), pf.run(xf)
+        np.testing.assert_array_equal(got8, gotf)
+        if end is None:
+            ref = oracle.predict(xf)[0]
+            assert np.abs(got8 - ref).max() <= tol
+            assert got8.argmax(-1).tolist() == ref.argmax(-1).tolist()
+        p8.close()
+        pf.close()
