@@ -498,6 +498,13 @@ class StageWorker:
         if self.executor is not None:
             self.executor.close()
             self.executor = None
+        for r in self.rails:  # ingest rails: staging buffers on the other GPUs
+            for p in r["staging"]:
+                try:
+                    r["backend"].free(p)
+                except Exception:
+                    pass
+        self.rails, self._active_rails = [], []
         try:
             self.backend.close()
         except Exception:
