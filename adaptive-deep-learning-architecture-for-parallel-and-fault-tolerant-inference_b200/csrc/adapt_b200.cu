@@ -455,17 +455,9 @@ int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const vo
     // place (residual in, sum out), so d_out is 0.  d_res >= 3 keeps at least one residual chunk in flight
     // while another is being worked on.
     const bool has_res = residual != nullptr && p.epi_tma != 0;
-    int stages, d_out, d_res;
-    if (memory_bound) {
-        stages = env_int("ADAPT_MB_STAGE_CAP", 0) ? (p.num_k_blocks < 3 ? 3 : (p.num_k_blocks > 4 ? 4 : p.num_k_blocks))
-                                                  : adapt::kMaxStages;  // whatever fits after the epilogue rings
-        d_out = has_res ? 0 : 2;
-        d_res = has_res ? 4 : 0;
-    } else {
-        stages = adapt::kMaxStages;
-        d_out = has_res ? 0 : 2;
-        d_res = has_res ? 3 : 0;
-    }
+    int stages = adapt::kMaxStages;  // as many operand stages as fit beside the epilogue rings (loop below)
+    int d_out = has_res ? 0 : 2;
+    int d_res = has_res ? (memory_bound ? 4 : 3) : 0;
     if (!p.epi_tma) d_out = 2;  // slabs unused by the direct epilogue; keep the layout minimal
     stages = env_int("ADAPT_STAGES", stages);
     if (!has_res) {
