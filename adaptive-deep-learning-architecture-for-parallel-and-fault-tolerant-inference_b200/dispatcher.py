@@ -564,9 +564,21 @@ class DEFER:
             self.concurrency_sem = threading.Semaphore(self.max_inflight or (2 * self._n_workers + 4))
             order = list(range(n))  # spare workers (len(computeNodes) > n) idle until a failover needs them
             self._reconfigure(order, list(partition_layers), first=True)
-            threads = [threading.Thread(target=self._result_server, args=(output_stream,), daemon=True, name="defer-collector"),
-                       threading.Thread(target=self._task_watchdog, daemon=True, name="defer-watchdog"),
-                       threading.Thread(target=self._startDistEdgeInference, args=(input_stream,), daemon=True, name="defer-feeder")]
+            def guarded(fn, *a):
+                # a service thread that is still inside an iteration when the session is torn down (the control
+                # segment is unmapped under it) must end quietly; any other exception is the session's error
+                def run():
+                    try:
+                        fn(*a)
+                    except Exception as e:  # noqa: BLE001
+                        if not self._shutdown_event.is_set():
+                            self.error = self.error or f"{fn.__name__}: {type(e).__name__}: {e}"
+                            self._shutdown_event.set()
+                return run
+
+            threads = [threading.Thread(target=guarded(self._result_server, output_stream), daemon=True, name="defer-collector"),
+                       threading.Thread(target=guarded(self._task_watchdog), daemon=True, name="defer-watchdog"),
+                       threading.Thread(target=guarded(self._startDistEdgeInference, input_stream), daemon=True, name="defer-feeder")]
             for t in threads:
                 t.start()
             self._ready.set()
