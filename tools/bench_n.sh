@@ -1,3 +1,5 @@
+#!/bin/bash
+# bench.py on N GPUs exactly as the driver launches it:  gpurun --gpus N -- 'bash tools/bench_n.sh N'
 cd /root/repo
 N=$1
 timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 30 --warmup 5 --no-cpu-baseline > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err

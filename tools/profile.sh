@@ -1,3 +1,7 @@
+#!/bin/bash
+# Capture recipe behind profiles/r1_*: plain run first, then the ncu launch list, then `ncu --set full` of one step's
+# 54 conv_gemm launches (report kept in /tmp on the box, only CSV exports come back), then the per-op table.
+# Run on a GPU box:  gpurun --timeout 2400 -- 'bash tools/profile.sh' ; then python tools/summarize_profiles.py r1 ...
 cd /root/repo
 set -x
 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-uint8-leg > gpurun_out/prof_plain.json 2> gpurun_out/prof_plain.err || exit 1
