@@ -128,6 +128,25 @@ int encode_tiled_2d_bf16(CUtensorMap* m, const void* base, uint64_t inner, uint6
     return ADAPT_OK;
 }
 
+// Output of the stem-by-phase kernel as a 5-D tensor (channel, column phase, unit column, row, image): pixel
+// q = 4 * unit + phase.  One store = 32 unit columns of one phase of one row; whatever lies beyond Wo / Ho is clipped.
+int encode_phase_out_bf16(CUtensorMap* m, const void* base, int C, int Wo, int Ho, int N) {
+    DriverApi* d;
+    int rc = get_driver(&d);
+    if (rc) return rc;
+    cuuint64_t dims[5] = {(cuuint64_t)C, 4, (cuuint64_t)(Wo / 4), (cuuint64_t)Ho, (cuuint64_t)N};
+    cuuint64_t strides[4] = {(cuuint64_t)C * 2, (cuuint64_t)C * 2 * 4, (cuuint64_t)Wo * C * 2, (cuuint64_t)Ho * Wo * C * 2};
+    cuuint32_t box[5] = {(cuuint32_t)C, 1, 32, 1, 1};
+    cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+    CUtensorMap tmp;
+    CUresult r = d->encodeTiled(&tmp, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(base), dims, strides, box, estr,
+                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return 1;  // the caller keeps the st.global write-out (and its descriptor untouched)
+    *m = tmp;
+    return ADAPT_OK;
+}
+
 // NHWC activation tensor described as (C, W, H, N) for im2col-mode loads of a
 // kh x kw / stride / symmetric-pad convolution; one load = 128 output pixels x 64 channels.
 int encode_im2col_bf16(CUtensorMap* m, const void* base, int C, int W, int H, int N, int kh, int kw, int stride,
@@ -260,6 +279,8 @@ int init_conv_kernels_for_device() {
     SETC(128, A_TILED, 2) SETC(256, A_TILED, 2) SETC(128, A_IM2COL, 2) SETC(256, A_IM2COL, 2)
     SETC(128, A_TILED, 4) SETC(256, A_TILED, 4) SETC(128, A_IM2COL, 4) SETC(256, A_IM2COL, 4)
 #undef SETC
+    CUDA_TRY(cudaFuncSetAttribute(adapt::conv_gemm_kernel<256, adapt::A_S2DP, 1, false>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, adapt::kMaxSmemBytes));
     CUDA_TRY(cudaFuncSetAttribute(adapt::conv_gemm_kernel<64, adapt::A_ROW3, 1, false>,
                                   cudaFuncAttributeMaxDynamicSharedMemorySize, adapt::kMaxSmemBytes));
     CUDA_TRY(cudaFuncSetAttribute(adapt::conv_gemm_kernel<128, adapt::A_ROW3, 2, true>,
@@ -273,6 +294,65 @@ int init_conv_kernels_for_device() {
 }
 
 // Build the launch record (tensor maps + params) for one convolution.
+// Space-to-depth stem by column phase (A_S2DP, conv_gemm_sm100.cuh): 4x4 / stride 1 / VALID over 16-channel pixels
+// stored in rows of whole 128-byte units, 64 output channels.  Returns 1 if the geometry is not this case.
+int build_s2dp_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const void* w_bf16, const float* scale,
+                      const float* bias, void* out, int relu, int num_sms) {
+    if (!(g.kh == 4 && g.kw == 4 && g.Cin == 16 && g.Cout == 64 && g.stride == 1 && g.pad == 0 && g.W % 4 == 0 &&
+          g.Ho <= g.H - 3 && g.Wo <= g.W - 3))
+        return 1;
+    const int units_per_row = g.W / 4;
+    const long long M_walk = (long long)g.batch * g.H * units_per_row;  // one GEMM row per unit of every image row
+    if (M_walk <= 0 || M_walk > 0x7fffffffLL) return 1;
+    adapt::ConvGemmParams& p = L->p;
+    memset(&p, 0, sizeof(p));
+    p.M = (int)M_walk;
+    p.N = g.Cout;
+    p.num_k_blocks = 4;  // one per filter row: 4 taps x 16 channels
+    p.m_tiles = (int)((M_walk + adapt::kBlockM - 1) / adapt::kBlockM);
+    p.n_tiles = 1;
+    p.H = g.H; p.W = g.W; p.Cin = g.Cin; p.Ho = g.Ho; p.Wo = g.Wo;
+    p.kh = 4; p.kw = 4; p.stride = 1; p.pad = 0;
+    p.c_blocks = 1;
+    p.K_real = 256;
+    p.scale = scale;
+    p.bias = bias;
+    p.out_bf16 = reinterpret_cast<__nv_bfloat16*>(out);
+    p.relu = relu;
+    p.in = reinterpret_cast<const __nv_bfloat16*>(in);
+    p.row_pitch = units_per_row;
+    p.row_valid = (g.Wo + 3) / 4;
+    p.epi_tma = 2;  // staged epilogue, st.global write-out maps (unit, phase) to pixels
+    p.b_resident = 1;
+    p.d_out = 1;
+    p.d_res = 0;
+    L->block_n = 256;  // four 64-column accumulators
+    L->a_mode = adapt::A_S2DP;
+    L->cluster = 1;
+    L->pair = false;
+    L->grid = p.m_tiles < num_sms ? p.m_tiles : num_sms;
+    int rc = encode_tiled_2d_bf16(&L->tmap_b, w_bf16, 256, (uint64_t)g.Cout, adapt::kBlockK, 64);
+    if (rc) return rc;
+    rc = encode_tiled_2d_bf16(&L->tmap_a, in, adapt::kBlockK, (uint64_t)M_walk, adapt::kBlockK, adapt::kRow3Rows);
+    if (rc) return rc;
+    L->tmap_out = L->tmap_b;
+    // rows of exactly 32 units (what the ingest writes for 224-pixel images): a warp's 32-row slab is one image row
+    // of one phase, so it can leave through one 5-D TMA store instead
+    if (units_per_row == 32 && g.Wo % 4 == 0 && g.Cout == 64 && env_int("ADAPT_S2DP_TMA_STORE", 1) != 0 &&
+        encode_phase_out_bf16(&L->tmap_out, out, g.Cout, g.Wo, g.Ho, g.batch) == ADAPT_OK) {
+        p.epi_tma = 1;
+        p.d_out = 2;
+    }
+    L->tmap_res = L->tmap_b;
+    const int fixed = 4 * 64 * adapt::kBlockK * 2 + adapt::conv_gemm_epi_bytes(256, p.d_out, 0) + adapt::kBarrierBytes + 1024;
+    int stages = (adapt::kMaxSmemBytes - fixed) / adapt::kRow3ABytes;
+    if (stages > adapt::kMaxStages) stages = adapt::kMaxStages;
+    if (stages < 2) return 1;
+    p.stages = stages;
+    L->smem = fixed + stages * adapt::kRow3ABytes;
+    return ADAPT_OK;
+}
+
 int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const void* w_bf16, const float* scale,
                       const float* bias, const void* residual, void* out, bool out_f32, int relu, int a_mode_req,
                       int block_n_req, int num_sms) {
@@ -284,7 +364,13 @@ int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const vo
     const long long M = (long long)g.batch * g.Ho * g.Wo;
     if (M <= 0 || M > 0x7fffffffLL) return fail(ADAPT_EINVAL, "conv: bad M=%lld", M);
 
+    if ((a_mode_req == adapt::A_S2DP || (a_mode_req < 0 && g_force_a_mode < 0 && env_int("ADAPT_S2DP", 1) != 0)) &&
+        residual == nullptr && !out_f32) {
+        const int rc = build_s2dp_launch(L, g, in, w_bf16, scale, bias, out, relu, num_sms);
+        if (rc <= 0) return rc;  // built (0) or failed (< 0); 1 = not the stem geometry, fall through
+    }
     int a_mode = a_mode_req >= 0 ? a_mode_req : g_force_a_mode;
+    if (a_mode == adapt::A_S2DP) a_mode = -1;
     const bool plain = g.kh == 1 && g.kw == 1 && g.stride == 1 && g.pad == 0;
     if (a_mode < 0) {
         if (g.Cin % 64 != 0)
@@ -567,6 +653,10 @@ cudaError_t launch_conv_ex(const ConvLaunch& L, cudaStream_t s) {
 template <int BN>
 cudaError_t launch_conv_bn(const ConvLaunch& L, cudaStream_t s) {
     if (L.a_mode == adapt::A_GATHER) return launch_conv_ex<BN, adapt::A_GATHER, 1, false>(L, s);
+    if (L.a_mode == adapt::A_S2DP) {
+        if constexpr (BN == 256) return launch_conv_ex<256, adapt::A_S2DP, 1, false>(L, s);
+        return cudaErrorInvalidConfiguration;
+    }
     if (L.a_mode == adapt::A_ROW3) {
         if constexpr (BN == 128) {
             if (L.pair) return launch_conv_ex<128, adapt::A_ROW3, 2, true>(L, s);
@@ -587,6 +677,11 @@ cudaError_t launch_conv_bn(const ConvLaunch& L, cudaStream_t s) {
 }
 
 int run_conv_launch(const ConvLaunch& L, cudaStream_t s) {
+    static const int debug = env_int("ADAPT_DEBUG", 0);
+    if (debug)
+        fprintf(stderr, "[adapt] conv M=%d N=%d kblocks=%d a_mode=%d bn=%d pair=%d cluster=%d grid=%d stages=%d smem=%d b_res=%d epi=%d\n",
+                L.p.M, L.p.N, L.p.num_k_blocks, L.a_mode, L.block_n, (int)L.pair, L.cluster, L.grid, L.p.stages, L.smem,
+                L.p.b_resident, L.p.epi_tma);
     if (L.cluster > 1 && L.block_n < 128) return fail(ADAPT_EINVAL, "conv: clusters need block_n >= 128");
     if (L.block_n == 64)
         CUDA_TRY(launch_conv_bn<64>(L, s));
@@ -775,8 +870,9 @@ int run_steps(adapt_stage* st, const std::vector<Step>& steps, cudaStream_t stre
                 const int threads = 256;
                 if (st->mode == ADAPT_MODE_BF16 && o.Cout == 16) {
                     // space-to-depth ingest for the stem: (H, W, 3) -> (Ho, Wo, 16) with `pad` folded in
-                    if (o.Cin != 3 || o.Ho * 2 != o.H + 2 * o.pad || o.Wo * 2 != o.W + 2 * o.pad)
-                        return fail(ADAPT_EINVAL, "ingest(s2d): expects 3 channels and Ho = (H + 2*pad) / 2");
+                    // (Wo may be wider than the image needs: the extra pixels of each stored row are written as zeros)
+                    if (o.Cin != 3 || o.Ho * 2 != o.H + 2 * o.pad || o.Wo * 2 < o.W + 2 * o.pad)
+                        return fail(ADAPT_EINVAL, "ingest(s2d): expects 3 channels, Ho = (H + 2*pad) / 2, Wo >= (W + 2*pad) / 2");
                     const long long outs = (long long)B * o.Ho * o.Wo;
                     const unsigned blocks = (unsigned)((outs + threads - 1) / threads);
                     __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(s.out);

@@ -41,7 +41,16 @@ namespace adapt {
 // each row are discarded), so that tap s of output position m is input position m + s of the same walk: one
 // im2col load of 128 + 2 (rounded to 136) positions per (filter row, channel block) feeds three k-blocks
 // through descriptors whose start is shifted by s pixel rows.  The A bytes an SM ingests drop 3x.
-enum AMode : int { A_TILED = 0, A_IM2COL = 1, A_GATHER = 2, A_ROW3 = 3 };
+//
+// A_S2DP: the space-to-depth stem (4x4 / stride 1 over 16-channel pixels, 64 output channels) by column PHASE.
+// The image rows are stored 4k pixels wide, so the image is a sequence of 128-byte UNITS of four pixels.  An
+// output pixel q = 4j + phi needs pixels q .. q+3 of filter row r, i.e. the 32-byte chunks phi .. phi+3 counted
+// from unit j: chunk (phi + s) lives in unit row (phi+s)/4 at byte ((phi+s) mod 4) * 32.  One plain 2-D load of
+// 128 + 1 (rounded to 136) consecutive units per filter row therefore serves 128 output positions j of ALL FOUR
+// phases -- 512 output pixels -- through descriptors shifted by whole rows and by K-chunks, into four 64-column
+// accumulators (the "wide pixel" im2col path fetches the same bytes four times, at 32-byte offsets).  The walk
+// runs over units of all H rows (output rows >= Ho and the unit column beyond Wo are discarded).
+enum AMode : int { A_TILED = 0, A_IM2COL = 1, A_GATHER = 2, A_ROW3 = 3, A_S2DP = 4 };
 
 struct ConvGemmParams {
     int M;             // output pixels in this launch: batch * Ho * Wo
@@ -165,8 +174,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     static_assert(!PAIR || CL == 2, "a CTA pair is a cluster of two");
     static_assert(A_MODE != A_ROW3 || CL == 1 || PAIR, "row-reuse mode: single CTA or CTA pair");
     constexpr bool ROW3 = A_MODE == A_ROW3;
-    constexpr int kBBytes = (PAIR ? BLOCK_N / 2 : BLOCK_N) * kBlockK * 2;
-    constexpr int kATile = ROW3 ? kRow3ABytes : kABytes;  // A bytes per stage
+    constexpr bool S2DP = A_MODE == A_S2DP;
+    static_assert(!S2DP || (BLOCK_N == 256 && CL == 1 && !PAIR), "stem-by-phase: four 64-column accumulators, single CTA");
+    constexpr int kMmaN = S2DP ? 64 : BLOCK_N;  // N of one tcgen05.mma
+    constexpr int kBBytes = (PAIR ? kMmaN / 2 : kMmaN) * kBlockK * 2;
+    constexpr int kATile = (ROW3 || S2DP) ? kRow3ABytes : kABytes;  // A bytes per stage
     constexpr int kBPerStage = ROW3 ? 3 : 1;              // B tiles (k-blocks) per stage
     constexpr int kStageBytes = kATile + kBPerStage * kBBytes;
     constexpr int kTmemCols = 2 * BLOCK_N;  // double-buffered accumulator (power of 2 >= 32)
@@ -272,7 +284,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         int mb = 0, nb = 0;
         bool mv = true;
         if (tile_at(0, mb, nb, mv)) {
-            const int rows = PAIR ? BLOCK_N / 2 : (CL == 1 ? BLOCK_N : BLOCK_N / CL);
+            const int rows = PAIR ? BLOCK_N / 2 : (CL == 1 ? kMmaN : BLOCK_N / CL);
             const int row0 = nb * BLOCK_N + (CL > 1 ? cl_rank * rows : 0);
             const int nkb = p.num_k_blocks < kStages ? p.num_k_blocks : kStages;
             for (int kb = 0; kb < nkb; ++kb) ptx::tma_prefetch_2d(&tmap_b, kb * kBlockK, row0);
@@ -291,6 +303,27 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         bool m_valid = true;
         for (long long ti = 0; tile_at(ti, m_blk_raw, n_blk, m_valid); ++ti) {
             const int m_blk = m_valid ? m_blk_raw : p.m_tiles - 1;  // overhanging CTA: re-load a valid tile
+            if constexpr (S2DP) {
+                // one filter row per stage: 136 consecutive units starting at this tile's first unit, r rows down;
+                // the whole weight matrix (4 k-blocks of 64 x 64) arrives with the CTA's first tile and stays
+                for (int r4 = 0; r4 < k_iters; ++r4) {
+                    ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+                    if (ptx::elect_one()) {
+                        if (r4 == 0) stamp(ti, TR_PROD_FIRST);
+                        if (r4 == k_iters - 1) stamp(ti, TR_PROD_LAST);
+                        const bool load_b = ti == 0;
+                        ptx::mbar_expect_tx(&full_bar[stage], kATile + (load_b ? kBBytes : 0));
+                        ptx::tma_load_2d(smem_a + stage * kATile, &tmap_a, &full_bar[stage], 0, m_blk * kBlockM + r4 * p.row_pitch);
+                        if (load_b) ptx::tma_load_2d(smem_b + r4 * kBBytes, &tmap_b, &full_bar[stage], r4 * kBlockK, 0);
+                    }
+                    __syncwarp();
+                    if (++stage == kStages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+                continue;
+            }
             if constexpr (ROW3) {
                 // start of this tile in the padded-flat walk: position q0 of row p0 of image img0
                 const int m0 = m_blk * kBlockM;
@@ -418,7 +451,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         }
     } else if (warp_idx == 1) {
         // ===================== MMA issuer =====================
-        constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(PAIR ? 2 * kBlockM : kBlockM, BLOCK_N);
+        constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(PAIR ? 2 * kBlockM : kBlockM, kMmaN);
         int stage = 0;
         uint32_t phase = 0;
         int m_blk_u = 0, n_blk_u = 0;
@@ -432,6 +465,37 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             ptx::tc_fence_after();
             if (lane == 0) stamp(tile_iter, TR_MMA_START);
             const uint32_t tmem_d = tmem_base + acc_stage * BLOCK_N;
+            if constexpr (S2DP) {
+                for (int r4 = 0; r4 < k_iters; ++r4) {
+                    ptx::mbar_wait(&full_bar[stage], phase);
+                    ptx::tc_fence_after();
+                    if (r4 == 0 && lane == 0) stamp(tile_iter, TR_MMA_FIRST);
+                    if (ptx::elect_one()) {
+                        const uint32_t a_base = ptx::smem_u32(smem_a + stage * kATile);
+                        const uint64_t b_desc = ptx::make_kmajor_sw128_desc(ptx::smem_u32(smem_b + r4 * kBBytes));
+#pragma unroll
+                        for (int phi = 0; phi < 4; ++phi) {      // column phase: accumulator phi
+#pragma unroll
+                            for (int s4 = 0; s4 < 4; ++s4) {     // filter column = 32-byte chunk (phi + s) from unit j
+                                const int chunk = phi + s4;
+                                const uint64_t a_desc =
+                                    ptx::make_kmajor_sw128_desc(a_base + (chunk >> 2) * (kBlockK * 2) + (chunk & 3) * 32);
+                                ptx::umma_bf16_ss(tmem_d + phi * kMmaN, a_desc, b_desc + 2 * s4, idesc, (r4 | s4) != 0 ? 1u : 0u);
+                            }
+                        }
+                        ptx::umma_commit(&empty_bar[stage]);
+                        if (r4 == k_iters - 1) {
+                            ptx::umma_commit(&tmem_full_bar[acc_stage]);
+                            stamp(tile_iter, TR_MMA_DONE);
+                        }
+                    }
+                    __syncwarp();
+                    if (++stage == kStages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+            }
             if constexpr (ROW3) {
                 int tap_r3 = 0, cb3 = 0;
                 for (int it = 0; it < k_iters; ++it) {
@@ -481,7 +545,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     }
                 }
             }
-            if constexpr (!ROW3) for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+            if constexpr (!ROW3 && !S2DP) for (int kb = 0; kb < p.num_k_blocks; ++kb) {
                 ptx::mbar_wait(&full_bar[stage], phase);
                 ptx::tc_fence_after();
                 if (kb == 0 && lane == 0) stamp(tile_iter, TR_MMA_FIRST);
@@ -586,7 +650,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 const int n_tile0 = n_blk * BLOCK_N;
                 const bool slab_ok = m_valid && m_row0 < p.M;
                 // this tile's scale / bias -> per-warp smem (read back as broadcasts)
-                for (int i = lane; i < BLOCK_N / 4; i += 32) {
+                for (int i = lane; i < kMmaN / 4; i += 32) {  // (stem-by-phase: the four accumulators share 64 channels)
                     ptx::sts128f(scale_sa + i * 16, __ldg(reinterpret_cast<const float4*>(p.scale + n_tile0) + i));
                     ptx::sts128f(bias_sa + i * 16, __ldg(reinterpret_cast<const float4*>(p.bias + n_tile0) + i));
                 }
@@ -632,8 +696,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         if (p.epi_tma == 1 && lane == 0) epi_store_wait_read(static_cast<int>(ring) - 1);
                         __syncwarp();
                     }
-                    const uint32_t sc = scale_sa + c * kEpiCols * 4;
-                    const uint32_t bi = bias_sa + c * kEpiCols * 4;
+                    const uint32_t sc = scale_sa + (S2DP ? 0 : c * kEpiCols * 4);
+                    const uint32_t bi = bias_sa + (S2DP ? 0 : c * kEpiCols * 4);
                     auto drain = [&](auto relu_tag) {
                         constexpr bool kRelu = decltype(relu_tag)::value;
 #pragma unroll
@@ -676,13 +740,48 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     __syncwarp();
                     if (p.epi_tma == 1) {
                         if (lane == 0) {
-                            ptx::tma_store_2d(&tmap_out, slab_ptr, n_tile0 + c * kEpiCols, m_row0);
+                            if constexpr (S2DP) {
+                                // rows of exactly 32 units: this warp's slab is one image row of phase c; the unit
+                                // columns past Wo and the walk's rows past Ho fall outside the tensor and are clipped
+                                const int walk_row = m_row0 >> 5;
+                                const int img = walk_row / p.H;
+                                ptx::tma_store_5d(&tmap_out, slab_ptr, 0, c, 0, walk_row - img * p.H, img);
+                            } else {
+                                ptx::tma_store_2d(&tmap_out, slab_ptr, n_tile0 + c * kEpiCols, m_row0);
+                            }
                             ptx::tma_store_commit();
                         }
                     } else {
                         // coalesced write-out: 8 lanes cover one 128-byte row segment, 4 rows per instruction
                         const int ch = lane & 7;
-                        if constexpr (ROW3) {
+                        if constexpr (S2DP) {
+                            // chunk c is column phase c: unit position m -> (image, row, unit column j) -> pixel 4j + c.
+                            // Rows past Ho and the unit column past Wo exist only in the walk.
+                            __nv_bfloat16* gcol = p.out_bf16 + ch * 8;
+                            int m = m_row0 + (lane >> 3);
+                            int rest = m / p.row_pitch;
+                            int j = m - rest * p.row_pitch;
+                            int img = rest / p.H;
+                            int prow = rest - img * p.H;
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                const int row = i * 4 + (lane >> 3);
+                                const uint4 val = ptx::lds128(slab + row * 128 + ((ch ^ (row & 7)) << 4));
+                                const int q = 4 * j + c;
+                                if (m < p.M && prow < p.Ho && q < p.Wo)
+                                    *reinterpret_cast<uint4*>(
+                                        gcol + ((static_cast<size_t>(img) * p.Ho + prow) * p.Wo + q) * p.N) = val;
+                                m += 4;
+                                j += 4;
+                                while (j >= p.row_pitch) {  // (rows narrower than four units wrap more than once)
+                                    j -= p.row_pitch;
+                                    if (++prow == p.H) {
+                                        prow = 0;
+                                        ++img;
+                                    }
+                                }
+                            }
+                        } else if constexpr (ROW3) {
                             // padded-flat position -> output pixel; the two overhang positions of every row are dropped
                             __nv_bfloat16* gcol = p.out_bf16 + n_tile0 + c * kEpiCols + ch * 8;
                             int m = m_row0 + (lane >> 3);

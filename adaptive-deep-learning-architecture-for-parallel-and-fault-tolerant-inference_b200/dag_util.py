@@ -178,6 +178,12 @@ def is_s2d_stem(model: Model, l: Layer) -> bool:
     return img.class_name == "InputLayer" and c == 3 and h % 2 == 0 and w % 2 == 0
 
 
+def s2d_pitch(w: int) -> int:
+    """Stored row width (pixels) of the space-to-depth image: whole 128-byte units of four pixels, and exactly 32
+    units when the image fits (then a 32-row epilogue slab of the stem kernel is one image row)."""
+    return 128 if w <= 128 else (w + 3) // 4 * 4
+
+
 def s2d_kernel(k: np.ndarray) -> np.ndarray:
     """(7,7,3,Cout) stride-2 kernel -> (4,4,16,Cout) stride-1 kernel over the space-to-depth image whose
     channel (py*2+px)*3+c holds padded pixel (2*hh+py, 2*ww+px, c); taps with r or s == 7 and the four pad
@@ -333,8 +339,10 @@ def compile_part(part: PartModel, windex: Dict[str, int], mode: int = N.MODE_BF1
                 s2d_pad = l0.name
         if s2d_pad is not None:
             hp, wp = h + 6, w + 6
-            t0 = new_t((hp // 2) * (wp // 2) * 16, N.DT_WORK, part.start + ":s2d")
-            ops.append(Op(N.OP_INGEST, t_in, t0, H=h, W=w, Cin=c, Ho=hp // 2, Wo=wp // 2, Cout=16, pad=3,
+            # rows are stored S2D_PITCH(wp // 2) pixels wide (zero beyond the image): whole 128-byte units of four
+            # 16-channel pixels, which is what the stem's phase-decomposed loads walk
+            t0 = new_t((hp // 2) * s2d_pitch(wp // 2) * 16, N.DT_WORK, part.start + ":s2d")
+            ops.append(Op(N.OP_INGEST, t_in, t0, H=h, W=w, Cin=c, Ho=hp // 2, Wo=s2d_pitch(wp // 2), Cout=16, pad=3,
                           in_format=input_format, layers=[part.start, s2d_pad]))
             done.add(s2d_pad)
             val[s2d_pad] = t0
@@ -381,7 +389,7 @@ def compile_part(part: PartModel, windex: Dict[str, int], mode: int = N.MODE_BF1
                     # 7x7 stride-2 stem as a 4x4 stride-1 VALID convolution over the space-to-depth image
                     src_t = val[src_name]
                     hp, wp, _ = shape_of(src_name)
-                    h, w, cin = hp // 2, wp // 2, 16
+                    h, w, cin = hp // 2, s2d_pitch(wp // 2), 16   # (stored width; the output size comes from the layer)
                     k, stride, pad = 4, 1, 0
                 elif src_name in pend_pad:
                     src_t, pad = pend_pad[src_name]

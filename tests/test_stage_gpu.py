@@ -58,6 +58,9 @@ CONV_CASES = [
     (16, 14, 14, 256, 256, 3, 1, 1, False, True, -1),  # auto: tensor-bound 3x3 -> im2col on CTA pairs
     (8, 28, 28, 128, 512, 1, 1, 0, True, True, -1),    # auto: 1x1 + residual, slabs used in place
     (7, 56, 56, 256, 64, 1, 1, 0, False, True, -1),    # auto: single n-tile, resident B (172 tiles)
+    (3, 20, 24, 16, 64, 4, 1, 0, False, True, 4),      # stem by column phase (A_S2DP): tiles cross rows and images
+    (2, 115, 116, 16, 64, 4, 1, 0, False, True, -1),   # auto: the space-to-depth stem geometry -> A_S2DP
+    (2, 9, 8, 16, 64, 4, 1, 0, False, False, 4),       # A_S2DP, rows narrower than four units
 ]
 
 

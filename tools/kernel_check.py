@@ -84,8 +84,15 @@ CASES = {
         ("r3_rect", 3, 20, 36, 64, 128, 3, 1, 1, 0, 1, 0),
         ("r3_b1", 1, 14, 14, 64, 64, 3, 1, 1, 0, 0, 0),
     ],
+    # space-to-depth stem by column phase (A_S2DP): rows of whole 4-pixel units; tiles crossing rows and images
+    "s2dp": [
+        ("sp_small", 5, 20, 24, 16, 64, 4, 1, 0, 0, 1, 0),
+        ("sp_b1", 1, 115, 116, 16, 64, 4, 1, 0, 0, 1, 0),
+        ("sp_b3", 3, 115, 116, 16, 64, 4, 1, 0, 0, 0, 0),
+        ("sp_narrow", 2, 9, 8, 16, 64, 4, 1, 0, 0, 1, 0),
+    ],
 }
-MODE = {"tiled": 0, "im2col": 1, "gather": 2, "pair_tiled": 0, "pair_im2col": 1, "row3": 3}
+MODE = {"tiled": 0, "im2col": 1, "gather": 2, "pair_tiled": 0, "pair_im2col": 1, "row3": 3, "s2dp": 4}
 
 
 def run_group(group: str) -> int:
@@ -169,7 +176,7 @@ def run_perf() -> int:
         ("conv5_1x1_512_2048", 7, 7, 512, 2048, 1, 1, 0),
         ("conv3_s2_256_128", 56, 56, 256, 128, 1, 2, 0),
         ("stem_gather", 224, 224, 8, 64, 7, 2, 3),
-        ("stem_s2d", 115, 115, 16, 64, 4, 1, 0),
+        ("stem_s2d", 115, 116, 16, 64, 4, 1, 0),
         ("conv2_3_res", 56, 56, 64, 256, 1, 1, 0, 1),
         ("conv3_3_res", 28, 28, 128, 512, 1, 1, 0, 1),
         ("conv4_3_res", 14, 14, 256, 1024, 1, 1, 0, 1),
@@ -291,7 +298,7 @@ def main() -> int:
     if args.group:
         return run_group(args.group)
     rc_all = 0
-    groups = os.environ.get("KC_GROUPS", "tiled,im2col,gather,pair_tiled,pair_im2col,row3,perf").split(",")
+    groups = os.environ.get("KC_GROUPS", "tiled,im2col,gather,pair_tiled,pair_im2col,row3,s2dp,perf").split(",")
     for g in groups:
         t0 = time.time()
         p = subprocess.run([sys.executable, os.path.abspath(__file__), "--group", g], timeout=600)
