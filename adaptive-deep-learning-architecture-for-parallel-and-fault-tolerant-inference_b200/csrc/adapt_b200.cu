@@ -199,6 +199,18 @@ int encode_row3_bf16(CUtensorMap* m, const void* base, int C, int W, int H, int 
     return ADAPT_OK;
 }
 
+// True only when `ptr` is plain device memory allocated on `device` itself (not a peer GPU's allocation, not a
+// CUDA-IPC mapping of one, not host or managed memory).  Used to decide whether a caller-provided weight tensor
+// may be the source of a cluster-multicast TMA load.
+bool pointer_is_local_device_memory(const void* ptr, int device) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, ptr) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeDevice && a.device == device;
+}
+
 // ---------------------------------------------------------------- conv launch records
 struct ConvGeom {
     int batch, H, W, Cin, Ho, Wo, Cout, kh, kw, stride, pad;
@@ -353,9 +365,13 @@ int build_s2dp_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const vo
     return ADAPT_OK;
 }
 
+// `w_local`: the weight tensor is known to be an allocation of the GPU the kernel runs on.  The optional
+// cluster variant multicasts the B operand (ADAPT_CLUSTER=2/4); TMA multicast loads here read only this GPU's
+// memory, since on B200 a TMA multicast load from another GPU's memory hung the GPU.  Without that knowledge
+// the launch never multicasts.
 int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const void* w_bf16, const float* scale,
                       const float* bias, const void* residual, void* out, bool out_f32, int relu, int a_mode_req,
-                      int block_n_req, int num_sms) {
+                      int block_n_req, int num_sms, bool w_local) {
     if (g.Cin % 8 != 0) return fail(ADAPT_EINVAL, "conv: stored Cin=%d must be a multiple of 8", g.Cin);
     if (g.Cout % 8 != 0) return fail(ADAPT_EINVAL, "conv: Cout=%d must be a multiple of 8", g.Cout);
     if (g_force_a_mode == -2) g_force_a_mode = env_int("ADAPT_FORCE_A_MODE", -1);
@@ -448,7 +464,7 @@ int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const vo
     // Thread-block clusters with a multicast B operand for the layers that are bound by L2 -> SM traffic
     // (tensor-bound class, TMA A path, bf16 output whose width the tile divides).
     int cluster = 1;
-    if (!memory_bound && a_mode != adapt::A_GATHER && bn >= 128 && !out_f32 && g.Cout % bn == 0 &&
+    if (w_local && !memory_bound && a_mode != adapt::A_GATHER && bn >= 128 && !out_f32 && g.Cout % bn == 0 &&
         env_int("ADAPT_EPI_MODE", 1) != 0) {
         // Measured on B200 (profiles/): multicasting B does not speed these layers up -- they are bound by
         // shared-memory bandwidth (TMA fills + MMA operand reads), not by L2 -> SM traffic -- so it is off by
@@ -847,8 +863,9 @@ int build_steps(adapt_stage* st, Plan* plan, int slot) {
         if (o.kind == ADAPT_OP_CONV && st->mode == ADAPT_MODE_BF16) {
             const WeightDev& w = st->weights[o.weight];
             ConvGeom g{plan->batch, o.H, o.W, o.Cin, o.Ho, o.Wo, o.Cout, o.kh, o.kw, o.stride, o.pad};
+            // (w.kernel is this stage's own cudaMalloc on st->device: upload_weights)
             int rc = build_conv_launch(&s.conv, g, s.in, w.kernel, w.scale, w.bias, s.res, s.out, o.out_f32 != 0,
-                                       o.relu, -1, 0, st->num_sms);
+                                       o.relu, -1, 0, st->num_sms, /*w_local=*/true);
             if (rc) return rc;
         }
         steps.push_back(s);
@@ -1262,7 +1279,8 @@ int adapt_conv2d_bf16(int device, const void* in, const void* w, const float* sc
     if (Ho <= 0 || Wo <= 0) return fail(ADAPT_EINVAL, "conv2d: empty output");
     ConvGeom g{batch, H, W, Cin, Ho, Wo, Cout, kh, kw, stride, pad};
     ConvLaunch L;
-    rc = build_conv_launch(&L, g, in, w, scale, bias, residual, out, out_is_f32 != 0, relu, a_mode, block_n, num_sms);
+    rc = build_conv_launch(&L, g, in, w, scale, bias, residual, out, out_is_f32 != 0, relu, a_mode, block_n, num_sms,
+                           pointer_is_local_device_memory(w, device));
     if (rc) return rc;
     // Developer timeline (tools/kernel_check.py --group trace): with ADAPT_TRACE_FILE set, every call of this
     // entry point runs synchronously and appends the per-CTA, per-tile role timestamps to that file.
@@ -1353,7 +1371,8 @@ int adapt_dense_softmax_noalloc(int device, const void* in, const void* w, const
     // element of logits[0 : batch*cout) is overwritten, so nothing has to be cleared first) ...
     ConvGeom g{batch, 1, 1, cin, 1, 1, cout, 1, 1, 1, 0};
     ConvLaunch L;
-    rc = build_conv_launch(&L, g, in, w, scale, bias, nullptr, logits, /*out_f32=*/true, /*relu=*/0, -1, 0, num_sms);
+    rc = build_conv_launch(&L, g, in, w, scale, bias, nullptr, logits, /*out_f32=*/true, /*relu=*/0, -1, 0, num_sms,
+                           /*w_local=*/false);  // (fp32 logits never take the cluster variant anyway)
     if (rc) return rc;
     rc = run_conv_launch(L, stream);
     if (rc) return rc;

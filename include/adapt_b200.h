@@ -157,6 +157,9 @@ void adapt_stage_destroy(adapt_stage_t* stage);
  * a_mode: -1 auto, 0 tiled TMA, 1 im2col TMA, 2 software gather, 3 row reuse (3x3 / stride 1 / pad 1 without
  * residual only; other shapes fall back to im2col), 4 stem by column phase (4x4 / stride 1 / VALID, 16 -> 64
  * channels, W a multiple of 4; other shapes fall back).  block_n: 0 auto, 64/128/256.
+ * The optional cluster variant (ADAPT_CLUSTER=2/4) multicasts the weight tile; it is taken only when `w` is plain
+ * device memory allocated on `device` itself (TMA multicast loads here read only this GPU's memory, since on B200 a
+ * TMA multicast load from another GPU's memory hung the GPU).  Any other `w` runs without multicast.
  * Stands in for one Conv2D+BatchNormalization(+Add)(+ReLU) group inside `model.predict`
  * (reference src/node.py:177). */
 int adapt_conv2d_bf16(int device, const void* in, const void* w, const float* scale, const float* bias,
