@@ -17,6 +17,7 @@
 #include <cstring>
 #include <map>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -303,6 +304,19 @@ int init_conv_kernels_for_device() {
     SETP(128, A_TILED) SETP(256, A_TILED) SETP(128, A_IM2COL) SETP(256, A_IM2COL)
 #undef SETP
     return ADAPT_OK;
+}
+
+// Per-device one-time set-up of the conv kernels' attributes, for the entry points that have no stage handle;
+// callers on different threads may race to be first, so the bookkeeping is locked.
+int init_conv_kernels_once(int device) {
+    static std::mutex mu;
+    static bool done[64] = {false};
+    if (device < 0 || device >= 64) return init_conv_kernels_for_device();
+    std::lock_guard<std::mutex> lock(mu);
+    if (done[device]) return ADAPT_OK;
+    const int rc = init_conv_kernels_for_device();
+    if (rc == ADAPT_OK) done[device] = true;
+    return rc;
 }
 
 // Build the launch record (tensor maps + params) for one convolution.
@@ -1266,12 +1280,8 @@ int adapt_conv2d_bf16(int device, const void* in, const void* w, const float* sc
         return fail(ADAPT_EINVAL, "conv2d: bad geometry");
     int rc = require_device(device);
     if (rc) return rc;
-    static bool attr_done[64] = {false};
-    if (device < 64 && !attr_done[device]) {
-        rc = init_conv_kernels_for_device();
-        if (rc) return rc;
-        attr_done[device] = true;
-    }
+    rc = init_conv_kernels_once(device);
+    if (rc) return rc;
     int num_sms = 0;
     CUDA_TRY(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, device));
     const int Ho = (H + 2 * pad - kh) / stride + 1;
@@ -1325,9 +1335,11 @@ namespace {
 // stand-in symbol, never an address a kernel could use, so the real address is looked up once
 // per device (with that device current) and cached.
 float* g_noalloc_logits_addr[64] = {nullptr};
+std::mutex g_noalloc_mu;  // first calls on one device from several threads
 
 int noalloc_scratch(int device, float** out) {
     if (device < 0 || device >= 64) return fail(ADAPT_EINVAL, "noalloc: device %d unsupported", device);
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
     if (g_noalloc_logits_addr[device] == nullptr) {
         float* ptr = nullptr;
         cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_noalloc_logits);
@@ -1353,14 +1365,14 @@ int adapt_dense_softmax_noalloc(int device, const void* in, const void* w, const
                     "dense_softmax_noalloc: batch %d x cout %d = %lld logits exceeds the fixed scratch of %d floats "
                     "(ADAPT_NOALLOC_MAX_LOGITS); split the batch or use the stage API",
                     batch, cout, (long long)batch * cout, (int)ADAPT_NOALLOC_MAX_LOGITS);
+    // the kernels read these with 16-byte vector loads / TMA: a caller carving them out of its own arena must keep
+    // that alignment (a misaligned address is a sticky fault of the whole context, so it is refused here)
+    if (((uintptr_t)in | (uintptr_t)w | (uintptr_t)scale | (uintptr_t)bias | (uintptr_t)probs) & 15)
+        return fail(ADAPT_EINVAL, "dense_softmax_noalloc: in, w, scale, bias and probs must be 16-byte aligned");
     int rc = require_device(device);
     if (rc) return rc;
-    static bool attr_done[64] = {false};
-    if (device < 64 && !attr_done[device]) {  // first call on this device: one-time set-up, no allocation
-        rc = init_conv_kernels_for_device();
-        if (rc) return rc;
-        attr_done[device] = true;
-    }
+    rc = init_conv_kernels_once(device);  // first call on this device: one-time set-up
+    if (rc) return rc;
     float* logits = nullptr;
     rc = noalloc_scratch(device, &logits);
     if (rc) return rc;

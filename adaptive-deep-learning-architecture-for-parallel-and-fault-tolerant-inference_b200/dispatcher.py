@@ -31,8 +31,8 @@ from . import _native as N
 from .dag_util import PartModel, construct_model, layer_macs
 from .fabric import (G_EPOCH, G_NWORKERS, G_PHASE, G_T0, G_T1, G_TIMING_REQ, KIND_DATA, KIND_PINNED, KIND_RESIDENT, KIND_STOP,
                      W_ELAPSED_US, W_TIMING_ACK, MAX_WORKERS, PHASE_CONFIGURE, PHASE_INIT,
-                     PHASE_QUIESCE, PHASE_RUN, PHASE_SHUTDOWN, POISON, W_ACK_QUIESCE, W_ACK_READY, W_KILL, W_STATE,
-                     ControlRing, CudaBackend, HealthTable, ResultRing, ShmRegion, StateEnum)
+                     PHASE_QUIESCE, PHASE_RUN, PHASE_SHUTDOWN, FLAG_BASE_STEP, W_ACK_QUIESCE, W_ACK_READY, W_KILL, W_STATE,
+                     ControlRing, CudaBackend, HealthTable, ResultRing, ShmRegion, StateEnum, poison_value)
 from .node import IMAGE_BYTES, OUT_ROW_BYTES, StageWorker, arena_slot_bytes
 
 # ports of the reference protocol (src/dispatcher.py:15-17); unused on a single NVSwitch box,
@@ -198,6 +198,9 @@ class DEFER:
         self._next_deliver = 0
         self._k_feed = 0
         self._k_collect = 0
+        self._flag_base = 0x100       # flag values of the current epoch are flag_base + k + 1 (see _reconfigure)
+        self._collect_base = 0x100
+        self._dropped: set = set()    # workers that held a stage and lost it (candidates for elastic re-join)
         self._ready = threading.Event()
         self._kill_time: Optional[float] = None
         self._region: Optional[ShmRegion] = None
@@ -263,11 +266,17 @@ class DEFER:
 
     def _reconfigure(self, order: List[int], part_at: List[str], first: bool = False) -> None:
         """Two-phase reconfiguration: QUIESCE (everyone drains, nothing stale can land afterwards),
-        then CONFIGURE (flags zeroed, programs re-sliced, neighbours re-wired)."""
+        then CONFIGURE (flags reset to the new base, programs re-sliced, neighbours re-wired)."""
         h = self.health
         epoch = h.epoch + 1
+        # Flag values are `flag_base + k + 1`; the new epoch's base lies beyond everything the old epoch can have
+        # written (its base + the micro-batches fed in it + a margin).  A stage that was dropped while its GPU was
+        # still running (a heartbeat false positive, a stalled process) can therefore write whatever it has queued:
+        # none of it satisfies a wait, or matches a result slot's ready word, of the new epoch.
+        old_base = self._flag_base
+        self._flag_base = (old_base + self._k_feed + FLAG_BASE_STEP) & 0xFFFFFFFF
         h.write_table({"epoch": epoch, "order": order, "part_at": part_at, "warm_batches": self.warm_batches,
-                       "handoff": self.handoff, "ingest_rails": self.ingest_rails})
+                       "handoff": self.handoff, "ingest_rails": self.ingest_rails, "flag_base": self._flag_base})
         h.g[G_EPOCH] = epoch
         active = list(order)
         t_start = time.perf_counter()
@@ -276,12 +285,24 @@ class DEFER:
             # A worker's host thread can itself be stuck inside a CUDA call that waits for a flag a dead
             # stage will never write (e.g. a pageable host-to-device copy ordered behind such a wait), so
             # the dispatcher releases every flag wait centrally while it collects the acknowledgements.
-            self._wait_acks(active, W_ACK_QUIESCE, epoch, 30.0, poison=True)
+            self._wait_acks(active, W_ACK_QUIESCE, epoch, 30.0, poison=poison_value(old_base))
+            # Workers that lost their stage but whose process still beats (declared dead on a late heartbeat, or
+            # never part of the order) drain too; they are given a bounded moment to say so.  Whoever stays silent
+            # is covered by the flag base above.
+            others = [w for w in range(self._n_workers) if w not in active and not int(h.w[w, W_KILL])
+                      and h.age_ms(w) <= 4 * self.heartbeat_timeout * 1e3 and int(h.w[w, W_STATE]) != StateEnum.ERROR]
+            if others:
+                try:
+                    self._wait_acks(others, W_ACK_QUIESCE, epoch, max(0.25, 4 * self.heartbeat_timeout),
+                                    poison=poison_value(old_base))
+                except (TimeoutError, RuntimeError):
+                    self.stats["unacked_bystanders"] = self.stats.get("unacked_bystanders", 0) + 1
         t_quiesced = time.perf_counter()
         h.g[G_PHASE] = PHASE_CONFIGURE
         with self._collect_lock:  # the collector is between iterations: safe to reset its cursor
             self.results.reset()
             self._k_collect = 0
+            self._collect_base = self._flag_base
         for r in self.rings:
             r.clear()
         # (graph capture + warm-up happen here; under a profiler that replays every kernel it takes minutes)
@@ -293,11 +314,11 @@ class DEFER:
         self.stats.setdefault("reconfig_phases_ms", []).append(
             {"quiesce": round((t_quiesced - t_start) * 1e3, 2), "configure": round((time.perf_counter() - t_quiesced) * 1e3, 2)})
 
-    def _wait_acks(self, wids: List[int], word: int, epoch: int, timeout: float, poison: bool = False) -> None:
+    def _wait_acks(self, wids: List[int], word: int, epoch: int, timeout: float, poison: Optional[int] = None) -> None:
         t0 = time.monotonic()
         while True:
-            if poison:
-                self.flags_host[:, :] = POISON
+            if poison is not None:
+                self.flags_host[:, :] = poison
             pending = [w for w in wids if int(self.health.w[w, word]) != epoch]
             if not pending:
                 return
@@ -388,7 +409,7 @@ class DEFER:
                 return 100e-6
             k = self._k_collect
             r = k % ResultRing.SLOTS
-            if int(res.ready[r][0]) != ((k + 1) & 0xFFFFFFFF):
+            if int(res.ready[r][0]) != ((self._collect_base + k + 1) & 0xFFFFFFFF):
                 return 10e-6
             hdr = res.hdr[r]
             epoch, seq, batch = int(hdr[2]), int(hdr[3]), int(hdr[4])
@@ -427,8 +448,11 @@ class DEFER:
             alive = set(self._get_available_workers())
             dead = [w for w in self.order if w not in alive]
             if not dead:
-                # elastic re-join: a worker that is healthy again but holds no stage is given one
-                joiners = sorted(w for w in alive if w not in self.order and not int(self.health.w[w, W_KILL]))
+                # elastic re-join: a worker that LOST its stage and is healthy again gets one back.
+                # Spare workers (more computeNodes than partitions) never held one: they stay idle -- the caller's
+                # `partition_layers` define the pipeline -- until a fail-over needs them (_failover).
+                joiners = sorted(w for w in alive if w in self._dropped and w not in self.order
+                                 and not int(self.health.w[w, W_KILL]))
                 if joiners:
                     try:
                         self._rejoin(joiners)
@@ -452,11 +476,20 @@ class DEFER:
             self.stats.setdefault("detect_ms", []).append(round((t0 - self._kill_time) * 1e3, 2))
         with self._feed_lock:  # feeder paused
             survivors = [w for w in self.order if w not in dead]
+            self._dropped.update(dead)
+            # idle spares (healthy, never killed, not in the pipeline) step in for the stages that were lost
+            alive = set(self._get_available_workers())
+            spares = sorted(w for w in alive if w not in self.order and w not in dead and w not in self._dropped
+                            and not int(self.health.w[w, W_KILL]))
+            survivors = sorted(survivors + spares[:len(self.order) - len(survivors)])
             if not survivors:
                 raise RuntimeError("no surviving stage")
             if self.order[0] in dead and self.session.get("ipc", False):
                 raise RuntimeError("the dispatcher-local first stage died; inputs cannot be re-routed across processes")
-            part_at = balanced_part_at(self.model, len(survivors))
+            if len(survivors) == len(self._user_part_at) + 1:
+                part_at = list(self._user_part_at)  # the stage count is whole again: the caller's own cut points
+            else:
+                part_at = balanced_part_at(self.model, len(survivors))
             self._reconfigure(survivors, part_at)
             with self.inflight_lock:
                 pending = sorted(self.inflight_tasks.items())
@@ -473,8 +506,12 @@ class DEFER:
         t0 = time.perf_counter()
         with self._feed_lock:  # feeder paused
             order = sorted(set(self.order) | set(joiners))
-            part_at = balanced_part_at(self.model, len(order))
+            if len(order) == len(self._user_part_at) + 1:
+                part_at = list(self._user_part_at)  # back to the stage count the caller cut the model for
+            else:
+                part_at = balanced_part_at(self.model, len(order))
             self._reconfigure(order, part_at)
+            self._dropped.difference_update(joiners)
             with self.inflight_lock:
                 pending = sorted(self.inflight_tasks.items())
             for seq, task in pending:
@@ -535,6 +572,7 @@ class DEFER:
         try:
             self.model = model
             self.models_to_dispatch = self._partition(model, list(partition_layers))  # validates part_at
+            self._user_part_at = list(partition_layers)
             n = len(self.models_to_dispatch)
             if isinstance(self.computeNodes, (str, int)):
                 self.computeNodes = [self.computeNodes]

@@ -28,7 +28,15 @@ import numpy as np
 
 from . import _native as N
 
-POISON = 0x7FFF0000  # flag value that satisfies every outstanding ">= k" wait (cyclic compare)
+# Flag values are `flag_base + k + 1` ("micro-batch k of this epoch done"), compared cyclically on 32 bits
+# (cuStreamWaitValue32 GEQ: (int32)(*flag - value) >= 0).  Every reconfiguration moves the base past anything the old
+# epoch can have written (dispatcher._reconfigure), so values of different epochs never alias.
+FLAG_BASE_STEP = 0x10000     # added on top of the old epoch's highest value
+POISON_OFFSET = 0x40000000   # base + this satisfies every outstanding ">= base + k" wait of the epoch
+
+
+def poison_value(flag_base: int) -> int:
+    return (int(flag_base) + POISON_OFFSET) & 0xFFFFFFFF
 
 
 # ------------------------------------------------------------------------------------------------
@@ -191,7 +199,7 @@ class HealthTable:
 # ------------------------------------------------------------------------------------------------
 class ResultRing:
     """R slots of [int64 header x8 | payload].  The last stage DMA-writes the payload, then a
-    stream-ordered 32-bit write publishes `ready = k + 1`; the dispatcher polls, copies out and
+    stream-ordered 32-bit write publishes `ready = flag_base + k + 1`; the dispatcher polls, copies out and
     sets `free = k + 1`.  header words: 0 ready(u32 in low half), 1 free, 2 epoch, 3 seq, 4 batch."""
 
     SLOTS = 8

@@ -28,9 +28,9 @@ import numpy as np
 from . import _native as N
 from .dag_util import construct_model
 from .fabric import (G_EPOCH, G_PHASE, G_T0, G_T1, G_TIMING_REQ, KIND_DATA, KIND_PINNED, KIND_RESIDENT, KIND_STOP, PHASE_CONFIGURE, PHASE_QUIESCE, PHASE_RUN,
-                     PHASE_SHUTDOWN, POISON, W_ACK_QUIESCE, W_ACK_READY, W_DEVICE, W_ERRORS, W_ELAPSED_US, W_HEARTBEAT, W_KILL, W_LAST_K, W_PID,
+                     PHASE_SHUTDOWN, W_ACK_QUIESCE, W_ACK_READY, W_DEVICE, W_ERRORS, W_ELAPSED_US, W_HEARTBEAT, W_KILL, W_LAST_K, W_PID,
                      W_TIMING_ACK,
-                     ControlRing, CudaBackend, HealthTable, ResultRing, ShmRegion, StateEnum)
+                     ControlRing, CudaBackend, HealthTable, ResultRing, ShmRegion, StateEnum, poison_value)
 
 # uint32 word indices inside a worker's flag block.  Flags live in the pinned, device-mapped
 # control segment (host memory): GPUs write / wait on them with stream memory operations, and the
@@ -103,6 +103,7 @@ class StageWorker:
         self.peers: Dict[int, int] = {}
         self.executor = None
         self.epoch = -1
+        self.fb = 0  # flag base of the current epoch (partition table, `flag_base`)
         self.stage_index = -1
         self.n_stages = 0
         self.prev_wid = self.next_wid = -1
@@ -118,6 +119,13 @@ class StageWorker:
         self.rails: List[dict] = []          # ingest rails ever created (other GPUs' PCIe links)
         self._active_rails: List[dict] = []  # ... of the GPUs in the current stage order
         self.on_kill: Optional[Callable[[], None]] = None
+        # Fault injection for the tests (like `DEFER.inject_kill`): ADAPT_FAULT_INJECT="stale_slot:<k>" makes the LAST
+        # stage of a multi-stage pipeline run micro-batch k of every epoch on the OTHER input slot, i.e. on the
+        # tensor of micro-batch k-1 -- the hand-off bug a value check of the delivered results has to catch.
+        self._fault_stale_k = -1
+        fault = os.environ.get("ADAPT_FAULT_INJECT", "")
+        if fault.startswith("stale_slot:"):
+            self._fault_stale_k = int(fault.split(":")[1])
         if hasattr(self.backend, "abort_check"):  # synchronous test backends must be able to give up a wait
             self.backend.abort_check = lambda: (self.health.phase != PHASE_RUN or bool(self.health.w[self.wid, W_KILL])
                                                 or self._stop.is_set())
@@ -183,7 +191,7 @@ class StageWorker:
         until both streams are idle."""
         t0 = time.monotonic()
         while True:
-            self._write_own_flags(POISON)
+            self._write_own_flags(poison_value(self.fb))
             if not (self.backend.busy(self.copy_stream) or self.backend.busy(self.stream)
                     or self.backend.busy(self.xfer_stream)
                     or any(r["backend"].busy(r["stream"]) for r in getattr(self, "rails", []))):
@@ -200,7 +208,8 @@ class StageWorker:
         table = self.health.read_table()
         assert table["epoch"] == epoch, (table, epoch)
         order: List[int] = table["order"]
-        self._write_own_flags(0)
+        self.fb = int(table.get("flag_base", 0)) & 0xFFFFFFFF
+        self._write_own_flags(self.fb)   # "nothing of this epoch done yet"
         self.ring.clear()
         self.k_expect = 0
         if self.wid not in order:
@@ -221,7 +230,11 @@ class StageWorker:
             self.prev_wid = order[i - 1] if i > 0 else -1
             self.next_wid = order[i + 1] if i + 1 < len(order) else -1
             mode = table.get("handoff", "auto")
-            big = getattr(self.executor, "out_bytes_per_image", 0) >= COPY_HANDOFF_MIN_BYTES
+            out_bytes = getattr(self.executor, "out_bytes_per_image", 0)
+            if self.next_wid >= 0 and self.max_batch * out_bytes > self.slot_bytes:
+                raise RuntimeError(f"cut tensor of {self.max_batch} x {out_bytes} bytes does not fit a {self.slot_bytes}-byte "
+                                   f"hand-off slot (session mode {self.mode!r})")
+            big = out_bytes >= COPY_HANDOFF_MIN_BYTES
             self.handoff_copy = self.next_wid >= 0 and (mode == "copy" or (mode == "auto" and big))
             for s in (0, 1):
                 if self.next_wid < 0:
@@ -281,12 +294,17 @@ class StageWorker:
         kind, epoch, k, seq, batch, aux = rec
         b, ex = self.backend, self.executor
         s = k & 1
+        # flag values of micro-batch k in this epoch: "k done" = flag_base + k + 1 (cyclic 32-bit compare).  The base
+        # moves past everything the previous epoch can have written, so a late write from a stage that was dropped
+        # while still running can never satisfy a wait of this epoch.
+        v_done = (self.fb + k + 1) & 0xFFFFFFFF   # this micro-batch
+        v_prev = (self.fb + k - 1) & 0xFFFFFFFF   # the micro-batch that used slot s before (k - 2)
         first = self.stage_index == 0
         last = self.stage_index == self.n_stages - 1
         if first and (kind & KIND_RESIDENT):
             # measurement mode: the input batch was preloaded into both input slots (no copy); keep the
             # copy-side flag current so that copied micro-batches can follow resident ones
-            b.write_flag(self.stream, self.flag(self.wid, F_H2D_DONE + s), k + 1)
+            b.write_flag(self.stream, self.flag(self.wid, F_H2D_DONE + s), v_done)
         elif first:
             # host -> device copy of the input on the copy stream, double buffered against compute
             nbytes = batch * self.session["in_row_bytes"]
@@ -297,7 +315,7 @@ class StageWorker:
                 # there, i.e. possibly forever behind a flag a dead stage never writes.)
                 fl = self.flags_host[self.wid]
                 t0 = time.monotonic()
-                while k >= 2 and ((int(fl[F_H2D_DONE + s]) - (k - 1)) & 0xFFFFFFFF) >= 0x80000000:
+                while k >= 2 and ((int(fl[F_H2D_DONE + s]) - v_prev) & 0xFFFFFFFF) >= 0x80000000:
                     if self.health.phase != PHASE_RUN or self._stop.is_set():
                         return
                     if time.monotonic() - t0 > 30:
@@ -309,9 +327,9 @@ class StageWorker:
             lane = k % (len(rails) + 1)
             if lane == 0:
                 if k >= 2:
-                    b.wait_flag(self.copy_stream, self.flag(self.wid, F_IN_CONSUMED + s), k - 1)
+                    b.wait_flag(self.copy_stream, self.flag(self.wid, F_IN_CONSUMED + s), v_prev)
                 b.h2d(self.in_buf(self.wid, s), src, nbytes, self.copy_stream)
-                b.write_flag(self.copy_stream, self.flag(self.wid, F_H2D_DONE + s), k + 1)
+                b.write_flag(self.copy_stream, self.flag(self.wid, F_H2D_DONE + s), v_done)
             else:
                 # over GPU j's PCIe link into its staging buffer (no dependency: runs ahead), then -- once this
                 # stage has consumed what the slot held -- one NVLink copy into the input slot
@@ -321,18 +339,18 @@ class StageWorker:
                 rail["count"] += 1
                 rb.h2d(stg, src, nbytes, rs)
                 if k >= 2:
-                    rb.wait_flag(rs, self.flag(self.wid, F_IN_CONSUMED + s), k - 1)
+                    rb.wait_flag(rs, self.flag(self.wid, F_IN_CONSUMED + s), v_prev)
                 rb.d2d(self.in_buf(self.wid, s), stg, nbytes, rs)
-                rb.write_flag(rs, self.flag(self.wid, F_H2D_DONE + s), k + 1)
-            b.wait_flag(self.stream, self.flag(self.wid, F_H2D_DONE + s), k + 1)
+                rb.write_flag(rs, self.flag(self.wid, F_H2D_DONE + s), v_done)
+            b.wait_flag(self.stream, self.flag(self.wid, F_H2D_DONE + s), v_done)
         else:
-            b.wait_flag(self.stream, self.flag(self.wid, F_IN_READY + s), k + 1)
+            b.wait_flag(self.stream, self.flag(self.wid, F_IN_READY + s), v_done)
         staged = (not last) and self.handoff_copy
         if staged and k >= 2:
             # local output slot s is re-used: its copy to the consumer (micro-batch k-2) must be done
-            b.wait_flag(self.stream, self.flag(self.wid, F_OUT_COPIED + s), k - 1)
+            b.wait_flag(self.stream, self.flag(self.wid, F_OUT_COPIED + s), v_prev)
         elif not last and k >= 2:
-            b.wait_flag(self.stream, self.flag(self.wid, F_OUT_FREE + s), k - 1)
+            b.wait_flag(self.stream, self.flag(self.wid, F_OUT_FREE + s), v_prev)
         if last:
             r = k % ResultRing.SLOTS
             hdr = self.results.hdr[r]
@@ -346,33 +364,33 @@ class StageWorker:
         timed = self._timing_events is not None
         if timed and k == int(self.health.g[G_T0]):
             b.event_record(self._timing_events[0], self.stream)
-        ex.enqueue(s, batch, self.stream)
+        ex.enqueue(s ^ 1 if (k == self._fault_stale_k and last and not first) else s, batch, self.stream)
         self.launches += ex.num_launches
         if first:  # (also for resident micro-batches, so that a later copied one finds the flag current)
-            b.write_flag(self.stream, self.flag(self.wid, F_IN_CONSUMED + s), k + 1)
+            b.write_flag(self.stream, self.flag(self.wid, F_IN_CONSUMED + s), v_done)
         else:
-            b.write_flag(self.stream, self.flag(self.prev_wid, F_OUT_FREE + s), k + 1)
+            b.write_flag(self.stream, self.flag(self.prev_wid, F_OUT_FREE + s), v_done)
         if last:
             hdr[2], hdr[3], hdr[4] = epoch, seq, batch
             off = r * self.results.stride
             b.d2h(self.results_dev + off + ResultRing.HDR, self.d_out, batch * OUT_ROW_BYTES, self.stream)
-            b.write_flag(self.stream, self.results_dev + off, k + 1)
+            b.write_flag(self.stream, self.results_dev + off, v_done)
         elif staged:
             # Large cut tensor: the stage wrote it to a LOCAL slot; a copy engine pushes it over NVLink on
             # the transfer stream while this stage's SMs start the next micro-batch (hand-off overlapped
             # with compute instead of stretching the last kernel to NVLink speed).
             x = self.xfer_stream
-            b.write_flag(self.stream, self.flag(self.wid, F_OUT_READY + s), k + 1)
-            b.wait_flag(x, self.flag(self.wid, F_OUT_READY + s), k + 1)
+            b.write_flag(self.stream, self.flag(self.wid, F_OUT_READY + s), v_done)
+            b.wait_flag(x, self.flag(self.wid, F_OUT_READY + s), v_done)
             if k >= 2:
-                b.wait_flag(x, self.flag(self.wid, F_OUT_FREE + s), k - 1)  # consumer done with its slot s
+                b.wait_flag(x, self.flag(self.wid, F_OUT_FREE + s), v_prev)  # consumer done with its slot s
             b.d2d(self.in_buf(self.next_wid, s), self.out_buf(s), batch * self.executor.out_bytes_per_image, x)
-            b.write_flag(x, self.flag(self.wid, F_OUT_COPIED + s), k + 1)
-            b.write_flag(x, self.flag(self.next_wid, F_IN_READY + s), k + 1)
+            b.write_flag(x, self.flag(self.wid, F_OUT_COPIED + s), v_done)
+            b.write_flag(x, self.flag(self.next_wid, F_IN_READY + s), v_done)
             self.rings[self.next_wid].push((kind, epoch, k, seq, batch, 0))
         else:
             # Small cut tensor: the last kernel's epilogue stored it straight into the consumer's slot
-            b.write_flag(self.stream, self.flag(self.next_wid, F_IN_READY + s), k + 1)
+            b.write_flag(self.stream, self.flag(self.next_wid, F_IN_READY + s), v_done)
             self.rings[self.next_wid].push((kind, epoch, k, seq, batch, 0))
         if timed and k == int(self.health.g[G_T1]) - 1:
             b.event_record(self._timing_events[1], self.stream)

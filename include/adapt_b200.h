@@ -175,13 +175,18 @@ int adapt_conv2d_bf16(int device, const void* in, const void* w, const float* sc
  *
  *   probs[b, :] = softmax(in[b, :] @ w^T * scale + bias)      in: bf16 [batch][cin], w: bf16 [cout][cin],
  *                                                              scale/bias: fp32 [cout], probs: fp32 [batch][cout]
- * All pointers are device pointers owned by the caller; cin and cout must be multiples of 8.
+ * All pointers are device pointers owned by the caller and must be 16-byte aligned (the kernels use 128-bit
+ * loads and TMA; a caller sub-allocating from its own arena has to keep that alignment -- anything else is
+ * refused with ADAPT_EINVAL); cin and cout must be multiples of 8.
  * The only intermediate, the fp32 logits, lives in a fixed array inside the library
- * (ADAPT_NOALLOC_MAX_LOGITS floats = 1 MiB per GPU, held from library load to process exit), so the
- * call performs no cudaMalloc / cudaFree and calls no allocating library routine.
+ * (ADAPT_NOALLOC_MAX_LOGITS floats = 1 MiB per GPU), so the call performs no cudaMalloc / cudaFree and calls no
+ * allocating library routine.  The array is part of the library's device code: the CUDA runtime reserves it
+ * when it loads that code on a device (with lazy loading, at the first call that touches it there) and keeps it
+ * until the process exits -- so make one warm-up call per device while memory is still available.
  *   - LIMIT: batch * cout <= ADAPT_NOALLOC_MAX_LOGITS, otherwise ADAPT_EINVAL with a message.
- *   - The first call on each device looks up the array's device address and sets kernel attributes
- *     (no allocation); make that first call before starting any stream capture.
+ *   - The first call on each device looks up the array's device address and sets kernel attributes; make that
+ *     first call before starting any stream capture.  First calls racing from several threads are serialised
+ *     inside the library.
  *   - Every call uses the same array and leaves its logits there.  Nothing needs clearing (each call
  *     overwrites all batch * cout entries it reads), but two calls whose GPU work overlaps -- different
  *     streams, or different threads -- race on it: serialise them on one stream. */

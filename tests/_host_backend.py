@@ -123,6 +123,9 @@ class HostBackend:
         ctypes.memset(dst, value, int(nbytes))
 
     def make_executor(self, model, part, mode, max_batch, input_format="float32"):
+        # cut tensors move as fp32 here; the session's hand-off slots are sized for its mode's element size
+        if mode not in ("fp32", "fp32-check"):
+            raise ValueError("the host test backend moves fp32 activations: run the session with mode='fp32'")
         return HostExecutor(model, part, max_batch, self.delay, input_format)
 
     def close(self):

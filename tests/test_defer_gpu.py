@@ -11,10 +11,9 @@ os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")  # several stages' st
 import numpy as np  # noqa: E402
 import pytest  # noqa: E402
 
-from _util import KO, oracle_for  # noqa: E402
+from _util import KO, StreamChecker, distinct_images  # noqa: E402
 
 pytestmark = pytest.mark.gpu
-PROB_TOL_BF16 = 1e-2
 
 
 def _ngpu():
@@ -49,13 +48,17 @@ def _run(defer, model, part_at, inputs, kill_after=None, kill_stage=None, timeou
     return outs, stats, launches
 
 
-def _check(model, inputs, outs, tol=PROB_TOL_BF16):
-    o = oracle_for(model)
-    for x, y in zip(inputs, outs):
-        ref = o.predict(np.asarray(x))[0]
-        assert y.shape == ref.shape and y.dtype == np.float32
-        assert np.abs(y - ref).max() <= tol
-        assert y.argmax(-1).tolist() == ref.argmax(-1).tolist()
+def _check(model, part_at, inputs, outs, mode="bf16", oracle_every=1, **kw):
+    """Every delivered micro-batch against the un-partitioned model on that very input (bit for bit on fused-group
+    cuts) and against the oracle -- see _util.StreamChecker.  `part_at` may be a list of cut lists (a stream that
+    lived through re-slicing): bit-exactness then needs every one of them on fused-group boundaries."""
+    cuts = [c for p in part_at for c in p] if part_at and isinstance(part_at[0], (list, tuple)) else list(part_at)
+    max_batch = max(int(np.asarray(x).shape[0]) for x in inputs)
+    chk = StreamChecker(model, cuts, mode=mode, max_batch=max_batch, **kw)
+    try:
+        chk.check(inputs, outs, oracle_every=oracle_every)
+    finally:
+        chk.close()
 
 
 def test_reference_driver_shape(pkg, model50):
@@ -66,7 +69,7 @@ def test_reference_driver_shape(pkg, model50):
     x = KO.synthetic_images(1, seed=7, kind="caffe")
     outs, stats, launches = _run(defer, model50, [], [x] * 10)
     assert len(outs) == 10 and all(o.shape == (1, 1000) for o in outs)
-    _check(model50, [x], outs[:1])
+    _check(model50, [], [x], outs[:1], oracle_tol="absolute")
     for o in outs[1:]:
         np.testing.assert_array_equal(o, outs[0])
     assert launches >= 10 * 58
@@ -77,11 +80,35 @@ def test_pipeline_stages_sharing_one_gpu(pkg, model50, part_at):
     from adapt_b200.dispatcher import DEFER
 
     n = len(part_at) + 1
-    inputs = [KO.synthetic_images(b, seed=300 + i, kind="normal") for i, b in enumerate([4, 3, 4, 1, 2, 4, 4, 4])]
+    inputs = [distinct_images(b, 300, i) for i, b in enumerate([4, 3, 4, 1, 2, 4, 4, 4])]
     defer = DEFER(["cuda:0"] * n, max_batch=4)
     outs, stats, _ = _run(defer, model50, part_at, inputs)
     assert stats["delivered"] == len(inputs) and stats["failovers"] == 0
-    _check(model50, inputs, outs)
+    _check(model50, part_at, inputs, outs)
+    # the check has teeth: two micro-batches of equal size delivered in each other's place fail it
+    swapped = list(outs)
+    swapped[5], swapped[6] = swapped[6], swapped[5]
+    with pytest.raises(AssertionError):
+        _check(model50, part_at, inputs, swapped, oracle_every=0)
+
+
+def test_value_check_catches_a_stale_input_slot(pkg, model50, monkeypatch):
+    """Fault injection (node.StageWorker, ADAPT_FAULT_INJECT): the last stage runs micro-batch 5 on the other input
+    slot, i.e. on micro-batch 4's cut tensor.  Delivery counts and order are untouched -- only the values are wrong,
+    and the per-micro-batch check must say so (and point at micro-batch 5)."""
+    from adapt_b200.dispatcher import DEFER
+
+    part_at = ["conv3_block4_out"]
+    inputs = [distinct_images(4, 330, i) for i in range(8)]
+    monkeypatch.setenv("ADAPT_FAULT_INJECT", "stale_slot:5")
+    defer = DEFER(["cuda:0"] * 2, max_batch=4)
+    outs, stats, _ = _run(defer, model50, part_at, inputs)
+    monkeypatch.delenv("ADAPT_FAULT_INJECT")
+    assert stats["delivered"] == len(inputs)
+    with pytest.raises(AssertionError, match="micro-batch 5"):
+        _check(model50, part_at, inputs, outs, oracle_every=0)
+    _check(model50, part_at, inputs[:5], outs[:5], oracle_every=0)      # everything before it is right
+    _check(model50, part_at, inputs[6:], outs[6:], oracle_every=0)      # ... and after
 
 
 def test_pipeline_across_gpus(pkg, model50):
@@ -91,22 +118,22 @@ def test_pipeline_across_gpus(pkg, model50):
 
     n = min(_ngpu(), 4)
     part_at = balanced_part_at(model50, n)
-    inputs = [KO.synthetic_images(4, seed=400 + i, kind="normal") for i in range(12)]
+    inputs = [distinct_images(4, 400, i) for i in range(12)]
     defer = DEFER([f"cuda:{i}" for i in range(n)], max_batch=4)
     outs, stats, _ = _run(defer, model50, part_at, inputs)
     assert stats["delivered"] == 12
-    _check(model50, inputs, outs)
+    _check(model50, part_at, inputs, outs, oracle_every=3)
 
 
 def test_pinned_torch_inputs(pkg, model50):
     torch = pytest.importorskip("torch")
     from adapt_b200.dispatcher import DEFER
 
-    xs = [KO.synthetic_images(2, seed=500 + i, kind="normal") for i in range(4)]
+    xs = [distinct_images(2, 500, i) for i in range(4)]
     pinned = [torch.from_numpy(x).pin_memory() for x in xs]
     defer = DEFER(["cuda:0"], max_batch=2)
     outs, _, _ = _run(defer, model50, [], pinned)
-    _check(model50, xs, outs)
+    _check(model50, [], xs, outs)
 
 
 def test_ingest_rails_across_gpus(pkg, model50):
@@ -118,12 +145,12 @@ def test_ingest_rails_across_gpus(pkg, model50):
     from adapt_b200.dispatcher import DEFER, balanced_part_at
 
     n = min(_ngpu(), 4)
-    xs = [KO.synthetic_images(3, seed=700 + i, kind="normal") for i in range(30)]
+    xs = [distinct_images(3, 700, i) for i in range(30)]
     pinned = [torch.from_numpy(x).pin_memory() for x in xs]
     defer = DEFER([f"cuda:{i}" for i in range(n)], max_batch=3, heartbeat_timeout=0.05, ingest_rails="auto")
     outs, stats, _ = _run(defer, model50, balanced_part_at(model50, n), pinned, kill_after=12, kill_stage=n - 1)
     assert stats["failovers"] == 1 and stats["delivered"] == 30
-    _check(model50, xs, outs)
+    _check(model50, [balanced_part_at(model50, n), balanced_part_at(model50, n - 1)], xs, outs, oracle_every=6)
     with pytest.raises(ValueError):
         DEFER(["cuda:0"], ingest_rails="sometimes")
 
@@ -132,12 +159,14 @@ def test_failover_resliced_and_replayed(pkg, model50):
     from adapt_b200.dispatcher import DEFER
 
     devs = [f"cuda:{i % max(1, _ngpu())}" for i in range(3)]
-    inputs = [KO.synthetic_images(2, seed=600 + i, kind="normal") for i in range(40)]
+    inputs = [distinct_images(2, 600, i) for i in range(40)]
     defer = DEFER(devs, max_batch=2, heartbeat_timeout=0.05)
     outs, stats, _ = _run(defer, model50, ["conv2_block3_out", "conv4_block1_out"], inputs, kill_after=10, kill_stage=1)
     assert stats["failovers"] == 1 and stats["delivered"] == 40
     assert len(defer.part_at) == 1
-    _check(model50, inputs, outs)                       # FIFO, nothing lost, nothing duplicated
+    # FIFO, nothing lost, nothing duplicated, and every value that of ITS input (all cuts, before and after the
+    # re-slice, are block outputs: bit for bit against the un-partitioned model)
+    _check(model50, [["conv2_block3_out", "conv4_block1_out"], defer.part_at], inputs, outs, oracle_every=8)
     assert stats["failover_ms"] and stats["failover_ms"][0] < 1000.0   # sub-second recovery (north_star)
 
 
@@ -147,7 +176,7 @@ def test_elastic_rejoin_after_failover_gpu(pkg, model50):
     from adapt_b200.dispatcher import DEFER
 
     devs = [f"cuda:{i % max(1, _ngpu())}" for i in range(3)]
-    inputs = [KO.synthetic_images(2, seed=800 + i, kind="normal") for i in range(60)]
+    inputs = [distinct_images(2, 800, i) for i in range(60)]
     defer = DEFER(devs, max_batch=2, heartbeat_timeout=0.05)
     in_q, out_q = queue.Queue(10), queue.Queue()
     t = threading.Thread(target=defer.run_defer, args=(model50, ["conv2_block3_out", "conv4_block1_out"], in_q, out_q),
@@ -177,7 +206,7 @@ def test_elastic_rejoin_after_failover_gpu(pkg, model50):
     t.join(30)
     assert stats["failovers"] == 1 and stats["rejoins"] == 1 and stats["delivered"] == len(inputs)
     assert len(order) == 3 and victim in order
-    _check(model50, inputs, outs)
+    _check(model50, [["conv2_block3_out", "conv4_block1_out"]], inputs, outs, oracle_every=12)  # (re-slices cut at block outputs too)
 
 
 def test_uint8_inputs_through_defer(pkg, model50):
@@ -193,7 +222,8 @@ def test_uint8_inputs_through_defer(pkg, model50):
     devs = [f"cuda:{i % max(1, _ngpu())}" for i in range(2)]
     defer = DEFER(devs, max_batch=2, input_format="uint8")
     outs, _, _ = _run(defer, model50, ["conv3_block4_out"], items)
-    _check(model50, [preprocess_input(x) for x in xs], outs)
+    _check(model50, ["conv3_block4_out"], xs, outs, input_format="uint8", preprocess=preprocess_input,
+           oracle_tol="absolute")
 
 
 def test_fp32_check_mode_through_defer(pkg, model50):
@@ -202,4 +232,4 @@ def test_fp32_check_mode_through_defer(pkg, model50):
     inputs = [KO.synthetic_images(1, seed=700 + i, kind="caffe") for i in range(2)]
     defer = DEFER(["cuda:0", "cuda:0"], mode="fp32", max_batch=1)
     outs, _, _ = _run(defer, model50, ["conv3_block4_out"], inputs)
-    _check(model50, inputs, outs, tol=1e-4)
+    _check(model50, ["conv3_block4_out"], inputs, outs, mode="fp32", oracle_tol="absolute")

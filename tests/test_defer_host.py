@@ -266,6 +266,96 @@ def test_elastic_rejoin_after_failover(pkg, model50):
         np.testing.assert_allclose(y, o.predict(x)[0], rtol=1e-5, atol=1e-7)
 
 
+def test_spare_workers_idle_until_a_failover_needs_them(pkg, model50):
+    """More computeNodes than partitions: the caller's `part_at` defines the pipeline, the spare worker holds no stage
+    (no re-slice, no re-join right after start-up).  When a stage dies the spare steps in, and because the stage
+    count is whole again the caller's own cut points are kept."""
+    import threading
+
+    from adapt_b200.dispatcher import DEFER
+
+    o = oracle_for(model50)
+    part_at = ["conv3_block4_out"]
+    inputs = [KO.synthetic_images(1, seed=370 + i, kind="normal") for i in range(6)]
+    d = DEFER([0, 1, 2], mode="fp32", max_batch=1, backend_factory=lambda dev: HostBackend(dev, delay=0.01),
+              heartbeat_timeout=0.3)
+    in_q, out_q = queue.Queue(4), queue.Queue()
+    t = threading.Thread(target=d.run_defer, args=(model50, part_at, in_q, out_q), daemon=True)
+    t.start()
+    d.wait_ready(60)
+    outs = []
+
+    def pump(items):
+        for x in items:
+            in_q.put(x)
+            outs.append(out_q.get(timeout=60))
+
+    pump(inputs[:2])
+    time.sleep(1.0)                          # many watchdog ticks
+    assert d.order == [0, 1] and d.part_at == part_at and d.stats["rejoins"] == 0 and d.health.epoch == 1
+    d.inject_kill(1)
+    pump(inputs[2:])
+    assert d.stats["failovers"] == 1 and d.order == [0, 2] and d.part_at == part_at and d.stats["rejoins"] == 0
+    assert d.error is None and out_q.empty()
+    d.shutdown()
+    t.join(30)
+    for x, y in zip(inputs, outs):
+        np.testing.assert_allclose(y, o.predict(x)[0], rtol=1e-5, atol=1e-7)
+
+
+def test_flag_values_of_different_epochs_never_alias(pkg, model50):
+    """Flag and result-ready values are `flag_base + k + 1`; every reconfiguration moves the base past whatever the
+    old epoch can have written, so a late write of a dropped-but-running stage cannot satisfy a wait of the new
+    epoch.  Checked here on the published table and by injecting exactly such stale writes after a fail-over."""
+    import threading
+
+    from adapt_b200.dispatcher import DEFER
+    from adapt_b200.fabric import FLAG_BASE_STEP
+    from adapt_b200.node import F_IN_READY
+
+    o = oracle_for(model50)
+    inputs = [KO.synthetic_images(1, seed=380 + i, kind="normal") for i in range(8)]
+    d = DEFER([0, 1, 2], mode="fp32", max_batch=1, backend_factory=lambda dev: HostBackend(dev, delay=0.01),
+              heartbeat_timeout=0.3)
+    in_q, out_q = queue.Queue(4), queue.Queue()
+    t = threading.Thread(target=d.run_defer, args=(model50, ["conv2_block3_out", "conv4_block1_out"], in_q, out_q), daemon=True)
+    t.start()
+    d.wait_ready(60)
+    outs = []
+
+    def pump(items):
+        for x in items:
+            in_q.put(x)
+            outs.append(out_q.get(timeout=60))
+
+    base0 = d.health.read_table()["flag_base"]
+    pump(inputs[:3])
+    d.inject_kill(1)
+    pump(inputs[3:5])
+    base1 = d.health.read_table()["flag_base"]
+    assert base1 >= base0 + 3 + FLAG_BASE_STEP       # beyond base0 + (micro-batches fed in epoch 1) + 1
+    # what a zombie of the old epoch would still write: "micro-batch k done" values of the OLD base, into the new
+    # last stage's input-ready flags and into a result slot's ready word
+    last = d.order[-1]
+    delivered = d.stats["delivered"]
+    for k in range(8):
+        d.flags_host[last, F_IN_READY + (k & 1)] = (base0 + k + 1) & 0xFFFFFFFF
+        d.results.ready[k % 8][0] = (base0 + k + 1) & 0xFFFFFFFF
+    time.sleep(0.2)
+    assert d.stats["delivered"] == delivered and out_q.empty() and d.error is None    # nothing was accepted
+    # (the stale values also clobbered live flags of this synchronous test backend: start a clean epoch to go on)
+    d.revive(1)
+    t0 = time.time()
+    while d.stats["rejoins"] == 0 and time.time() - t0 < 20:
+        time.sleep(0.01)
+    assert d.stats["rejoins"] == 1
+    pump(inputs[5:])
+    d.shutdown()
+    t.join(30)
+    for x, y in zip(inputs, outs):
+        np.testing.assert_allclose(y, o.predict(x)[0], rtol=1e-5, atol=1e-7)
+
+
 def test_cascading_kills(pkg, model50):
     """Two stages die one after the other (3 -> 2 -> 1 stages): each death is detected and re-sliced on its own,
     the stream stays FIFO and exactly-once, and the last survivor runs the whole model."""

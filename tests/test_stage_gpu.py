@@ -120,13 +120,12 @@ def test_full_model_bf16(model50, oracle, kind, batch):
     np.testing.assert_allclose(got.sum(-1), 1.0, atol=1e-4)
     assert np.abs(got - ref).max() <= PROB_TOL_BF16
     assert got.argmax(-1).tolist() == ref.argmax(-1).tolist()
+    assert rel_err(logits, ref_logits) <= 3e-2   # (measured ~4e-3: bf16 storage between 53 layers)
     if kind == "normal":
         # N(0,1) inputs keep logits O(0.1): the 1e-2 bound can be stated on logits too
         assert np.abs(logits - ref_logits).max() <= PROB_TOL_BF16
         top5 = lambda a: [set(r) for r in np.argsort(a, -1)[:, -5:]]  # noqa: E731
         assert sum(len(a & b) for a, b in zip(top5(logits), top5(ref_logits))) >= 5 * batch - batch
-    else:
-        assert rel_err(logits, ref_logits) <= 3e-2
 
 
 def test_full_model_fp32_check_mode(model50, oracle):
