@@ -76,6 +76,7 @@ SYMBOLS = {
     "adapt_stage_prepare": (_I, [_VP, _I, _I]),
     "adapt_stage_enqueue": (_I, [_VP, _I, _I, _VP]),
     "adapt_stage_profile": (_I, [_VP, _I, _I, _VP, _I, C.POINTER(C.c_float), _I]),
+    "adapt_stage_time_kind": (_I, [_VP, _I, _I, _VP, _I, _I, C.POINTER(C.c_float), C.POINTER(_I)]),
     "adapt_stage_read_tensor": (_I, [_VP, _I, _VP, _SZ, _VP]),
     "adapt_stage_num_launches": (_I, [_VP, _I]),
     "adapt_stage_destroy": (None, [_VP]),

@@ -1250,6 +1250,55 @@ int adapt_stage_profile(adapt_stage_t* st, int slot, int batch, void* stream_v, 
     return ADAPT_OK;
 }
 
+int adapt_stage_time_kind(adapt_stage_t* st, int slot, int batch, void* stream_v, int kind, int reps, float* ms_per_rep,
+                          int* n_launches) {
+    Plan* plan = nullptr;
+    int rc = get_plan(st, slot, batch, &plan);
+    if (rc) return rc;
+    if (!ms_per_rep || reps <= 0) return fail(ADAPT_EINVAL, "time_kind: need reps > 0 and an output pointer");
+    std::vector<Step> only;
+    for (const Step& s : plan->steps[slot])
+        if (s.kind == kind) only.push_back(s);
+    if (n_launches) *n_launches = (int)only.size();
+    if (only.empty()) {
+        *ms_per_rep = 0.f;
+        return ADAPT_OK;
+    }
+    // the same launches (attributes included: programmatic dependent launch between consecutive convolutions)
+    // captured into their own graph, so that the class is timed the way it runs inside the stage's graph
+    cudaStream_t cap;
+    CUDA_TRY(cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking));
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    cudaError_t e = cudaStreamBeginCapture(cap, cudaStreamCaptureModeThreadLocal);
+    if (e == cudaSuccess) {
+        rc = run_steps(st, only, cap);
+        e = cudaStreamEndCapture(cap, &graph);
+    }
+    cudaStreamDestroy(cap);
+    if (rc == ADAPT_OK && e != cudaSuccess) rc = fail(ADAPT_ECUDA, "time_kind: capture failed: %s", cudaGetErrorString(e));
+    if (rc == ADAPT_OK && (e = cudaGraphInstantiate(&exec, graph, 0)) != cudaSuccess)
+        rc = fail(ADAPT_ECUDA, "time_kind: cudaGraphInstantiate: %s", cudaGetErrorString(e));
+    if (graph) cudaGraphDestroy(graph);
+    if (rc) return rc;
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
+    cudaEvent_t e0, e1;
+    CUDA_TRY(cudaEventCreate(&e0));
+    CUDA_TRY(cudaEventCreate(&e1));
+    for (int r = 0; r < 3; ++r) CUDA_TRY(cudaGraphLaunch(exec, stream));  // warm-up
+    CUDA_TRY(cudaEventRecord(e0, stream));
+    for (int r = 0; r < reps; ++r) CUDA_TRY(cudaGraphLaunch(exec, stream));
+    CUDA_TRY(cudaEventRecord(e1, stream));
+    CUDA_TRY(cudaStreamSynchronize(stream));
+    float ms = 0.f;
+    CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
+    *ms_per_rep = ms / (float)reps;
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaGraphExecDestroy(exec);
+    return ADAPT_OK;
+}
+
 int adapt_stage_num_launches(adapt_stage_t* st, int batch) {
     if (!st) return fail(ADAPT_EINVAL, "stage is null");
     (void)batch;

@@ -721,8 +721,10 @@ def _rendezvous_dispatcher(defer: "DEFER", model, devices: List[int]) -> List[St
     return [wk]
 
 
-def join_session_as_worker(model, device: Optional[int] = None, backend_factory=None) -> None:
-    """Body of `Node().run()` on ranks > 0 of a torchrun launch."""
+def join_session_as_worker(model, device: Optional[int] = None, backend_factory=None) -> bool:
+    """One session of `Node().run()` on ranks > 0 of a torchrun launch: rendezvous with the dispatcher rank, serve a
+    stage until it shuts the session down.  Returns False when the dispatcher announced that no session follows
+    (`end_sessions`)."""
     import torch.distributed as dist
 
     backend_factory = backend_factory or (lambda d: CudaBackend(d))
@@ -731,6 +733,8 @@ def join_session_as_worker(model, device: Optional[int] = None, backend_factory=
     box: List[object] = [None]
     dist.broadcast_object_list(box, src=0)
     session = box[0]
+    if session is None:
+        return False
     wk = StageWorker(rank, device, model, session, backend_factory(device))
     token = wk.allocate()
     gathered: List[object] = [None] * dist.get_world_size()
@@ -742,3 +746,13 @@ def join_session_as_worker(model, device: Optional[int] = None, backend_factory=
         wk.run()  # blocks until PHASE_SHUTDOWN
     finally:
         wk.close()
+    return True
+
+
+def end_sessions() -> None:
+    """Dispatcher rank of a torchrun launch: tell the worker ranks (blocked in `Node().run()`, waiting for the next
+    session's rendezvous) that none follows."""
+    import torch.distributed as dist
+
+    if _torchrun_world() > 1 and dist.is_initialized():
+        dist.broadcast_object_list([None], src=0)

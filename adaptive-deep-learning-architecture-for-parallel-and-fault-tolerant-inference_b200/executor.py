@@ -109,6 +109,12 @@ class StageExecutor:
                         "shape": [op.H, op.W, op.Cin, op.Cout, op.kh, op.stride]})
         return out
 
+    def time_kind(self, slot: int, batch: int, kind: int, stream: int = 0, reps: int = 20) -> Tuple[float, int]:
+        """(device ms per step, launches) of all ops of one kind, run as their own CUDA graph (PDL overlap kept)."""
+        ms, n = C.c_float(0), C.c_int(0)
+        N.check(self.lib.adapt_stage_time_kind(self.handle, slot, batch, stream, kind, reps, C.byref(ms), C.byref(n)))
+        return float(ms.value), int(n.value)
+
     def read_logits(self, batch: int, stream: int = 0) -> np.ndarray:
         if "logits" not in self.program.taps:
             raise KeyError("this stage does not contain the `predictions` layer")

@@ -535,14 +535,19 @@ class StageWorker:
 
 class Node:
     """Reference-compatible shell: `Node().run()` (reference src/node.py:181,210-211) turns this
-    process into the worker for one GPU of a torchrun-launched session.  It blocks until the
-    dispatcher (rank 0) shuts the session down."""
+    process into the worker for one GPU of a torchrun-launched deployment.  Like the reference's worker it
+    serves one configuration after another -- here: one DEFER session after another, each with its own
+    partition table and micro-batch size -- and returns when the dispatcher (rank 0) calls
+    `dispatcher.end_sessions()`."""
 
-    def __init__(self, model=None, device: Optional[int] = None):
+    def __init__(self, model=None, device: Optional[int] = None, backend_factory=None):
         self.model = model
         self.device = device
+        self.backend_factory = backend_factory
+        self.sessions_served = 0
 
     def run(self) -> None:
         from .dispatcher import join_session_as_worker
 
-        join_session_as_worker(self.model, self.device)
+        while join_session_as_worker(self.model, self.device, self.backend_factory):
+            self.sessions_served += 1

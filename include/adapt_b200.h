@@ -144,6 +144,15 @@ int adapt_stage_read_tensor(adapt_stage_t* stage, int tensor, void* host_dst, si
 int adapt_stage_profile(adapt_stage_t* stage, int slot, int batch, void* stream, int reps, float* ms_per_op,
                         int n_ops);
 
+/* Measurement aid: the ops of ONE kind (ADAPT_OP_*) of (`slot`, `batch`) captured into their own CUDA graph -- same
+ * launches and launch attributes as inside the stage's graph, so consecutive convolutions keep their programmatic
+ * dependent launch overlap -- and timed over `reps` graph launches with one pair of CUDA events on `stream`.
+ * *ms_per_rep = device time of that class per step; *n_launches = launches of that kind.  Overwrites the stage's
+ * internal activations with meaningless values (inputs of the skipped ops are stale); synchronises.
+ * No reference counterpart (bench.py's roofline accounting). */
+int adapt_stage_time_kind(adapt_stage_t* stage, int slot, int batch, void* stream, int kind, int reps,
+                          float* ms_per_rep, int* n_launches);
+
 /* Number of kernel launches one enqueue() of `batch` images performs (for bench accounting). */
 int adapt_stage_num_launches(adapt_stage_t* stage, int batch);
 

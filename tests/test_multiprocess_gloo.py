@@ -25,27 +25,34 @@ def _worker(rank, world, port, q):
     import adapt_b200
     from _host_backend import SharedHostBackend
     from _util import KO, oracle_for
-    from adapt_b200.dispatcher import DEFER, join_session_as_worker
+    from adapt_b200.dispatcher import DEFER, end_sessions
+    from adapt_b200.node import Node
 
     model = adapt_b200.ResNet50(weights=None)
     try:
         if rank > 0:
-            join_session_as_worker(model, device=rank, backend_factory=SharedHostBackend)
-            q.put((rank, "ok", None))
+            node = Node(model, device=rank, backend_factory=SharedHostBackend)
+            node.run()                       # serves session after session until the dispatcher ends them
+            q.put((rank, "ok", node.sessions_served))
             return
-        inputs = [KO.synthetic_images(1, seed=900 + i, kind="normal") for i in range(4)]
-        defer = DEFER(["10.0.0.1", "10.0.0.2"], mode="fp32", max_batch=1, backend_factory=SharedHostBackend, heartbeat_timeout=5.0)
-        in_q, out_q = queue.Queue(), queue.Queue()
-        t = threading.Thread(target=defer.run_defer, args=(model, ["conv3_block4_out"], in_q, out_q), daemon=True)
-        t.start()
-        defer.wait_ready(120)
-        for x in inputs:
-            in_q.put(x)
-        outs = [out_q.get(timeout=120) for _ in inputs]
-        defer.shutdown()
-        t.join(30)
         o = oracle_for(model)
-        err = max(float(np.abs(y - o.predict(x)[0]).max()) for x, y in zip(inputs, outs))
+        err = 0.0
+        # two sessions back to back (what bench.py does for BASELINE's other configs): other cuts, other micro-batch
+        for part_at, batch in ((["conv3_block4_out"], 1), (["conv4_block6_out"], 2)):
+            inputs = [KO.synthetic_images(batch, seed=900 + i, kind="normal") for i in range(3)]
+            defer = DEFER(["10.0.0.1", "10.0.0.2"], mode="fp32", max_batch=batch, backend_factory=SharedHostBackend,
+                          heartbeat_timeout=5.0)
+            in_q, out_q = queue.Queue(), queue.Queue()
+            t = threading.Thread(target=defer.run_defer, args=(model, part_at, in_q, out_q), daemon=True)
+            t.start()
+            defer.wait_ready(120)
+            for x in inputs:
+                in_q.put(x)
+            outs = [out_q.get(timeout=120) for _ in inputs]
+            defer.shutdown()
+            t.join(30)
+            err = max([err] + [float(np.abs(y - o.predict(x)[0]).max()) for x, y in zip(inputs, outs)])
+        end_sessions()
         q.put((0, "ok", err))
     except Exception as e:  # noqa: BLE001
         import traceback
@@ -81,5 +88,5 @@ def test_two_rank_pipeline_over_gloo():
         if p.is_alive():
             p.kill()
     assert results.get(0, ("missing", None))[0] == "ok", results
-    assert results.get(1, ("missing", None))[0] == "ok", results
+    assert results.get(1, ("missing", None)) == ("ok", 2), results      # the worker rank served both sessions
     assert results[0][1] < 1e-5
