@@ -28,6 +28,15 @@ namespace {
 
 thread_local std::string g_last_error;
 
+// Configuration-time CUDA work -- allocation, kernel attribute set-up, weight upload, stream capture and graph
+// instantiation -- is serialised per process.  Several stage workers can live in one process (one thread per GPU,
+// or several stages sharing a GPU); measured on B200: a stage's capture was occasionally invalidated ("operation
+// failed due to a previous error during capture") while a sibling thread was creating its stage (cudaMalloc,
+// cudaFuncSetAttribute, synchronous copies) even in thread-local capture mode.  Steady-state calls (enqueue, flag
+// writes, async copies) never take this lock.
+std::recursive_mutex g_config_mu;
+#define CONFIG_LOCK() std::lock_guard<std::recursive_mutex> _config_lock(g_config_mu)
+
 int fail(int code, const char* fmt, ...) {
     char buf[1024];
     va_list ap;
@@ -756,6 +765,7 @@ struct adapt_stage {
     int max_batch = 0;
     int num_sms = 0;
     bool use_graph = true;
+    unsigned warmed_kinds = 0;  // op kinds whose kernels this stage has already launched outside a capture
     std::vector<WeightDev> weights;
     std::vector<adapt_tensor_desc> tdesc;
     std::vector<void*> tptr;  // internal tensors: sub-ranges of `arena`
@@ -1082,6 +1092,7 @@ int adapt_device_count(void) {
 int adapt_stage_create(int device, int dtype_mode, int max_batch, const adapt_weight_desc* weights, int n_weights,
                        const adapt_tensor_desc* tensors, int n_tensors, const adapt_op_desc* ops, int n_ops,
                        adapt_stage_t** out) {
+    CONFIG_LOCK();
     if (!out) return fail(ADAPT_EINVAL, "out is null");
     *out = nullptr;
     if (dtype_mode != ADAPT_MODE_BF16 && dtype_mode != ADAPT_MODE_FP32_CHECK)
@@ -1113,6 +1124,7 @@ int adapt_stage_create(int device, int dtype_mode, int max_batch, const adapt_we
 
 int adapt_stage_reslice(adapt_stage_t* st, const adapt_tensor_desc* tensors, int n_tensors, const adapt_op_desc* ops,
                         int n_ops) {
+    CONFIG_LOCK();
     if (!st) return fail(ADAPT_EINVAL, "stage is null");
     int rc = require_device(st->device);
     if (rc) return rc;
@@ -1162,12 +1174,27 @@ int get_plan(adapt_stage_t* st, int slot, int batch, Plan** out) {
 }  // namespace
 
 int adapt_stage_prepare(adapt_stage_t* st, int slot, int batch) {
+    CONFIG_LOCK();
     Plan* plan = nullptr;
     int rc = get_plan(st, slot, batch, &plan);
     if (rc) return rc;
     if (!st->use_graph || plan->exec[slot]) return ADAPT_OK;
     cudaStream_t cap;
     CUDA_TRY(cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking));
+    // A kernel's very first launch loads its module (lazy loading), which is not something to do inside a
+    // capture: run the program once as plain launches if it contains a kind this stage has not launched yet.
+    unsigned kinds = 0;
+    for (const Step& s : plan->steps[slot]) kinds |= 1u << s.kind;
+    if (kinds & ~st->warmed_kinds) {
+        rc = run_steps(st, plan->steps[slot], cap);
+        cudaError_t we = cudaStreamSynchronize(cap);
+        if (rc == ADAPT_OK && we != cudaSuccess) rc = fail(ADAPT_ECUDA, "prepare: warm-up run: %s", cudaGetErrorString(we));
+        if (rc) {
+            cudaStreamDestroy(cap);
+            return rc;
+        }
+        st->warmed_kinds |= kinds;
+    }
     cudaGraph_t graph = nullptr;
     cudaError_t e = cudaStreamBeginCapture(cap, cudaStreamCaptureModeThreadLocal);
     if (e != cudaSuccess) {
@@ -1252,6 +1279,7 @@ int adapt_stage_profile(adapt_stage_t* st, int slot, int batch, void* stream_v, 
 
 int adapt_stage_time_kind(adapt_stage_t* st, int slot, int batch, void* stream_v, int kind, int reps, float* ms_per_rep,
                           int* n_launches) {
+    CONFIG_LOCK();
     Plan* plan = nullptr;
     int rc = get_plan(st, slot, batch, &plan);
     if (rc) return rc;
@@ -1306,6 +1334,7 @@ int adapt_stage_num_launches(adapt_stage_t* st, int batch) {
 }
 
 void adapt_stage_destroy(adapt_stage_t* st) {
+    CONFIG_LOCK();
     if (!st) return;
     if (cudaSetDevice(st->device) == cudaSuccess) {
         cudaDeviceSynchronize();
@@ -1447,6 +1476,7 @@ int adapt_dense_softmax_noalloc(int device, const void* in, const void* w, const
 
 // ---------------------------------------------------------------- hand-off plumbing
 int adapt_device_alloc(int device, size_t bytes, void** out) {
+    CONFIG_LOCK();
     if (!out || bytes == 0) return fail(ADAPT_EINVAL, "device_alloc: bad argument");
     int rc = require_device(device);
     if (rc) return rc;
@@ -1456,6 +1486,7 @@ int adapt_device_alloc(int device, size_t bytes, void** out) {
 }
 
 int adapt_device_free(int device, void* ptr) {
+    CONFIG_LOCK();
     int rc = require_device(device);
     if (rc) return rc;
     CUDA_TRY(cudaFree(ptr));
@@ -1463,6 +1494,7 @@ int adapt_device_free(int device, void* ptr) {
 }
 
 int adapt_peer_enable(int a, int b) {
+    CONFIG_LOCK();
     if (a == b) return ADAPT_OK;
     int rc = require_device(a);
     if (rc) return rc;
@@ -1494,6 +1526,7 @@ int adapt_ipc_export(int device, void* ptr, void* handle64_out) {
 }
 
 int adapt_ipc_import(int device, const void* handle64, void** out) {
+    CONFIG_LOCK();
     if (!handle64 || !out) return fail(ADAPT_EINVAL, "ipc_import: null");
     int rc = require_device(device);
     if (rc) return rc;
@@ -1504,6 +1537,7 @@ int adapt_ipc_import(int device, const void* handle64, void** out) {
 }
 
 int adapt_ipc_close(int device, void* ptr) {
+    CONFIG_LOCK();
     int rc = require_device(device);
     if (rc) return rc;
     CUDA_TRY(cudaIpcCloseMemHandle(ptr));
@@ -1610,6 +1644,7 @@ int adapt_stream_query(int device, void* stream, int* busy_out) {
     return ADAPT_OK;
 }
 int adapt_host_register(int device, void* host_ptr, size_t bytes, void** dev_ptr_out) {
+    CONFIG_LOCK();
     if (!host_ptr || !bytes || !dev_ptr_out) return fail(ADAPT_EINVAL, "host_register: bad argument");
     int rc = require_device(device);
     if (rc) return rc;
@@ -1624,6 +1659,7 @@ int adapt_host_register(int device, void* host_ptr, size_t bytes, void** dev_ptr
     return ADAPT_OK;
 }
 int adapt_host_unregister(int device, void* host_ptr) {
+    CONFIG_LOCK();
     int rc = require_device(device);
     if (rc) return rc;
     cudaError_t e = cudaHostUnregister(host_ptr);
@@ -1635,6 +1671,7 @@ int adapt_host_unregister(int device, void* host_ptr) {
     return ADAPT_OK;
 }
 int adapt_stream_create(int device, void** stream_out) {
+    CONFIG_LOCK();
     if (!stream_out) return fail(ADAPT_EINVAL, "stream_create: null");
     int rc = require_device(device);
     if (rc) return rc;
@@ -1644,6 +1681,7 @@ int adapt_stream_create(int device, void** stream_out) {
     return ADAPT_OK;
 }
 int adapt_stream_destroy(int device, void* stream) {
+    CONFIG_LOCK();
     int rc = require_device(device);
     if (rc) return rc;
     CUDA_TRY(cudaStreamDestroy(reinterpret_cast<cudaStream_t>(stream)));
