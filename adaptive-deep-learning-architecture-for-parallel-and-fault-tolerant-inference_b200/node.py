@@ -534,20 +534,168 @@ class StageWorker:
 
 
 class Node:
-    """Reference-compatible shell: `Node().run()` (reference src/node.py:181,210-211) turns this
-    process into the worker for one GPU of a torchrun-launched deployment.  Like the reference's worker it
-    serves one configuration after another -- here: one DEFER session after another, each with its own
-    partition table and micro-batch size -- and returns when the dispatcher (rank 0) calls
-    `dispatcher.end_sessions()`."""
+    """Reference-compatible shell: `Node().run()` (reference src/node.py:181,210-211).
 
-    def __init__(self, model=None, device: Optional[int] = None, backend_factory=None):
+    Default (`listen=False`): this process becomes the worker for one GPU of a torchrun-launched deployment.  Like
+    the reference's worker it serves one configuration after another -- here: one DEFER session after another, each
+    with its own partition table and micro-batch size -- and returns when the dispatcher (rank 0) calls
+    `dispatcher.end_sessions()`.
+
+    `listen=True`: the worker speaks the REFERENCE's wire protocol (wire.py) on its ports -- configuration on 6001,
+    data on 6000, results to the dispatcher's 6003 -- so that a B200 stage can sit behind an unmodified remote
+    dispatcher: a configuration message (model JSON, partition index, weights) installs a partition as
+    one GPU stage, every data message is run through it and the result sent back.  `run()` then blocks until
+    `stop()`."""
+
+    def __init__(self, model=None, device: Optional[int] = None, backend_factory=None, listen: bool = False,
+                 data_port: Optional[int] = None, config_port: Optional[int] = None, dispatcher_addr=None,
+                 predictor_factory=None, codec=None, mode: str = "bf16", max_batch: int = 32, chunk_size: int = 512 * 1000,
+                 bind_host: str = "0.0.0.0"):
         self.model = model
         self.device = device
         self.backend_factory = backend_factory
         self.sessions_served = 0
+        # ---- wire mode
+        from . import wire
+
+        self.listen = listen
+        self.data_port = wire.DATA_PORT if data_port is None else int(data_port)
+        self.config_port = wire.CONFIG_PORT if config_port is None else int(config_port)
+        self.dispatcher_addr = dispatcher_addr      # (host, port) results go to; default: config peer, port 6003
+        self.predictor_factory = predictor_factory  # (model, start, end) -> object with .run(x) / .close(); default: one GPU stage
+        self.codec = codec or wire.default_codec()
+        self.mode, self.max_batch, self.chunk_size, self.bind_host = mode, int(max_batch), int(chunk_size), bind_host
+        self.node_state = NodeState(chunk_size=chunk_size)
+        self.jobs: Dict[int, object] = {}           # partition index -> predictor (the reference's job_queue entry)
+        self._jobs_lock = threading.Lock()
+        self._wire_stop = threading.Event()
+        self._servers: List[object] = []
+        self.ready = threading.Event()
+        self.served = 0
+        self.errors: List[str] = []
 
     def run(self) -> None:
+        if self.listen:
+            return self._serve_wire()
         from .dispatcher import join_session_as_worker
 
         while join_session_as_worker(self.model, self.device, self.backend_factory):
             self.sessions_served += 1
+
+    # ------------------------------------------------------------------ wire mode
+    def _make_predictor(self, start: str, end: str):
+        if self.predictor_factory is not None:
+            return self.predictor_factory(self.model, start, end)
+        from .executor import LocalPredictor
+
+        return LocalPredictor(self.model, mode=self.mode, device=self.device or 0, max_batch=self.max_batch, start=start, end=end)
+
+    def _listen_socket(self, port: int):
+        import socket
+
+        srv = socket.socket(socket.AF_INET, socket.SOCK_STREAM)
+        srv.setsockopt(socket.SOL_SOCKET, socket.SO_REUSEADDR, 1)
+        srv.bind((self.bind_host, port))
+        srv.listen(5)
+        srv.settimeout(0.1)
+        self._servers.append(srv)
+        return srv
+
+    def _config_server(self, srv) -> None:
+        """Configuration port (reference src/node.py:65-98): JSON + index + weights -> load the partition -> ACK."""
+        import socket
+
+        from . import wire
+        from .dag_util import construct_model
+
+        while not self._wire_stop.is_set():
+            try:
+                cli, peer = srv.accept()
+            except socket.timeout:
+                continue
+            except OSError:
+                return
+            try:
+                cli.setblocking(True)
+                model_json, index, weights = wire.recv_full_configuration(cli, self.chunk_size, self.codec)
+                order = [l.name for l in self.model.layers]
+                start, end = wire.partition_bounds_from_json(model_json, order)
+                part = construct_model(self.model, start, end, f"part{index}")
+                # the shipped arrays are `part.get_weights()`: per layer, in model order (src/dispatcher.py:243)
+                it = iter(weights)
+                for l in part.layers:
+                    n = len(l.get_weights())
+                    if n:
+                        l.set_weights([np.asarray(next(it)) for _ in range(n)])
+                if next(it, None) is not None:
+                    raise ValueError("more weight arrays than the partition's layers hold")
+                self.model._version += 1
+                pred = self._make_predictor(start, end)
+                with self._jobs_lock:
+                    old = self.jobs.pop(index, None)
+                    self.jobs[index] = pred
+                if old is not None:
+                    old.close()
+                if self.dispatcher_addr is None:
+                    self.dispatcher_addr = (peer[0], wire.RESULT_PORT)
+                self.node_state.state = StateEnum.BUSY
+                cli.sendall(wire.ACK)
+                time.sleep(0.05)  # (as the reference: let the ACK leave before closing)
+            except Exception as e:  # noqa: BLE001  (the reference prints and goes back to listening)
+                self.errors.append(f"config: {type(e).__name__}: {e}")
+            finally:
+                cli.close()
+
+    def _data_server(self, srv) -> None:
+        """Data port (reference src/node.py:127-179): index + payload -> predict -> result to the dispatcher."""
+        import socket
+
+        from . import wire
+
+        while not self._wire_stop.is_set():
+            try:
+                cli, _ = srv.accept()
+            except socket.timeout:
+                continue
+            except OSError:
+                return
+            try:
+                cli.setblocking(True)
+                msg = wire.recv_data_message(cli, self.chunk_size)
+                if msg is None:
+                    continue
+                index, payload = msg
+                with self._jobs_lock:
+                    pred = self.jobs.get(index)
+                if pred is None:
+                    raise KeyError(f"data for partition {index}, which was never configured")
+                out = pred.run(self.codec.decode(payload))
+                # [inferred] the result message mirrors the data message: index, framed payload, SHUT_WR
+                wire.forward_data_to_worker(self.dispatcher_addr, self.codec.encode(out), index, self.chunk_size)
+                self.served += 1
+            except Exception as e:  # noqa: BLE001
+                self.errors.append(f"data: {type(e).__name__}: {e}")
+            finally:
+                cli.close()
+
+    def _serve_wire(self) -> None:
+        if self.model is None:
+            raise ValueError("Node(listen=True) needs the model whose partitions it will be sent")
+        threads = [threading.Thread(target=self._config_server, args=(self._listen_socket(self.config_port),), daemon=True),
+                   threading.Thread(target=self._data_server, args=(self._listen_socket(self.data_port),), daemon=True)]
+        for t in threads:
+            t.start()
+        self.ready.set()
+        while not self._wire_stop.is_set():
+            time.sleep(0.02)
+        for t in threads:
+            t.join(timeout=2)
+        for srv in self._servers:
+            srv.close()
+        with self._jobs_lock:
+            for p in self.jobs.values():
+                p.close()
+            self.jobs = {}
+
+    def stop(self) -> None:
+        self._wire_stop.set()
