@@ -115,3 +115,47 @@ def test_golden_vectors(model50):
     for name, v in gold["tap_mean_abs"].items():
         assert abs(float(np.abs(taps[name]).mean()) - v) <= 2e-4 * abs(v) + 1e-7, name
     np.testing.assert_allclose(o.logits[:, :8], np.array(gold["logits_head"]), rtol=2e-4, atol=2e-4)
+
+
+def test_timed_cpu_stage_equals_the_oracle(model50):
+    """`oracle/cpu_pipeline.py::TorchCpuStage` is what bench.py's cpu_baseline and `--impl reference` TIME (torch CPU
+    kernels); it must compute what the numpy oracle computes, on every partition BASELINE.json names."""
+    from oracle.cpu_pipeline import TorchCpuStage
+
+    weights = {l.name: l.get_weights() for l in model50.layers if l.get_weights()}
+    o = oracle_for(model50)
+    x = KO.synthetic_images(1, seed=9, kind="caffe")
+    full = o.predict(x)[0]
+    for part_at in ([], ["conv3_block4_out"], ["conv2_block3_out", "conv3_block4_out", "conv4_block6_out"]):
+        bounds = ["input_1"] + part_at + ["predictions"]
+        cur, cur_ref = x, x
+        for a, b in zip(bounds[:-1], bounds[1:]):
+            cur = TorchCpuStage(weights, a, b, threads=4)(cur)
+            cur_ref = o.run_range(cur_ref, a, b)[0]
+            assert cur.shape == cur_ref.shape
+            assert np.abs(cur - cur_ref).max() <= 1e-5 * max(1.0, float(np.abs(cur_ref).max())), (a, b)
+        assert np.abs(cur - full).max() <= 1e-5 and cur.argmax(-1).tolist() == full.argmax(-1).tolist()
+
+
+def test_tf_crosscheck_fixture_is_current(model50):
+    """tests/golden/resnet50_seed1234_tf_crosscheck.npz (tools/export_for_tf.py) is the hand-over artefact a maintainer
+    with TensorFlow runs tools/tf_check.py against.  Here: it still describes today's weight generator and oracle
+    (they are NOT reference outputs -- parity stays unpinned until tf_check.py has been run somewhere)."""
+    import sys
+
+    sys.path.insert(0, os.path.join(os.path.dirname(GOLD), "..", "tools"))
+    from export_for_tf import make_inputs, weights_digest
+
+    g = np.load(os.path.join(GOLD, "resnet50_seed1234_tf_crosscheck.npz"))
+    assert int(g["seed"]) == 1234 and int(g["n_weight_arrays"]) == 320
+    assert weights_digest(model50.get_weights()) == str(g["weights_sha256"])
+    x = make_inputs()
+    assert abs(float(np.float64(x).sum()) - float(g["inputs_sum"])) < 1e-3
+    o = oracle_for(model50)
+    names = [str(n) for n in g["tap_names"]]
+    probs, taps = o.predict(x[1:2], taps=names)          # (one of the two images keeps the CPU suite short)
+    np.testing.assert_allclose(probs, g["probs"][1:2], rtol=1e-4, atol=1e-7)
+    np.testing.assert_allclose(o.logits, g["logits"][1:2], rtol=1e-4, atol=1e-5)
+    for n in names:
+        s = taps[n].reshape(1, -1)[:, ::int(g["tap_stride"])]
+        np.testing.assert_allclose(s, g["tap_" + n][1:2], rtol=1e-4, atol=1e-5, err_msg=n)

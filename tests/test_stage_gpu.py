@@ -259,3 +259,36 @@ def test_uint8_ingest_matches_host_preprocessing(pkg, model50, oracle, end):
             assert got8.argmax(-1).tolist() == ref.argmax(-1).tolist()
         p8.close()
         pf.close()
+
+
+def test_cuda_path_against_the_committed_fixture(model50):
+    """The CUDA path against tests/golden/resnet50_seed1234_tf_crosscheck.npz -- the committed vectors a maintainer
+    with TensorFlow checks Keras against (tools/tf_check.py): probabilities, logits and the cut tensors BASELINE's
+    partitions hand off, in fp32 check mode (1e-4) and bf16 mode (cut tensors 2 %, logits 3e-2 relative)."""
+    import os
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, os.path.join(root, "tools"))
+    from export_for_tf import make_inputs
+
+    g = np.load(os.path.join(root, "tests", "golden", "resnet50_seed1234_tf_crosscheck.npz"))
+    x = make_inputs()
+    stride = int(g["tap_stride"])
+    for mode, ptol, ltol, ttol in (("fp32", PROB_TOL_FP32, 1e-4, 1e-4), ("bf16", PROB_TOL_BF16, 3e-2, CUT_TOL_BF16)):
+        p = _predictor(model50, mode=mode, max_batch=2)
+        probs = p.run(x)
+        logits = p.logits(2)
+        p.close()
+        assert np.abs(probs - g["probs"]).max() <= ptol, mode
+        assert probs.argmax(-1).tolist() == g["probs"].argmax(-1).tolist(), mode
+        for i in range(2):
+            assert rel_err(logits[i], g["logits"][i]) <= ltol, (mode, i)
+        for name in [str(n) for n in g["tap_names"]]:
+            q = _predictor(model50, mode=mode, max_batch=2, end=name)
+            t = q.run(x)
+            q.close()
+            assert tuple(t.shape[1:]) == tuple(int(v) for v in g["tapshape_" + name])
+            s = t.reshape(2, -1)[:, ::stride]
+            for i in range(2):
+                assert rel_err(s[i], g["tap_" + name][i]) <= ttol, (mode, name, i)
