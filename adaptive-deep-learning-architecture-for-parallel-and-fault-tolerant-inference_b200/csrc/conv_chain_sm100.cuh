@@ -1,0 +1,533 @@
+// Bottleneck-block chain: `_2_conv` (3x3 / stride 1 / pad 1, C -> C, +BN +ReLU) and `_3_conv` (1x1, C -> 4C, +BN
+// +shortcut Add +ReLU) of one Keras residual block in ONE kernel.
+//
+// Replaces, inside a stage's `model.predict` (reference src/node.py:177), the two launches
+//     y2  = relu(conv3x3(x) * s2 + b2)                 (written to HBM, read back)
+//     out = relu(conv1x1(y2) * s3 + b3 + shortcut)
+// by one: the 3x3's 128 x C accumulator tile, after scale / bias / ReLU and rounding to bf16 (the SAME rounding
+// point as the two-launch form), is exactly a 128 x K A-operand tile of the following 1x1 (point-wise: no halo), so
+// the epilogue warps write it into a swizzled shared-memory A tile and the MMA warp issues the second GEMM against
+// `_3_conv`'s weights.  The `_2_relu` tensor never exists in HBM (conv2: 103 MB of traffic per block at batch 128,
+// conv3: 51 MB) and a launch per block disappears.
+//
+// Phase 1 is the row-reuse form of conv_gemm_sm100.cuh (A_ROW3): the output is walked in "padded-flat" order (rows
+// of W + 2 positions, the last two of each row discarded), one im2col load of 136 positions per (filter row, channel
+// block) feeds the three horizontal taps through shifted descriptors.  Phase 2 therefore also runs on padded-flat
+// positions; its residual tile is fetched with an im2col-mode TMA load that walks the same positions (zero-filled
+// where a position is not a pixel) and its output leaves through the position -> pixel st.global write-out.
+//
+//   warp 0      TMA producer: per unit, the phase-1 stages (A row segments; the three B tiles of a filter row unless
+//               the 3x3's weights are resident), then one stage per phase-2 n-tile (`_3_conv` weights), all through
+//               ONE operand ring in the order the MMA warp consumes them
+//   warp 1      MMA issuer (phase 1 into acc1, then phase 2 per 128-column n-tile into acc2[n & 1])
+//   warps 2..9  epilogue, two groups of four.  Both groups turn acc1 into the A2 tile (32-column units alternate
+//               between the groups); group g then drains acc2[g], i.e. n-tiles g, g+2, ...
+//
+//   C = 64  (conv2): single CTA, N1 = 64; the 3x3's weights (72 KiB) stay resident in shared memory
+//   C = 128 (conv3): CTA pair (tcgen05 cta_group::2, 256 positions per unit), all weights streamed
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <cuda.h>
+#include <cstdint>
+#include <type_traits>
+
+#include "conv_gemm_sm100.cuh"
+#include "ptx_sm100.cuh"
+
+namespace adapt {
+
+struct ConvChainParams {
+    int M;          // padded-flat positions: batch * H * (W + 2)
+    int m_tiles;    // ceil(M / 128)
+    int H, W;       // spatial size of input, intermediate and output
+    int row_pitch;  // W + 2
+    int N2;         // output channels = 4 * C
+    const float* scale1;  // [C]   folded BN of the 3x3
+    const float* bias1;
+    const float* scale2;  // [N2]  folded BN of the 1x1
+    const float* bias2;
+    __nv_bfloat16* out;   // [batch * H * W, N2]
+    int stages;           // phase-1 operand ring depth
+    int ring;             // residual slabs per epilogue warp (2..4)
+};
+
+constexpr int kChainBN2 = 128;      // phase-2 n-tile width
+constexpr int kChainThreads = 320;  // TMA + MMA + 8 epilogue warps
+constexpr int kChainMaxStages = 6;
+constexpr int kChainMaxRing = 4;
+
+template <int C, bool PAIR>
+__host__ __device__ constexpr int conv_chain_smem_bytes(int stages, int ring) {
+    constexpr int b1 = (PAIR ? C / 2 : C) * 128;  // one k-block of the 3x3's weights held by this CTA
+    constexpr bool resident = !PAIR;
+    constexpr int c_blocks = C / 64;
+    // (a phase-2 stage -- one n-tile of the 1x1's weights, 16 KiB per CTA -- lives in the A slot of a ring stage)
+    const int ring1 = stages * kRow3ABytes + (resident ? 9 * c_blocks * b1 : stages * 3 * b1);
+    const int a2 = c_blocks * kABytes;
+    const int slabs = kEpiWarps * ring * kEpiSlabBytes;
+    const int sb = 2 * (C + 4 * C) * 4;
+    return ring1 + a2 + slabs + sb + 1024 /*barriers*/ + 1024 /*alignment*/;
+}
+
+template <int C, bool PAIR>
+__global__ void __launch_bounds__(kChainThreads, 1)
+conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w2,
+                  const __grid_constant__ CUtensorMap tmap_w3, const __grid_constant__ CUtensorMap tmap_res,
+                  const ConvChainParams p) {
+    static_assert(C == 64 || C == 128, "chain kernel: C = 64 (single CTA) or 128 (CTA pair)");
+    static_assert(PAIR == (C == 128), "C = 128 runs on CTA pairs, C = 64 on single CTAs");
+    constexpr int CL = PAIR ? 2 : 1;
+    constexpr bool RESIDENT = !PAIR;             // the 3x3's weights stay in shared memory
+    constexpr int c_blocks = C / 64;             // k-blocks per tap (phase 1) = k-blocks of phase 2
+    constexpr int k_iters = 3 * c_blocks;        // phase-1 pipeline steps per tile (one per filter row and channel block)
+    constexpr int n2_tiles = 4 * C / kChainBN2;  // 2 or 4 (even: n-tile n uses accumulator n & 1)
+    constexpr int kB1 = (PAIR ? C / 2 : C) * 128;
+    constexpr int kB2 = (PAIR ? kChainBN2 / 2 : kChainBN2) * 128;
+    constexpr int kW3Tile = c_blocks * kB2;      // one phase-2 n-tile of weights held by this CTA (16 KiB)
+    static_assert(kW3Tile <= kRow3ABytes, "a phase-2 weight tile must fit the A slot of a ring stage");
+    constexpr uint32_t kAcc2Col = 256;           // TMEM: acc1 at columns [0, C), acc2[b] at 256 + 128 b
+    constexpr uint16_t kClusterMask = static_cast<uint16_t>((1u << CL) - 1);
+    const int kStages = p.stages;
+    const uint32_t ring = static_cast<uint32_t>(p.ring);
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem_a = smem;
+    uint8_t* smem_b1 = smem_a + kStages * kRow3ABytes;
+    uint8_t* smem_a2 = smem_b1 + (RESIDENT ? 9 * c_blocks * kB1 : kStages * 3 * kB1);
+    uint8_t* smem_epi = smem_a2 + c_blocks * kABytes;
+    float* smem_sb = reinterpret_cast<float*>(smem_epi + kEpiWarps * p.ring * kEpiSlabBytes);  // scale1 bias1 scale2 bias2
+    uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(smem_sb) + 2 * (C + 4 * C) * 4);
+    uint64_t* full_bar = bars;                               // [kChainMaxStages]
+    uint64_t* empty_bar = bars + kChainMaxStages;            // [kChainMaxStages]
+    uint64_t* acc1_full = bars + 2 * kChainMaxStages;        // [1]
+    uint64_t* a2_full = acc1_full + 1;                       // [1]
+    uint64_t* acc2_full = a2_full + 1;                       // [2]
+    uint64_t* acc2_empty = acc2_full + 2;                    // [2]
+    uint64_t* w_full = acc2_empty + 2;                       // [1] resident weights
+    uint64_t* res_bar = w_full + 1;                          // [kEpiWarps][kChainMaxRing]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + kEpiWarps * kChainMaxRing);
+    constexpr int kNumBars = 2 * kChainMaxStages + 1 + 1 + 2 + 2 + 1 + kEpiWarps * kChainMaxRing;
+
+    const int warp_idx = __shfl_sync(0xffffffff, threadIdx.x / 32, 0);
+    const int lane = threadIdx.x % 32;
+    const int cl_rank = PAIR ? static_cast<int>(ptx::cluster_ctarank()) : 0;
+    const int num_units = (p.m_tiles + CL - 1) / CL;
+    const int unit0 = blockIdx.x / CL;
+    const int unit_step = gridDim.x / CL;
+    auto tile_at = [&](int i, int& m_blk, bool& m_valid) -> bool {
+        const int u = unit0 + i * unit_step;
+        if (u >= num_units) return false;
+        m_blk = u * CL + cl_rank;
+        m_valid = m_blk < p.m_tiles;  // (a pair's last unit may hang over the end of M)
+        return true;
+    };
+
+    if (warp_idx == 0) {
+        for (int i = lane; i < kNumBars; i += 32) {
+            uint32_t count = 1;
+            if (&bars[i] == a2_full) count = kEpiWarps * CL;                     // every epilogue warp (of both CTAs)
+            if (&bars[i] == acc2_empty || &bars[i] == acc2_empty + 1) count = 4 * CL;  // the draining group (of both CTAs)
+            ptx::mbar_init(&bars[i], count);
+        }
+        ptx::fence_mbar_init();
+    } else if (warp_idx == 2 && lane == 0) {
+        ptx::prefetch_tmap(&tmap_a);
+        ptx::prefetch_tmap(&tmap_w2);
+        ptx::prefetch_tmap(&tmap_w3);
+        ptx::prefetch_tmap(&tmap_res);
+    }
+    if (warp_idx == 1) {
+        if (PAIR) {
+            ptx::tmem_alloc_pair(tmem_slot, 512);
+            ptx::tmem_relinquish_pair();
+        } else {
+            ptx::tmem_alloc(tmem_slot, 512);
+            ptx::tmem_relinquish();
+        }
+    }
+    // folded BatchNorm constants of both layers -> shared memory, once per CTA (weights: nothing upstream writes them)
+    for (int i = threadIdx.x; i < C; i += blockDim.x) {
+        smem_sb[i] = __ldg(p.scale1 + i);
+        smem_sb[C + i] = __ldg(p.bias1 + i);
+    }
+    for (int i = threadIdx.x; i < 4 * C; i += blockDim.x) {
+        smem_sb[2 * C + i] = __ldg(p.scale2 + i);
+        smem_sb[2 * C + 4 * C + i] = __ldg(p.bias2 + i);
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (CL > 1) ptx::cluster_sync();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    ptx::griddep_launch_dependents();
+    if (RESIDENT && warp_idx == 0 && ptx::elect_one()) {
+        // the 3x3's weights, once: no kernel writes them, so this runs ahead of the dependency wait
+        ptx::mbar_expect_tx(w_full, 9 * c_blocks * kB1);
+        for (int kb = 0; kb < 9 * c_blocks; ++kb) ptx::tma_load_2d(smem_b1 + kb * kB1, &tmap_w2, w_full, kb * kBlockK, 0);
+    }
+    ptx::griddep_wait();
+
+    if (warp_idx == 0) {
+        // ===================== phase-1 producer =====================
+        int stage = 0;
+        uint32_t phase = 0;
+        int m_blk_raw = 0;
+        bool m_valid = true;
+        for (int ti = 0; tile_at(ti, m_blk_raw, m_valid); ++ti) {
+            const int m_blk = m_valid ? m_blk_raw : p.m_tiles - 1;
+            const int m0 = m_blk * kBlockM;
+            const int rest = m0 / p.row_pitch;
+            const int q0 = m0 - rest * p.row_pitch;
+            const int img0 = rest / p.H;
+            const int p0 = rest - img0 * p.H;
+            int tap_r = 0, cb = 0;
+            for (int it = 0; it < k_iters; ++it) {
+                ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+                if (ptx::elect_one()) {
+                    uint8_t* a_dst = smem_a + stage * kRow3ABytes;
+                    if (PAIR) {
+                        if (cl_rank == 0) ptx::mbar_expect_tx(&full_bar[stage], 2 * (kRow3ABytes + 3 * kB1));
+                        ptx::tma_load_im2col_4d_pair(a_dst, &tmap_a, &full_bar[stage], cb * kBlockK, q0 - 1, p0 - 1, img0, 0,
+                                                     static_cast<uint16_t>(tap_r));
+#pragma unroll
+                        for (int s3 = 0; s3 < 3; ++s3) {
+                            const int kbi = (tap_r * 3 + s3) * c_blocks + cb;
+                            ptx::tma_load_2d_pair(smem_b1 + (stage * 3 + s3) * kB1, &tmap_w2, &full_bar[stage], kbi * kBlockK,
+                                                  cl_rank * (C / 2));
+                        }
+                    } else {
+                        ptx::mbar_expect_tx(&full_bar[stage], kRow3ABytes);
+                        ptx::tma_load_im2col_4d(a_dst, &tmap_a, &full_bar[stage], cb * kBlockK, q0 - 1, p0 - 1, img0, 0,
+                                                static_cast<uint16_t>(tap_r));
+                    }
+                }
+                __syncwarp();
+                if (++cb == c_blocks) {
+                    cb = 0;
+                    ++tap_r;
+                }
+                if (++stage == kStages) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+            // phase-2 stages: one n-tile of the 1x1's weights each, in the A slot of the stage
+            for (int n2 = 0; n2 < n2_tiles; ++n2) {
+                ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+                if (ptx::elect_one()) {
+                    uint8_t* w_dst = smem_a + stage * kRow3ABytes;
+                    if (PAIR) {
+                        if (cl_rank == 0) ptx::mbar_expect_tx(&full_bar[stage], 2 * kW3Tile);
+#pragma unroll
+                        for (int kb = 0; kb < c_blocks; ++kb)
+                            ptx::tma_load_2d_pair(w_dst + kb * kB2, &tmap_w3, &full_bar[stage], kb * kBlockK,
+                                                  n2 * kChainBN2 + cl_rank * (kChainBN2 / 2));
+                    } else {
+                        ptx::mbar_expect_tx(&full_bar[stage], kW3Tile);
+#pragma unroll
+                        for (int kb = 0; kb < c_blocks; ++kb)
+                            ptx::tma_load_2d(w_dst + kb * kB2, &tmap_w3, &full_bar[stage], kb * kBlockK, n2 * kChainBN2);
+                    }
+                }
+                __syncwarp();
+                if (++stage == kStages) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+        }
+    } else if (warp_idx == 1) {
+        // ===================== MMA issuer =====================
+        constexpr uint32_t idesc1 = ptx::make_idesc_bf16_f32(PAIR ? 2 * kBlockM : kBlockM, C);
+        constexpr uint32_t idesc2 = ptx::make_idesc_bf16_f32(PAIR ? 2 * kBlockM : kBlockM, kChainBN2);
+        int stage = 0;
+        uint32_t phase = 0;
+        int m_blk = 0;
+        bool m_valid = true;
+        uint32_t j = 0;
+        if (RESIDENT) ptx::mbar_wait(w_full, 0);
+        for (int ti = 0; !(PAIR && cl_rank != 0) && tile_at(ti, m_blk, m_valid); ++ti) {
+            // ---- phase 1: acc1 = im2col(x) . W2^T   (acc1 is free: the A2 tile of the previous unit was complete,
+            // i.e. acc1 fully read, before that unit's phase 2 was issued)
+            ptx::tc_fence_after();
+            int tap_r = 0, cb = 0;
+            for (int it = 0; it < k_iters; ++it) {
+                ptx::mbar_wait(&full_bar[stage], phase);
+                ptx::tc_fence_after();
+                if (ptx::elect_one()) {
+                    const uint32_t a_base = ptx::smem_u32(smem_a + stage * kRow3ABytes);
+#pragma unroll
+                    for (int s3 = 0; s3 < 3; ++s3) {
+                        const int kbi = (tap_r * 3 + s3) * c_blocks + cb;
+                        const uint64_t a_desc = ptx::make_kmajor_sw128_desc(a_base + s3 * (kBlockK * 2));
+                        const uint64_t b_desc =
+                            ptx::make_kmajor_sw128_desc(ptx::smem_u32(smem_b1 + (RESIDENT ? kbi : stage * 3 + s3) * kB1));
+#pragma unroll
+                        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+                            if (PAIR)
+                                ptx::umma_bf16_ss_pair(tmem_base, a_desc + 2 * k, b_desc + 2 * k, idesc1, (it | s3 | k) != 0 ? 1u : 0u);
+                            else
+                                ptx::umma_bf16_ss(tmem_base, a_desc + 2 * k, b_desc + 2 * k, idesc1, (it | s3 | k) != 0 ? 1u : 0u);
+                        }
+                    }
+                    if (PAIR) {
+                        ptx::umma_commit_pair(&empty_bar[stage], kClusterMask);
+                        if (it == k_iters - 1) ptx::umma_commit_pair(acc1_full, kClusterMask);
+                    } else {
+                        ptx::umma_commit(&empty_bar[stage]);
+                        if (it == k_iters - 1) ptx::umma_commit(acc1_full);
+                    }
+                }
+                __syncwarp();
+                if (++cb == c_blocks) {
+                    cb = 0;
+                    ++tap_r;
+                }
+                if (++stage == kStages) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+            // ---- phase 2: acc2[n & 1] = A2 . W3[n]^T for every 128-column n-tile
+            if (PAIR)
+                ptx::mbar_wait_cluster(a2_full, static_cast<uint32_t>(ti) & 1);  // the peer CTA's warps arrive too
+            else
+                ptx::mbar_wait(a2_full, static_cast<uint32_t>(ti) & 1);
+            ptx::tc_fence_after();
+            for (int n2 = 0; n2 < n2_tiles; ++n2, ++j) {
+                const uint32_t buf = j & 1, use = j >> 1;
+                ptx::mbar_wait(&acc2_empty[buf], (use & 1) ^ 1);
+                ptx::mbar_wait(&full_bar[stage], phase);
+                ptx::tc_fence_after();
+                if (ptx::elect_one()) {
+                    const uint32_t tmem_d = tmem_base + kAcc2Col + buf * kChainBN2;
+                    const uint32_t w3_base = ptx::smem_u32(smem_a + stage * kRow3ABytes);
+#pragma unroll
+                    for (int kb = 0; kb < c_blocks; ++kb) {
+                        const uint64_t a_desc = ptx::make_kmajor_sw128_desc(ptx::smem_u32(smem_a2 + kb * kABytes));
+                        const uint64_t b_desc = ptx::make_kmajor_sw128_desc(w3_base + kb * kB2);
+#pragma unroll
+                        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+                            if (PAIR)
+                                ptx::umma_bf16_ss_pair(tmem_d, a_desc + 2 * k, b_desc + 2 * k, idesc2, (kb | k) != 0 ? 1u : 0u);
+                            else
+                                ptx::umma_bf16_ss(tmem_d, a_desc + 2 * k, b_desc + 2 * k, idesc2, (kb | k) != 0 ? 1u : 0u);
+                        }
+                    }
+                    if (PAIR) {
+                        ptx::umma_commit_pair(&empty_bar[stage], kClusterMask);
+                        ptx::umma_commit_pair(&acc2_full[buf], kClusterMask);
+                    } else {
+                        ptx::umma_commit(&empty_bar[stage]);
+                        ptx::umma_commit(&acc2_full[buf]);
+                    }
+                }
+                __syncwarp();
+                if (++stage == kStages) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+        }
+    } else if (warp_idx < 2 + kEpiWarps) {
+        // ===================== epilogue =====================
+        const int epi_warp = warp_idx - 2;
+        const int group = epi_warp >> 2;
+        const int lane_group = warp_idx & 3;  // TMEM lanes this warp may touch: [32 * lane_group, +32)
+        uint8_t* my_slabs = smem_epi + epi_warp * p.ring * kEpiSlabBytes;
+        const uint32_t slabs_sa = ptx::smem_u32(my_slabs);
+        const uint32_t sb_sa = ptx::smem_u32(smem_sb);
+        const uint32_t a2_sa = ptx::smem_u32(smem_a2);
+        uint64_t* my_res_bar = res_bar + epi_warp * kChainMaxRing;
+        uint32_t res_par = 0, slot = 0;
+        const uint32_t taddr_lane = tmem_base + (static_cast<uint32_t>(lane_group * 32) << 16);
+
+        // residual prefetch cursor: this warp's chunks in consumption order (tile, n-tile = group, group + 2, .., chunk)
+        int ri_ti = 0, ri_n2 = group, ri_c = 0, ri_q = 0, ri_p = 0, ri_img = 0;
+        uint32_t ri_slot = 0;
+        bool ri_live = false, ri_more = true;
+        auto ri_locate = [&]() {
+            int mb = 0;
+            bool mv = true;
+            ri_live = false;
+            ri_more = tile_at(ri_ti, mb, mv);
+            if (ri_more) {
+                const int m0 = mb * kBlockM + lane_group * 32;
+                const int rest = m0 / p.row_pitch;
+                ri_q = m0 - rest * p.row_pitch;
+                ri_img = rest / p.H;
+                ri_p = rest - ri_img * p.H;
+                ri_live = mv && m0 < p.M;
+            }
+        };
+        auto issue_residual = [&]() {
+            if (ri_live && lane == 0) {
+                ptx::mbar_expect_tx(&my_res_bar[ri_slot], kEpiSlabBytes);
+                ptx::tma_load_im2col_4d(my_slabs + ri_slot * kEpiSlabBytes, &tmap_res, &my_res_bar[ri_slot],
+                                        ri_n2 * kChainBN2 + ri_c * kEpiCols, ri_q, ri_p, ri_img, 0, 0);
+            }
+            if (++ri_slot == ring) ri_slot = 0;
+            if (++ri_c == kChainBN2 / kEpiCols) {
+                ri_c = 0;
+                ri_n2 += 2;
+                if (ri_n2 >= n2_tiles) {
+                    ri_n2 = group;
+                    ++ri_ti;
+                    ri_locate();
+                }
+            }
+        };
+        ri_locate();
+        for (uint32_t i = 0; i + 1 < ring; ++i) issue_residual();  // prime: ring - 1 chunks in flight
+
+        int m_blk = 0;
+        bool m_valid = true;
+        uint32_t uses = 0;  // n-tiles this group has drained so far (accumulator phase)
+        for (int ti = 0; tile_at(ti, m_blk, m_valid); ++ti) {
+            const int m_row0 = m_blk * kBlockM + lane_group * 32;
+            const bool slab_ok = m_valid && m_row0 < p.M;
+            // ---- epilogue 1: acc1 -> relu(acc * s + b) -> bf16 -> the A2 operand tile (K-major, 128-byte swizzle)
+            ptx::mbar_wait(acc1_full, static_cast<uint32_t>(ti) & 1);
+            ptx::tc_fence_after();
+            {
+                const int row = lane_group * 32 + lane;
+#pragma unroll 1
+                for (int u = group; u < C / 32; u += 2) {  // 32-column units alternate between the two groups
+                    uint32_t v[32];
+                    ptx::tmem_ld_32x32b_x32(taddr_lane + u * 32, v);
+                    ptx::tmem_ld_wait();
+                    const uint32_t sc = sb_sa + u * 32 * 4, bi = sb_sa + (C + u * 32) * 4;
+                    const uint32_t dst = a2_sa + (u >> 1) * kABytes + row * 128;
+#pragma unroll
+                    for (int jj = 0; jj < 4; ++jj) {  // 8 columns = one 16-byte unit of this thread's row
+                        const float4 s0 = ptx::lds128f(sc + jj * 32), s1 = ptx::lds128f(sc + jj * 32 + 16);
+                        const float4 b0 = ptx::lds128f(bi + jj * 32), b1 = ptx::lds128f(bi + jj * 32 + 16);
+                        const uint32_t* vv = &v[jj * 8];
+                        uint4 ov;
+                        ov.x = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[0]), s0.x, b0.x), fmaf(__uint_as_float(vv[1]), s0.y, b0.y));
+                        ov.y = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[2]), s0.z, b0.z), fmaf(__uint_as_float(vv[3]), s0.w, b0.w));
+                        ov.z = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[4]), s1.x, b1.x), fmaf(__uint_as_float(vv[5]), s1.y, b1.y));
+                        ov.w = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[6]), s1.z, b1.z), fmaf(__uint_as_float(vv[7]), s1.w, b1.w));
+                        const int unit16 = (u & 1) * 4 + jj;
+                        ptx::sts128(dst + ((unit16 ^ (row & 7)) << 4), ov);
+                    }
+                }
+                ptx::fence_proxy_async_smem();  // generic-proxy writes -> visible to the tensor core's reads
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) {
+                    if (PAIR)
+                        ptx::mbar_arrive_remote_release(a2_full, 0);
+                    else
+                        ptx::mbar_arrive(a2_full);
+                }
+            }
+            // ---- epilogue 2: this group's n-tiles
+#pragma unroll 1
+            for (int n2 = group; n2 < n2_tiles; n2 += 2, ++uses) {
+                ptx::mbar_wait(&acc2_full[group], uses & 1);
+                ptx::tc_fence_after();
+                const uint32_t taddr = taddr_lane + kAcc2Col + group * kChainBN2;
+#pragma unroll 1
+                for (int c = 0; c < kChainBN2 / kEpiCols; ++c) {
+                    uint32_t v0[32], v1[32];
+                    ptx::tmem_ld_32x32b_x32(taddr + c * kEpiCols, v0);
+                    ptx::tmem_ld_32x32b_x32(taddr + c * kEpiCols + 32, v1);
+                    ptx::tmem_ld_wait();
+                    if (c == kChainBN2 / kEpiCols - 1) {
+                        ptx::tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) {
+                            if (PAIR)
+                                ptx::mbar_arrive_remote(&acc2_empty[group], 0);
+                            else
+                                ptx::mbar_arrive(&acc2_empty[group]);
+                        }
+                    }
+                    const uint32_t slab = slabs_sa + slot * kEpiSlabBytes;
+                    const uint32_t this_slot = slot;
+                    if (++slot == ring) slot = 0;
+                    if (!slab_ok) {
+                        __syncwarp();
+                        issue_residual();
+                        continue;
+                    }
+                    ptx::mbar_wait(&my_res_bar[this_slot], (res_par >> this_slot) & 1);
+                    res_par ^= (1u << this_slot);
+                    const int col0 = n2 * kChainBN2 + c * kEpiCols;
+                    const uint32_t sc = sb_sa + (2 * C + col0) * 4, bi = sb_sa + (2 * C + 4 * C + col0) * 4;
+#pragma unroll
+                    for (int jj = 0; jj < 8; ++jj) {
+                        const uint32_t* vv = (jj < 4) ? &v0[jj * 8] : &v1[(jj - 4) * 8];
+                        const float4 s0 = ptx::lds128f(sc + jj * 32), s1 = ptx::lds128f(sc + jj * 32 + 16);
+                        const float4 b0 = ptx::lds128f(bi + jj * 32), b1 = ptx::lds128f(bi + jj * 32 + 16);
+                        float y[8];
+                        y[0] = fmaf(__uint_as_float(vv[0]), s0.x, b0.x);
+                        y[1] = fmaf(__uint_as_float(vv[1]), s0.y, b0.y);
+                        y[2] = fmaf(__uint_as_float(vv[2]), s0.z, b0.z);
+                        y[3] = fmaf(__uint_as_float(vv[3]), s0.w, b0.w);
+                        y[4] = fmaf(__uint_as_float(vv[4]), s1.x, b1.x);
+                        y[5] = fmaf(__uint_as_float(vv[5]), s1.y, b1.y);
+                        y[6] = fmaf(__uint_as_float(vv[6]), s1.z, b1.z);
+                        y[7] = fmaf(__uint_as_float(vv[7]), s1.w, b1.w);
+                        const uint32_t sw = ((jj ^ (lane & 7)) << 4) + lane * 128;
+                        const uint4 rv = ptx::lds128(slab + sw);
+                        const uint32_t r[4] = {rv.x, rv.y, rv.z, rv.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            y[2 * e] += __uint_as_float(r[e] << 16);
+                            y[2 * e + 1] += __uint_as_float(r[e] & 0xffff0000u);
+                        }
+                        uint4 ov;
+                        ov.x = ptx::pack_bf16x2_relu(y[0], y[1]);
+                        ov.y = ptx::pack_bf16x2_relu(y[2], y[3]);
+                        ov.z = ptx::pack_bf16x2_relu(y[4], y[5]);
+                        ov.w = ptx::pack_bf16x2_relu(y[6], y[7]);
+                        ptx::sts128(slab + sw, ov);
+                    }
+                    __syncwarp();
+                    {
+                        // coalesced write-out, padded-flat position -> pixel (the two overhang positions of a row are dropped)
+                        const int ch = lane & 7;
+                        __nv_bfloat16* gcol = p.out + col0 + ch * 8;
+                        int m = m_row0 + (lane >> 3);
+                        int rest = m / p.row_pitch;
+                        int q = m - rest * p.row_pitch;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int row = i * 4 + (lane >> 3);
+                            const uint4 val = ptx::lds128(slab + row * 128 + ((ch ^ (row & 7)) << 4));
+                            if (m < p.M && q < p.W)
+                                *reinterpret_cast<uint4*>(gcol + (static_cast<size_t>(rest) * p.W + q) * p.N2) = val;
+                            m += 4;
+                            q += 4;
+                            if (q >= p.row_pitch) {
+                                q -= p.row_pitch;
+                                ++rest;
+                            }
+                        }
+                    }
+                    __syncwarp();
+                    issue_residual();  // the slab just written out is free: refill it `ring - 1` chunks ahead
+                }
+            }
+        }
+    }
+
+    // ===================== teardown =====================
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (CL > 1) ptx::cluster_sync();
+    if (warp_idx == 1) {
+        ptx::tc_fence_after();
+        if (PAIR)
+            ptx::tmem_dealloc_pair(tmem_base, 512);
+        else
+            ptx::tmem_dealloc(tmem_base, 512);
+    }
+}
+
+}  // namespace adapt

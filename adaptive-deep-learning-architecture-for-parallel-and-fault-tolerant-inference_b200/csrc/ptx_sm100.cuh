@@ -154,6 +154,38 @@ __device__ __forceinline__ void mbar_arrive_remote(uint64_t* bar, uint32_t cta_r
         : "memory");
 }
 
+// Same, with release semantics at cluster scope: shared-memory data this CTA wrote before the arrive (and fenced
+// towards the async proxy) is what the waiting CTA's consumer sees after an acquire.cluster wait.
+__device__ __forceinline__ void mbar_arrive_remote_release(uint64_t* bar, uint32_t cta_rank) {
+    asm volatile(
+        "{\n\t"
+        ".reg .b32 remAddr32;\n\t"
+        "mapa.shared::cluster.u32 remAddr32, %0, %1;\n\t"
+        "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [remAddr32];\n\t"
+        "}\n"
+        ::"r"(smem_u32(bar)), "r"(cta_rank)
+        : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred P;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, P;\n\t"
+        "}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+    uint32_t spins = 0;
+    while (!mbar_try_wait_cluster(bar, parity)) {
+        if (++spins > (1u << 24)) __trap();
+    }
+}
+
 // ---- programmatic dependent launch: a kernel launched with programmatic stream serialization may start
 // while its predecessor in the stream is still running; griddep_wait() blocks until the predecessor has
 // completed and its writes are visible, griddep_launch_dependents() lets the successor start early.

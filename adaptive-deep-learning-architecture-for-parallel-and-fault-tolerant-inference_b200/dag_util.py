@@ -11,6 +11,7 @@ implicit-GEMM launch, ZeroPadding2D folded into the consumer, etc.
 from __future__ import annotations
 
 import json
+import os
 from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Sequence, Tuple
 
@@ -260,6 +261,7 @@ class Op:
     weight: int = -1
     out_f32: int = 0
     in_format: int = 0  # INGEST: N.IN_*
+    weight2: int = -1   # CONV_CHAIN: weight-table index of the 1x1
     layers: List[str] = field(default_factory=list)  # Keras layers this op covers
 
 
@@ -281,7 +283,7 @@ class StageProgram:
         o = (N.OpDesc * len(self.ops))()
         for i, p in enumerate(self.ops):
             o[i] = N.OpDesc(p.kind, p.inp, p.res, p.out, p.H, p.W, p.Cin, p.Ho, p.Wo, p.Cout, p.kh, p.kw, p.stride,
-                            p.pad, p.relu, p.weight, p.out_f32, p.in_format)
+                            p.pad, p.relu, p.weight, p.out_f32, p.in_format, p.weight2)
         return t, o
 
 
@@ -294,6 +296,41 @@ def cut_tensor_elems(model: Model, layer_name: str, mode: int) -> int:
     if len(shp) == 3:
         return shp[0] * shp[1] * _stored_c(shp[2], mode)
     return _stored_c(shp[0], mode)
+
+
+def chainable(o: "Op") -> bool:
+    """A `_2_conv` group the chain kernel can start from: 3x3 / stride 1 / pad 1, C -> C with C in {64, 128}, BN and ReLU
+    fused, no shortcut, on a map at least 28 wide (conv2 and conv3 of the ResNets)."""
+    return (o.kind == N.OP_CONV and o.kh == 3 and o.kw == 3 and o.stride == 1 and o.pad == 1 and o.relu == 1 and o.res < 0
+            and o.out_f32 == 0 and o.Cin == o.Cout and o.Cout in (64, 128) and o.W >= 28)
+
+
+def _chain_bottleneck_tails(ops: List["Op"], vt: List["VTensor"]) -> List["Op"]:
+    """Fuse every `_2_conv`(3x3)+bn+relu whose ONLY consumer is the block's `_3_conv`(1x1)+bn+add+relu into one
+    CONV_CHAIN op (csrc/conv_chain_sm100.cuh): the `_2_relu` tensor stays on chip.  The chained op takes the 1x1's place in
+    the program (in a block1 the shortcut convolution `_0_conv` sits between the two and must run first)."""
+    uses: Dict[int, List[int]] = {}
+    for i, o in enumerate(ops):
+        for t in (o.inp, o.res):
+            if t >= 0:
+                uses.setdefault(t, []).append(i)
+    drop, repl = set(), {}
+    for i, a in enumerate(ops):
+        if not chainable(a) or vt[a.out].role != N.T_INTERNAL or uses.get(a.out, []) == []:
+            continue
+        cons = uses[a.out]
+        if len(cons) != 1:
+            continue
+        j = cons[0]
+        b = ops[j]
+        if not (b.kind == N.OP_CONV and b.kh == 1 and b.kw == 1 and b.stride == 1 and b.pad == 0 and b.inp == a.out and b.res >= 0
+                and b.res != a.out and b.relu == 1 and b.out_f32 == 0 and b.Cin == a.Cout and b.Cout == 4 * a.Cout
+                and (b.H, b.W) == (a.Ho, a.Wo)):
+            continue
+        drop.add(i)
+        repl[j] = Op(N.OP_CONV_CHAIN, a.inp, b.out, res=b.res, H=a.H, W=a.W, Cin=a.Cin, Ho=a.Ho, Wo=a.Wo, Cout=b.Cout, kh=3, kw=3,
+                     stride=1, pad=1, relu=1, weight=a.weight, weight2=b.weight, layers=a.layers + b.layers)
+    return [repl.get(i, o) for i, o in enumerate(ops) if i not in drop]
 
 
 def compile_part(part: PartModel, windex: Dict[str, int], mode: int = N.MODE_BF16,
@@ -491,6 +528,8 @@ def compile_part(part: PartModel, windex: Dict[str, int], mode: int = N.MODE_BF1
     if vt[t_out].role == N.T_INPUT:
         raise RuntimeError("partition has no compute")
     vt[t_out].role = N.T_OUTPUT
+    if mode == N.MODE_BF16 and os.environ.get("ADAPT_CHAIN", "1") != "0":
+        ops = _chain_bottleneck_tails(ops, vt)
 
     # ---- liveness-based physical buffer assignment (internal tensors only)
     for i, o in enumerate(ops):

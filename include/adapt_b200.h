@@ -47,6 +47,10 @@ extern "C" {
 #define ADAPT_OP_AFFINE 5   /* stand-alone BatchNormalization and/or ReLU (a cut separated it from its  */
                             /* convolution): y = relu?(x * scale[c] + bias[c]); weight = -1: ReLU only  */
 #define ADAPT_OP_ZEROPAD 6  /* stand-alone ZeroPadding2D (a cut at conv1_pad / pool1_pad)               */
+#define ADAPT_OP_CONV_CHAIN 7 /* bf16 mode: convN_blockB_2_conv+bn+relu (3x3 / stride 1 / pad 1, C -> C) chained  */
+                            /* with _3_conv+bn+add+out (1x1, C -> 4C, shortcut, ReLU) in one kernel; the         */
+                            /* _2_relu tensor never reaches HBM.  C in {64, 128}, map width >= 28.               */
+                            /* weight = the 3x3's entry, weight2 = the 1x1's; Cin = C, Cout = 4C                  */
 
 /* tensor roles inside a stage program */
 #define ADAPT_T_INTERNAL 0  /* library-owned scratch activation                       */
@@ -87,6 +91,7 @@ typedef struct adapt_op_desc {
     int32_t weight;                  /* index into the weight table (CONV) or -1               */
     int32_t out_f32;                 /* CONV: write fp32 instead of the working dtype (logits) */
     int32_t in_format;               /* INGEST: ADAPT_IN_* (0 elsewhere)                       */
+    int32_t weight2;                 /* CONV_CHAIN: weight-table index of the 1x1 (-1 elsewhere) */
 } adapt_op_desc;
 
 /* INGEST input formats.  ADAPT_IN_F32 is the reference's queue contract: an fp32 NHWC image that already went
@@ -174,6 +179,17 @@ void adapt_stage_destroy(adapt_stage_t* stage);
 int adapt_conv2d_bf16(int device, const void* in, const void* w, const float* scale, const float* bias,
                       const void* residual, void* out, int out_is_f32, int batch, int H, int W, int Cin, int Cout,
                       int kh, int kw, int stride, int pad, int relu, int a_mode, int block_n, void* stream);
+
+/* Single-block entry point of ADAPT_OP_CONV_CHAIN (kernel-level parity tests and micro-benchmarks), all pointers
+ * DEVICE pointers on `device`:
+ *   mid = relu(conv3x3(in, w2) * scale1 + bias1)  rounded to bf16 (never stored),
+ *   out = relu(conv1x1(mid, w3) * scale2 + bias2 + residual)
+ *   in : bf16 NHWC [batch][H][W][C]      w2 : bf16 [C][3][3][C]      w3 : bf16 [4C][C]
+ *   residual, out : bf16 NHWC [batch][H][W][4C];  C in {64, 128}, W >= 28.
+ * Stands in for the layers convN_blockB_2_conv ... convN_blockB_out inside `model.predict` (reference src/node.py:177). */
+int adapt_conv_chain_bf16(int device, const void* in, const void* w2, const float* scale1, const float* bias1,
+                          const void* w3, const float* scale2, const float* bias2, const void* residual, void* out,
+                          int batch, int H, int W, int C, void* stream);
 
 /* Classifier head (Dense + softmax) for callers that must not allocate device memory.
  * This entry point has NO counterpart in the reference; it exists for users of this library whose

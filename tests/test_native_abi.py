@@ -39,10 +39,10 @@ def test_struct_layouts_match_header(pkg):
 
     assert ctypes.sizeof(_native.WeightDesc) == 3 * 8 + 4 * 4
     assert ctypes.sizeof(_native.TensorDesc) == 16
-    assert ctypes.sizeof(_native.OpDesc) == 18 * 4
+    assert ctypes.sizeof(_native.OpDesc) == 19 * 4
     hdr = open(os.path.join(ROOT, "include", "adapt_b200.h")).read()
     assert f"#define ADAPT_NOALLOC_MAX_LOGITS ({_native.NOALLOC_MAX_LOGITS // 1024} * 1024)" in hdr
-    for name, val in (("ADAPT_OP_ZEROPAD", _native.OP_ZEROPAD), ("ADAPT_OP_SOFTMAX", _native.OP_SOFTMAX),
+    for name, val in (("ADAPT_OP_ZEROPAD", _native.OP_ZEROPAD), ("ADAPT_OP_CONV_CHAIN", _native.OP_CONV_CHAIN), ("ADAPT_OP_SOFTMAX", _native.OP_SOFTMAX),
                       ("ADAPT_MODE_FP32_CHECK", _native.MODE_FP32_CHECK), ("ADAPT_T_OUTPUT", _native.T_OUTPUT)):
         assert re.search(rf"#define {name} {val}\b", hdr), name
 

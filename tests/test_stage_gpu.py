@@ -106,6 +106,83 @@ def test_conv_kernel_matches_oracle(nat, case, block_n):
     np.testing.assert_allclose(got, ref, rtol=2 ** -7, atol=2e-3)
 
 
+# ------------------------------------------------------------------ chained 3x3 -> 1x1 + shortcut block tail
+CHAIN_CASES = [
+    # B, H, W, C
+    (2, 56, 56, 64),      # conv2 geometry: single CTA, resident 3x3 weights
+    (6, 56, 56, 64),      # more tiles than SMs: several units per CTA, residual ring across units
+    (1, 28, 28, 64),      # fewer tiles than SMs
+    (3, 28, 28, 128),     # conv3 geometry: CTA pairs, streamed weights
+    (16, 28, 28, 128),    # several units per pair
+    (1, 28, 28, 128),     # odd number of tiles: the last pair hangs over the end
+    (2, 29, 34, 128),     # rows / images that do not divide the tile
+    (3, 31, 30, 64),
+]
+
+
+@pytest.mark.parametrize("case", CHAIN_CASES)
+def test_conv_chain_kernel_matches_oracle(nat, case):
+    """`adapt_conv_chain_bf16` (convN_blockB_2_conv .. convN_blockB_out in one kernel) against the oracle's layer math
+    with the intermediate rounded to bf16 where the two-launch form stores it."""
+    from adapt_b200.executor import DeviceBuffer, unwire_activation, wire_activation
+
+    B, H, W, C = case
+    lib = nat.lib()
+    rng = np.random.default_rng(hash(case) % (2 ** 31))
+    x = KO.bf16_round(rng.standard_normal((B, H, W, C)).astype(np.float32))
+    w2 = KO.bf16_round((rng.standard_normal((3, 3, C, C)) / np.sqrt(9 * C)).astype(np.float32))
+    w3 = KO.bf16_round((rng.standard_normal((1, 1, C, 4 * C)) / np.sqrt(C)).astype(np.float32))
+    s1, b1 = rng.uniform(0.5, 1.5, C).astype(np.float32), rng.standard_normal(C).astype(np.float32)
+    s2, b2 = rng.uniform(0.5, 1.5, 4 * C).astype(np.float32), rng.standard_normal(4 * C).astype(np.float32)
+    res = KO.bf16_round(rng.standard_normal((B, H, W, 4 * C)).astype(np.float32))
+    mid = np.maximum(KO.conv2d(KO.zero_pad(x, 1), w2, np.zeros(C, np.float32), 1, "valid") * s1 + b1, 0)
+    mid = KO.bf16_round(mid.astype(np.float32))
+    ref = np.maximum(KO.conv2d(mid, w3, np.zeros(4 * C, np.float32), 1, "valid") * s2 + b2 + res, 0)
+
+    def up(a):
+        buf = DeviceBuffer(0, a.nbytes)
+        nat.check(lib.adapt_memcpy_h2d(0, buf.ptr, a.ctypes.data, a.nbytes, None))
+        return buf
+
+    bufs = [up(wire_activation(x, 0)), up(wire_activation(np.ascontiguousarray(w2.transpose(3, 0, 1, 2)), 0)), up(s1), up(b1),
+            up(wire_activation(np.ascontiguousarray(w3.transpose(3, 0, 1, 2)), 0)), up(s2), up(b2), up(wire_activation(res, 0))]
+    d_out = DeviceBuffer(0, B * H * W * 4 * C * 2)
+    nat.check(lib.adapt_memset(0, d_out.ptr, 0xFF, B * H * W * 4 * C * 2, None))   # NaN pattern: unwritten pixels show up
+    nat.check(lib.adapt_conv_chain_bf16(0, *[b.ptr for b in bufs], d_out.ptr, B, H, W, C, None))
+    raw = np.empty(B * H * W * 4 * C * 2, np.uint8)
+    nat.check(lib.adapt_memcpy_d2h(0, raw.ctypes.data, d_out.ptr, raw.nbytes, None))
+    nat.check(lib.adapt_stream_sync(0, None))
+    got = unwire_activation(raw, (B, H, W, 4 * C), 0)
+    for b in bufs + [d_out]:
+        b.free()
+    assert np.isfinite(got).all(), "pixels the kernel never wrote"
+    # the intermediate is rounded at the same point on both sides, but a value within half a bf16 ulp of a rounding
+    # boundary can land on either side (fp32 summation order): allow a few such flips through the 1x1
+    np.testing.assert_allclose(got, ref, rtol=2 ** -6, atol=2e-2)
+    assert np.abs(got - ref).mean() <= 2e-3
+
+
+def test_chained_and_unchained_programs_agree(model50, monkeypatch):
+    """The stage program with CONV_CHAIN ops (default) against the same layers as separate 3x3 and 1x1 launches
+    (ADAPT_CHAIN=0): same rounding points, so cut tensors agree to bf16 re-rounding and the probabilities to 1e-3
+    relative."""
+    from adapt_b200 import _native as N
+
+    x = KO.synthetic_images(3, seed=77, kind="normal")
+    outs = {}
+    for chain in ("1", "0"):
+        monkeypatch.setenv("ADAPT_CHAIN", chain)
+        p = _predictor(model50, mode="bf16", max_batch=3, end="conv3_block4_out")
+        n_chain = sum(o.kind == N.OP_CONV_CHAIN for o in p.ex.program.ops)
+        assert n_chain == (7 if chain == "1" else 0)
+        q = _predictor(model50, mode="bf16", max_batch=3)
+        outs[chain] = (p.run(x), q.run(x))
+        p.close()
+        q.close()
+    assert rel_err(outs["1"][0], outs["0"][0]) <= 2e-2
+    assert rel_err(outs["1"][1], outs["0"][1]) <= 1e-3
+
+
 # ------------------------------------------------------------------ whole network
 @pytest.mark.parametrize("kind,batch", [("caffe", 4), ("normal", 3), ("normal", 1)])
 def test_full_model_bf16(model50, oracle, kind, batch):
