@@ -109,7 +109,9 @@ SYMBOLS = {
     "adapt_event_record": (_I, [_I, _VP, _VP]),
     "adapt_event_sync": (_I, [_I, _VP]),
     "adapt_event_elapsed_ms": (_I, [_I, _VP, _VP, C.POINTER(C.c_float)]),
+    "adapt_event_query": (_I, [_I, _VP, C.POINTER(_I)]),
     "adapt_event_destroy": (_I, [_I, _VP]),
+    "adapt_debug_spin": (_I, [_I, _VP, _I]),
 }
 
 

@@ -267,7 +267,7 @@ struct ConvLaunch {
 
 // Launch record of the chained `_2_conv` (3x3) -> `_3_conv` (1x1 + shortcut + ReLU) kernel (conv_chain_sm100.cuh).
 struct ChainLaunch {
-    CUtensorMap tmap_a, tmap_w2, tmap_w3, tmap_res;
+    CUtensorMap tmap_a, tmap_w2, tmap_w3, tmap_res, tmap_out;
     adapt::ConvChainParams p;
     int C = 0;
     int smem = 0;
@@ -797,7 +797,9 @@ int build_chain_launch(ChainLaunch* L, int batch, int H, int W, int C, const voi
     p.ring = env_int("ADAPT_CHAIN_RING", 2);
     if (p.ring < 2) p.ring = 2;
     if (p.ring > adapt::kChainMaxRing) p.ring = adapt::kChainMaxRing;
-    int stages = adapt::kChainMaxStages;
+    p.l2_prefetch = env_int("ADAPT_CHAIN_L2PF", 1);
+    int stages = env_int("ADAPT_CHAIN_STAGES", adapt::kChainMaxStages);
+    if (stages > adapt::kChainMaxStages) stages = adapt::kChainMaxStages;
     auto bytes = [&](int st) {
         return pair ? adapt::conv_chain_smem_bytes<128, true>(st, p.ring) : adapt::conv_chain_smem_bytes<64, false>(st, p.ring);
     };
@@ -821,7 +823,21 @@ int build_chain_launch(ChainLaunch* L, int batch, int H, int W, int C, const voi
     rc = encode_tiled_2d_bf16(&L->tmap_w3, w3, (uint64_t)C, (uint64_t)4 * C, adapt::kBlockK,
                               (uint32_t)(pair ? adapt::kChainBN2 / 2 : adapt::kChainBN2));
     if (rc) return rc;
-    return encode_padded_flat_slab_bf16(&L->tmap_res, residual, 4 * C, W, H, batch);
+    rc = encode_padded_flat_slab_bf16(&L->tmap_res, residual, 4 * C, W, H, batch);
+    if (rc) return rc;
+    // output as (channel, column, image row over all images): 64-channel x 32-column x 1-row boxes, clipped at the edges
+    DriverApi* d;
+    rc = get_driver(&d);
+    if (rc) return rc;
+    cuuint64_t dims[3] = {(cuuint64_t)4 * C, (cuuint64_t)W, (cuuint64_t)batch * H};
+    cuuint64_t strides[2] = {(cuuint64_t)4 * C * 2, (cuuint64_t)W * 4 * C * 2};
+    cuuint32_t box[3] = {(cuuint32_t)adapt::kEpiCols, 32, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = d->encodeTiled(&L->tmap_out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, out, dims, strides, box, estr,
+                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(ADAPT_ECUDA, "conv chain: output tensor map refused (%d)", (int)r);
+    return ADAPT_OK;
 }
 
 template <int C, bool PAIR>
@@ -847,7 +863,8 @@ cudaError_t launch_chain_ex(const ChainLaunch& L, cudaStream_t s) {
     }
     cfg.attrs = attr;
     cfg.numAttrs = n;
-    return cudaLaunchKernelEx(&cfg, adapt::conv_chain_kernel<C, PAIR>, L.tmap_a, L.tmap_w2, L.tmap_w3, L.tmap_res, L.p);
+    return cudaLaunchKernelEx(&cfg, adapt::conv_chain_kernel<C, PAIR>, L.tmap_a, L.tmap_w2, L.tmap_w3, L.tmap_res, L.tmap_out,
+                              L.p);
 }
 
 int run_chain_launch(const ChainLaunch& L, cudaStream_t s) {
@@ -1431,7 +1448,7 @@ int adapt_stage_profile(adapt_stage_t* st, int slot, int batch, void* stream_v, 
     return ADAPT_OK;
 }
 
-int adapt_stage_time_kind(adapt_stage_t* st, int slot, int batch, void* stream_v, int kind, int reps, float* ms_per_rep,
+int adapt_stage_time_kind(adapt_stage_t* st, int slot, int batch, void* stream_v, int kind_mask, int reps, float* ms_per_rep,
                           int* n_launches) {
     CONFIG_LOCK();
     Plan* plan = nullptr;
@@ -1440,7 +1457,7 @@ int adapt_stage_time_kind(adapt_stage_t* st, int slot, int batch, void* stream_v
     if (!ms_per_rep || reps <= 0) return fail(ADAPT_EINVAL, "time_kind: need reps > 0 and an output pointer");
     std::vector<Step> only;
     for (const Step& s : plan->steps[slot])
-        if (s.kind == kind) only.push_back(s);
+        if ((kind_mask >> s.kind) & 1) only.push_back(s);
     if (n_launches) *n_launches = (int)only.size();
     if (only.empty()) {
         *ms_per_rep = 0.f;
@@ -1887,6 +1904,31 @@ int adapt_event_elapsed_ms(int device, void* start, void* stop, float* ms_out) {
     CUDA_TRY(cudaEventElapsedTime(ms_out, reinterpret_cast<cudaEvent_t>(start), reinterpret_cast<cudaEvent_t>(stop)));
     return ADAPT_OK;
 }
+int adapt_event_query(int device, void* event, int* done_out) {
+    if (!done_out) return fail(ADAPT_EINVAL, "event_query: null");
+    int rc = require_device(device);
+    if (rc) return rc;
+    cudaError_t e = cudaEventQuery(reinterpret_cast<cudaEvent_t>(event));
+    if (e == cudaSuccess) {
+        *done_out = 1;
+    } else if (e == cudaErrorNotReady) {
+        cudaGetLastError();
+        *done_out = 0;
+    } else {
+        return fail(ADAPT_ECUDA, "cudaEventQuery: %s", cudaGetErrorString(e));
+    }
+    return ADAPT_OK;
+}
+
+int adapt_debug_spin(int device, void* stream, int microseconds) {
+    if (microseconds <= 0) return ADAPT_OK;
+    int rc = require_device(device);
+    if (rc) return rc;
+    adapt::spin_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>((long long)microseconds * 1000LL);
+    CUDA_TRY(cudaGetLastError());
+    return ADAPT_OK;
+}
+
 int adapt_event_destroy(int device, void* event) {
     int rc = require_device(device);
     if (rc) return rc;

@@ -14,7 +14,10 @@
 // of W + 2 positions, the last two of each row discarded), one im2col load of 136 positions per (filter row, channel
 // block) feeds the three horizontal taps through shifted descriptors.  Phase 2 therefore also runs on padded-flat
 // positions; its residual tile is fetched with an im2col-mode TMA load that walks the same positions (zero-filled
-// where a position is not a pixel) and its output leaves through the position -> pixel st.global write-out.
+// where a position is not a pixel) and its output leaves through tiled TMA stores on a (channel, column, image row)
+// view of the output: a warp's 32 consecutive positions touch up to three image rows, so the same slab is stored up to
+// three times with the column coordinate shifted by whole rows -- positions of other rows and the two overhang
+// positions fall outside the tensor and are clipped by the store.
 //
 //   warp 0      TMA producer: per unit, the phase-1 stages (A row segments; the three B tiles of a filter row unless
 //               the 3x3's weights are resident), then one stage per phase-2 n-tile (`_3_conv` weights), all through
@@ -50,6 +53,8 @@ struct ConvChainParams {
     __nv_bfloat16* out;   // [batch * H * W, N2]
     int stages;           // phase-1 operand ring depth
     int ring;             // residual slabs per epilogue warp (2..4)
+    int l2_prefetch;      // 1: every epilogue warp pulls its residual rows of the NEXT unit towards L2 while it works
+                          // on this one (HBM latency is then hidden by L2, not by the depth of the slab ring)
 };
 
 constexpr int kChainBN2 = 128;      // phase-2 n-tile width
@@ -74,7 +79,7 @@ template <int C, bool PAIR>
 __global__ void __launch_bounds__(kChainThreads, 1)
 conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w2,
                   const __grid_constant__ CUtensorMap tmap_w3, const __grid_constant__ CUtensorMap tmap_res,
-                  const ConvChainParams p) {
+                  const __grid_constant__ CUtensorMap tmap_out, const ConvChainParams p) {
     static_assert(C == 64 || C == 128, "chain kernel: C = 64 (single CTA) or 128 (CTA pair)");
     static_assert(PAIR == (C == 128), "C = 128 runs on CTA pairs, C = 64 on single CTAs");
     constexpr int CL = PAIR ? 2 : 1;
@@ -137,6 +142,9 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         ptx::prefetch_tmap(&tmap_w2);
         ptx::prefetch_tmap(&tmap_w3);
         ptx::prefetch_tmap(&tmap_res);
+#ifndef DBG3
+        ptx::prefetch_tmap(&tmap_out);
+#endif
     }
     if (warp_idx == 1) {
         if (PAIR) {
@@ -389,6 +397,23 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         for (int ti = 0; tile_at(ti, m_blk, m_valid); ++ti) {
             const int m_row0 = m_blk * kBlockM + lane_group * 32;
             const bool slab_ok = m_valid && m_row0 < p.M;
+            const int rest_w = m_row0 / p.row_pitch;          // image row (over all images) of this warp's first position
+            const int q_w = m_row0 - rest_w * p.row_pitch;    // ... and its column in the padded-flat row
+            const int n_rows_w = (q_w + 31) / p.row_pitch + 1;  // image rows the 32 positions touch (1..3)
+            if ((p.l2_prefetch & 1) && lane == 0) {
+                int mb = 0;
+                bool mv = true;
+                if (tile_at(ti + 1, mb, mv) && mv && mb * kBlockM + lane_group * 32 < p.M) {
+                    const int m0 = mb * kBlockM + lane_group * 32;
+                    const int rest = m0 / p.row_pitch;
+                    const int q = m0 - rest * p.row_pitch;
+                    const int img = rest / p.H;
+                    const int pr = rest - img * p.H;
+                    for (int n2 = group; n2 < n2_tiles; n2 += 2)
+                        for (int c = 0; c < kChainBN2 / kEpiCols; ++c)
+                            ptx::tma_prefetch_im2col_4d(&tmap_res, n2 * kChainBN2 + c * kEpiCols, q, pr, img, 0, 0);
+                }
+            }
             // ---- epilogue 1: acc1 -> relu(acc * s + b) -> bf16 -> the A2 operand tile (K-major, 128-byte swizzle)
             ptx::mbar_wait(acc1_full, static_cast<uint32_t>(ti) & 1);
             ptx::tc_fence_after();
@@ -450,7 +475,11 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                     const uint32_t slab = slabs_sa + slot * kEpiSlabBytes;
                     const uint32_t this_slot = slot;
                     if (++slot == ring) slot = 0;
+                    uint8_t* slab_ptr = my_slabs + this_slot * kEpiSlabBytes;
                     if (!slab_ok) {
+                        // nothing is stored from this chunk: the newest store group may still be reading the slab the
+                        // prefetch is about to refill
+                        if (lane == 0) ptx::tma_store_wait_read<0>();
                         __syncwarp();
                         issue_residual();
                         continue;
@@ -488,36 +517,31 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                         ov.w = ptx::pack_bf16x2_relu(y[6], y[7]);
                         ptx::sts128(slab + sw, ov);
                     }
+                    ptx::fence_proxy_async_smem();  // slab writes -> visible to the TMA stores
                     __syncwarp();
-                    {
-                        // coalesced write-out, padded-flat position -> pixel (the two overhang positions of a row are dropped)
-                        const int ch = lane & 7;
-                        __nv_bfloat16* gcol = p.out + col0 + ch * 8;
-                        int m = m_row0 + (lane >> 3);
-                        int rest = m / p.row_pitch;
-                        int q = m - rest * p.row_pitch;
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            const int row = i * 4 + (lane >> 3);
-                            const uint4 val = ptx::lds128(slab + row * 128 + ((ch ^ (row & 7)) << 4));
-                            if (m < p.M && q < p.W)
-                                *reinterpret_cast<uint4*>(gcol + (static_cast<size_t>(rest) * p.W + q) * p.N2) = val;
-                            m += 4;
-                            q += 4;
-                            if (q >= p.row_pitch) {
-                                q -= p.row_pitch;
-                                ++rest;
-                            }
-                        }
+                    if (lane == 0) {
+                        // slab row r is position (rest_w, q_w + r): one store per image row the slab touches, the column
+                        // coordinate shifted back by whole padded-flat rows; whatever falls outside [0, W) is clipped
+                        for (int s = 0; s < ((p.l2_prefetch & 4) ? 0 : ((p.l2_prefetch & 2) ? 1 : n_rows_w)); ++s)
+                            ptx::tma_store_3d(&tmap_out, slab_ptr, col0, q_w - s * p.row_pitch, rest_w + s);
+#ifndef DBG2
+                        ptx::tma_store_commit();
+                        // every store group but the one just issued has read its slab: the previous chunk's slab is
+                        // free for the residual `ring - 1` chunks ahead
+                        ptx::tma_store_wait_read<1>();
+#endif
                     }
                     __syncwarp();
-                    issue_residual();  // the slab just written out is free: refill it `ring - 1` chunks ahead
+                    issue_residual();
                 }
             }
         }
     }
 
     // ===================== teardown =====================
+#ifndef DBG1
+    if (warp_idx >= 2 && warp_idx < 2 + kEpiWarps && lane == 0) ptx::tma_store_wait<0>();  // bulk stores landed before exit
+#endif
     ptx::tc_fence_before();
     __syncthreads();
     if (CL > 1) ptx::cluster_sync();

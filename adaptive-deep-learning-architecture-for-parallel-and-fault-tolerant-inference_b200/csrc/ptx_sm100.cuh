@@ -197,6 +197,15 @@ __device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* m, int x, int
                  : "memory");
 }
 
+// L2 prefetch of an im2col box (no shared-memory destination, no barrier)
+__device__ __forceinline__ void tma_prefetch_im2col_4d(const CUtensorMap* m, int c, int w, int h, int n, uint16_t off_w,
+                                                       uint16_t off_h) {
+    asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global.im2col [%0, {%1, %2, %3, %4}], {%5, %6};" ::"l"(
+                     reinterpret_cast<uint64_t>(m)),
+                 "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h)
+                 : "memory");
+}
+
 // two fp32 -> packed bf16x2 (round to nearest even), `lo` in the low half; the _relu form clamps negatives to 0
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     uint32_t d;
@@ -238,6 +247,13 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* s
     asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
                      reinterpret_cast<uint64_t>(m)),
                  "r"(smem_u32(smem_src)), "r"(x), "r"(y)
+                 : "memory");
+}
+// tiled 3-D store (the chain kernel's padded-flat write-out: channel, column, image row; out-of-range parts are clipped)
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, const void* smem_src, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
+                     reinterpret_cast<uint64_t>(m)),
+                 "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
                  : "memory");
 }
 // tiled 5-D store (the stem-by-phase epilogue: channel, column phase, unit column, row, image)

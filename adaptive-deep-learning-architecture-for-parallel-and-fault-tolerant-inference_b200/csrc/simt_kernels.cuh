@@ -342,6 +342,18 @@ __global__ void softmax_rows_kernel(const float* __restrict__ logits, float* __r
 }
 
 // ---------------------------------------------------------------------------------------------
+// Fault injection for the straggler tests (adapt_debug_spin): keeps the stream busy for `ns` nanoseconds of the
+// global timer without touching memory -- a stage that is alive but slow.
+__global__ void spin_kernel(long long ns) {
+    unsigned long long t0, t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    do {
+        __nanosleep(1000);
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    } while (static_cast<long long>(t - t0) < ns);
+}
+
+// ---------------------------------------------------------------------------------------------
 // fp32 check mode: direct convolution with true fp32 FMAs (no tensor cores, no TF32).
 //   in  : NHWC fp32 (B,H,W,Cin),  w : HWIO fp32 (kh,kw,Cin,Cout)  (the Keras kernel layout as is)
 //   out = act((conv + 0) * scale + bias (+ residual))

@@ -31,7 +31,8 @@ from . import _native as N
 from .dag_util import PartModel, construct_model, layer_macs
 from .fabric import (G_EPOCH, G_NWORKERS, G_PHASE, G_T0, G_T1, G_TIMING_REQ, KIND_DATA, KIND_PINNED, KIND_RESIDENT, KIND_STOP,
                      W_ELAPSED_US, W_TIMING_ACK, MAX_WORKERS, PHASE_CONFIGURE, PHASE_INIT,
-                     PHASE_QUIESCE, PHASE_RUN, PHASE_SHUTDOWN, FLAG_BASE_STEP, W_ACK_QUIESCE, W_ACK_READY, W_KILL, W_STATE,
+                     PHASE_QUIESCE, PHASE_RUN, PHASE_SHUTDOWN, FLAG_BASE_STEP, W_ACK_QUIESCE, W_ACK_READY, W_BUSY_N, W_BUSY_US,
+                     W_KILL, W_LAST_K, W_STATE,
                      ControlRing, CudaBackend, HealthTable, ResultRing, ShmRegion, StateEnum, poison_value)
 from .node import IMAGE_BYTES, OUT_ROW_BYTES, StageWorker, arena_slot_bytes
 
@@ -151,7 +152,8 @@ class DEFER:
     def __init__(self, computeNodes, mode: str = "bf16", max_batch: int = 128, heartbeat_timeout: float = 0.05,
                  max_inflight: Optional[int] = None, backend_factory=None, warm_batches: Sequence[int] = (),
                  silent_kill: bool = True, handoff: str = "auto", ingest_rails: str = "auto",
-                 input_format: str = "float32") -> None:
+                 input_format: str = "float32", straggler_factor: Optional[float] = 8.0, straggler_window: float = 0.5,
+                 straggler_quarantine: float = 10.0, task_timeout: Optional[float] = None) -> None:
         self.computeNodes = computeNodes
         self.dispatchIP = self.get_local_ip()
         self.chunk_size = 512 * 1000
@@ -181,6 +183,21 @@ class DEFER:
         if input_format not in ("float32", "uint8"):
             raise ValueError("input_format must be 'float32' or 'uint8'")
         self.input_format = input_format
+        # Straggler policy (the reference's `start_time` per in-flight task + `_task_watchdog`, src/dispatcher.py:190-194,
+        # 302-304): a stage that is ALIVE but whose busy time per micro-batch stays above `straggler_factor` x its own
+        # healthy baseline for `straggler_window` seconds is dropped like a dead one (the model is re-sliced over the
+        # others) and may re-join after `straggler_quarantine` seconds; None / 0 switches the policy off.
+        # `task_timeout`: an in-flight micro-batch older than this (seconds) is taken as evidence that some stage is
+        # stuck -- the slowest one by busy-time ratio, else the one with the largest backlog, is dropped.
+        self.straggler_factor = float(straggler_factor) if straggler_factor else 0.0
+        self.straggler_window = float(straggler_window)
+        self.straggler_quarantine = float(straggler_quarantine)
+        self.task_timeout = float(task_timeout) if task_timeout else 0.0
+        self._busy_base: Dict[int, float] = {}     # worker -> lowest busy moving average seen in this epoch (microseconds)
+        self._slow_since: Dict[int, float] = {}    # worker -> when it was first seen above the threshold
+        self._quarantine: Dict[int, float] = {}    # worker -> time before which it may not re-join
+        self._strikes: Dict[int, int] = {}         # worker -> times it was dropped as a straggler (quarantine doubles)
+        self._healthy_us_per_mac: Dict[int, float] = {}  # worker -> its healthy busy time per MAC, kept across epochs
         # -- runtime state
         self._shutdown_event = threading.Event()
         self.inflight_lock = threading.Lock()
@@ -190,7 +207,8 @@ class DEFER:
         self.workers: List[StageWorker] = []
         self.models_to_dispatch: List[PartModel] = []
         self.part_at: List[str] = []
-        self.stats = {"delivered": 0, "replayed": 0, "failovers": 0, "failover_ms": [], "dropped_stale": 0, "rejoins": 0}
+        self.stats = {"delivered": 0, "replayed": 0, "failovers": 0, "failover_ms": [], "dropped_stale": 0, "rejoins": 0,
+                      "stragglers": 0}
         self.latencies_ms: List[float] = []
         self._feed_lock = threading.Lock()
         self._collect_lock = threading.Lock()
@@ -310,6 +328,15 @@ class DEFER:
         self._k_feed = 0
         self.order = order
         self.part_at = part_at
+        # a new partition: new baselines -- except for workers that were dropped as stragglers before: they are held
+        # to what they did when healthy (scaled to their new share of the model), so one that comes back still slow is
+        # caught again at once instead of calibrating the watchdog on its slowness
+        self._busy_base, self._slow_since = {}, {}
+        if self._healthy_us_per_mac:
+            macs = [p.macs() for p in self._partition(self.model, part_at)]
+            for i, w in enumerate(order):
+                if w in self._healthy_us_per_mac:
+                    self._busy_base[w] = self._healthy_us_per_mac[w] * macs[i]
         h.g[G_PHASE] = PHASE_RUN
         self.stats.setdefault("reconfig_phases_ms", []).append(
             {"quiesce": round((t_quiesced - t_start) * 1e3, 2), "configure": round((time.perf_counter() - t_quiesced) * 1e3, 2)})
@@ -448,11 +475,28 @@ class DEFER:
             alive = set(self._get_available_workers())
             dead = [w for w in self.order if w not in alive]
             if not dead:
+                slow = self._find_straggler()
+                if slow is not None:
+                    w, why = slow
+                    self.stats["stragglers"] += 1
+                    self.stats.setdefault("straggler_events", []).append({"worker": w, **why})
+                    self._strikes[w] = self._strikes.get(w, 0) + 1
+                    self._quarantine[w] = time.monotonic() + self.straggler_quarantine * 2 ** (self._strikes[w] - 1)
+                    if w in self._busy_base and w not in self._healthy_us_per_mac:
+                        stage_macs = self._partition(self.model, self.part_at)[self.order.index(w)].macs()
+                        self._healthy_us_per_mac[w] = self._busy_base[w] / max(1, stage_macs)
+                    try:
+                        self._failover([w])
+                    except Exception as e:  # noqa: BLE001
+                        self.error = f"straggler fail-over failed: {type(e).__name__}: {e}; worker {w}: {why}; {self.debug_state()}"
+                        self._shutdown_event.set()
+                    continue
                 # elastic re-join: a worker that LOST its stage and is healthy again gets one back.
                 # Spare workers (more computeNodes than partitions) never held one: they stay idle -- the caller's
                 # `partition_layers` define the pipeline -- until a fail-over needs them (_failover).
+                now = time.monotonic()
                 joiners = sorted(w for w in alive if w in self._dropped and w not in self.order
-                                 and not int(self.health.w[w, W_KILL]))
+                                 and not int(self.health.w[w, W_KILL]) and self._quarantine.get(w, 0.0) <= now)
                 if joiners:
                     try:
                         self._rejoin(joiners)
@@ -469,6 +513,51 @@ class DEFER:
             except Exception as e:  # noqa: BLE001
                 self.error = f"failover failed: {type(e).__name__}: {e}; dead workers: {causes}; {self.debug_state()}"
                 self._shutdown_event.set()
+
+    def _find_straggler(self):
+        """(worker, evidence) of a stage that is alive but slow, or None.  Two signals, both self-calibrating:
+        the stage's busy time per micro-batch (moving average its worker publishes, CUDA events around the stage's
+        work) against the LOWEST value that same stage showed in this epoch, and the age of the oldest in-flight
+        micro-batch (`inflight_tasks[seq]["start_time"]`) against `task_timeout`."""
+        if len(self.order) < 2:
+            return None  # nobody to hand the layers to
+        h, now = self.health, time.monotonic()
+        ratios = {}
+        # (under torchrun the dispatcher-local first stage cannot be handed to another rank: it is never a candidate)
+        candidates = self.order[1:] if self.session.get("ipc", False) else self.order
+        for w in candidates:
+            n, busy = int(h.w[w, W_BUSY_N]), float(h.w[w, W_BUSY_US])
+            if n < 8 or busy <= 0:
+                continue
+            base = min(self._busy_base.get(w, busy), busy)
+            self._busy_base[w] = base
+            ratios[w] = busy / max(base, 1.0)
+        if self.straggler_factor:
+            for w, r in ratios.items():
+                if r >= self.straggler_factor:
+                    t0 = self._slow_since.setdefault(w, now)
+                    if now - t0 >= self.straggler_window:
+                        return w, {"reason": "busy time", "busy_us": int(h.w[w, W_BUSY_US]), "baseline_us": int(self._busy_base[w]),
+                                   "ratio": round(r, 2), "held_s": round(now - t0, 3)}
+                else:
+                    self._slow_since.pop(w, None)
+        if self.task_timeout:
+            with self.inflight_lock:
+                oldest = min((t["start_time"] for t in self.inflight_tasks.values()), default=None)
+            if oldest is not None and time.time() - oldest > self.task_timeout:
+                if ratios and max(ratios.values()) >= 1.5:
+                    w = max(ratios, key=ratios.get)
+                    why = {"reason": "task timeout, slowest stage", "ratio": round(ratios[w], 2)}
+                else:
+                    # the stage that sits on the most unprocessed micro-batches of its predecessor
+                    lag = {w: int(h.w[p, W_LAST_K]) - int(h.w[w, W_LAST_K]) for p, w in zip(self.order[:-1], self.order[1:])}
+                    if not self.session.get("ipc", False):
+                        lag[self.order[0]] = self._k_feed - 1 - int(h.w[self.order[0], W_LAST_K])
+                    w = max(lag, key=lag.get)
+                    why = {"reason": "task timeout, largest backlog", "backlog": lag[w]}
+                why["oldest_task_age_s"] = round(time.time() - oldest, 3)
+                return w, why
+        return None
 
     def _failover(self, dead: List[int]) -> None:
         t0 = time.perf_counter()

@@ -102,17 +102,18 @@ class StageExecutor:
         for op, t in zip(self.program.ops, ms):
             # algorithmic work = the Keras layer's own MAC count (not the padded / space-to-depth form it runs in)
             macs = 0
-            if op.kind == N.OP_CONV:
+            if op.kind in (N.OP_CONV, N.OP_CONV_CHAIN):
                 macs = batch * sum(layer_macs(self.model, self.model.get_layer(n)) for n in op.layers
                                    if n in self.model._by_name)
             out.append({"layers": op.layers, "kind": op.kind, "ms": float(t), "macs": int(macs),
                         "shape": [op.H, op.W, op.Cin, op.Cout, op.kh, op.stride]})
         return out
 
-    def time_kind(self, slot: int, batch: int, kind: int, stream: int = 0, reps: int = 20) -> Tuple[float, int]:
-        """(device ms per step, launches) of all ops of one kind, run as their own CUDA graph (PDL overlap kept)."""
+    def time_kind(self, slot: int, batch: int, kinds: Sequence[int], stream: int = 0, reps: int = 20) -> Tuple[float, int]:
+        """(device ms per step, launches) of all ops of the given kinds, run as their own CUDA graph (PDL overlap kept)."""
         ms, n = C.c_float(0), C.c_int(0)
-        N.check(self.lib.adapt_stage_time_kind(self.handle, slot, batch, stream, kind, reps, C.byref(ms), C.byref(n)))
+        mask = sum(1 << int(k) for k in kinds)
+        N.check(self.lib.adapt_stage_time_kind(self.handle, slot, batch, stream, mask, reps, C.byref(ms), C.byref(n)))
         return float(ms.value), int(n.value)
 
     def read_logits(self, batch: int, stream: int = 0) -> np.ndarray:

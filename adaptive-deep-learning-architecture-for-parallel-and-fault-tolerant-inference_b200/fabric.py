@@ -147,7 +147,9 @@ _TABLE_BYTES = 8192    # JSON partition table
 G_EPOCH, G_PHASE, G_NWORKERS, G_TABLE_LEN, G_T0, G_T1, G_TIMING_REQ = 0, 1, 2, 3, 4, 5, 6
 # per-worker words
 (W_HEARTBEAT, W_STATE, W_KILL, W_ACK_QUIESCE, W_ACK_READY, W_LAST_K, W_PID, W_DEVICE, W_ERRORS, W_ELAPSED_US,
- W_TIMING_ACK) = range(11)
+ W_TIMING_ACK, W_BUSY_US, W_BUSY_N) = range(13)
+# W_BUSY_US: moving average of the device time this worker's stage spends per micro-batch (microseconds, this epoch);
+# W_BUSY_N: micro-batches folded into it.  Read by the dispatcher's straggler watchdog.
 
 
 class HealthTable:
@@ -314,6 +316,15 @@ class CudaBackend:
 
     def event_sync(self, event: int) -> None:
         N.check(self.lib.adapt_event_sync(self.device, event))
+
+    def event_done(self, event: int) -> bool:
+        v = C.c_int(0)
+        N.check(self.lib.adapt_event_query(self.device, event, C.byref(v)))
+        return bool(v.value)
+
+    def spin(self, stream: int, microseconds: int) -> None:
+        """Fault injection: keep `stream` busy for `microseconds` (a stage that is alive but slow)."""
+        N.check(self.lib.adapt_debug_spin(self.device, stream, int(microseconds)))
 
     def event_elapsed_ms(self, start: int, stop: int) -> float:
         v = C.c_float(0)

@@ -28,7 +28,7 @@ import numpy as np
 from . import _native as N
 from .dag_util import construct_model
 from .fabric import (G_EPOCH, G_PHASE, G_T0, G_T1, G_TIMING_REQ, KIND_DATA, KIND_PINNED, KIND_RESIDENT, KIND_STOP, PHASE_CONFIGURE, PHASE_QUIESCE, PHASE_RUN,
-                     PHASE_SHUTDOWN, W_ACK_QUIESCE, W_ACK_READY, W_DEVICE, W_ERRORS, W_ELAPSED_US, W_HEARTBEAT, W_KILL, W_LAST_K, W_PID,
+                     PHASE_SHUTDOWN, W_ACK_QUIESCE, W_ACK_READY, W_BUSY_N, W_BUSY_US, W_DEVICE, W_ERRORS, W_ELAPSED_US, W_HEARTBEAT, W_KILL, W_LAST_K, W_PID,
                      W_TIMING_ACK,
                      ControlRing, CudaBackend, HealthTable, ResultRing, ShmRegion, StateEnum, poison_value)
 
@@ -123,9 +123,21 @@ class StageWorker:
         # stage of a multi-stage pipeline run micro-batch k of every epoch on the OTHER input slot, i.e. on the
         # tensor of micro-batch k-1 -- the hand-off bug a value check of the delivered results has to catch.
         self._fault_stale_k = -1
+        # "slow_worker:<worker>:<microseconds>:<from k>": from micro-batch k on, that worker's stream is kept busy for the
+        # given time on top of every micro-batch (a stage that is alive but slow: what the straggler watchdog is for)
+        self._fault_slow = None
         fault = os.environ.get("ADAPT_FAULT_INJECT", "")
         if fault.startswith("stale_slot:"):
             self._fault_stale_k = int(fault.split(":")[1])
+        elif fault.startswith("slow_worker:"):
+            st, us, k0 = (int(v) for v in fault.split(":")[1:4])
+            self._fault_slow = (st, us, k0)
+        # per-micro-batch busy time of this stage (device time between two events around the stage's work), folded
+        # into a moving average in the health table: the straggler watchdog's input (reference src/dispatcher.py:193)
+        self._busy_events: List[tuple] = []
+        self._busy_pending: List[tuple] = []
+        self._busy_ewma = 0.0
+        self._busy_n = 0
         if hasattr(self.backend, "abort_check"):  # synchronous test backends must be able to give up a wait
             self.backend.abort_check = lambda: (self.health.phase != PHASE_RUN or bool(self.health.w[self.wid, W_KILL])
                                                 or self._stop.is_set())
@@ -247,6 +259,7 @@ class StageWorker:
             if table.get("warm_batches"):
                 self._warm(table["warm_batches"])
         self._setup_rails(order, table)
+        self._busy_reset()
         self.epoch = epoch
         self.health.w[self.wid, W_ACK_READY] = epoch
 
@@ -364,7 +377,15 @@ class StageWorker:
         timed = self._timing_events is not None
         if timed and k == int(self.health.g[G_T0]):
             b.event_record(self._timing_events[0], self.stream)
+        ev = self._busy_begin()
+        t_host = time.perf_counter()
         ex.enqueue(s ^ 1 if (k == self._fault_stale_k and last and not first) else s, batch, self.stream)
+        if self._fault_slow is not None and self._fault_slow[0] == self.wid and k >= self._fault_slow[2]:
+            if hasattr(b, "spin"):
+                b.spin(self.stream, self._fault_slow[1])
+            else:
+                time.sleep(self._fault_slow[1] * 1e-6)
+        self._busy_end(ev, t_host)
         self.launches += ex.num_launches
         if first:  # (also for resident micro-batches, so that a later copied one finds the flag current)
             b.write_flag(self.stream, self.flag(self.wid, F_IN_CONSUMED + s), v_done)
@@ -396,6 +417,49 @@ class StageWorker:
             b.event_record(self._timing_events[1], self.stream)
             self._timing_armed = True
         self.health.w[self.wid, W_LAST_K] = k
+
+    # ------------------------------------------------------------------ busy time (straggler watchdog input)
+    def _busy_begin(self):
+        b = self.backend
+        if not hasattr(b, "event_done"):
+            return None
+        self._busy_poll()
+        if self._busy_events:
+            pair = self._busy_events.pop()
+        elif len(self._busy_pending) < 16:
+            pair = (b.event_create(), b.event_create())
+        else:
+            return None  # (every pair is still in flight: skip this sample)
+        b.event_record(pair[0], self.stream)
+        return pair
+
+    def _busy_end(self, pair, t_host: float) -> None:
+        if pair is None:
+            if not hasattr(self.backend, "event_done"):  # synchronous test backend: the call itself is the work
+                self._busy_fold((time.perf_counter() - t_host) * 1e6)
+            return
+        self.backend.event_record(pair[1], self.stream)
+        self._busy_pending.append(pair)
+
+    def _busy_poll(self) -> None:
+        b = self.backend
+        while self._busy_pending and b.event_done(self._busy_pending[0][1]):
+            pair = self._busy_pending.pop(0)
+            self._busy_fold(b.event_elapsed_ms(pair[0], pair[1]) * 1e3)
+            self._busy_events.append(pair)
+
+    def _busy_fold(self, us: float) -> None:
+        self._busy_n += 1
+        self._busy_ewma = us if self._busy_n == 1 else 0.75 * self._busy_ewma + 0.25 * us
+        self.health.w[self.wid, W_BUSY_US] = int(self._busy_ewma)
+        self.health.w[self.wid, W_BUSY_N] = self._busy_n
+
+    def _busy_reset(self) -> None:
+        self._busy_events += self._busy_pending  # (streams are drained when this runs)
+        self._busy_pending = []
+        self._busy_ewma, self._busy_n = 0.0, 0
+        self.health.w[self.wid, W_BUSY_US] = 0
+        self.health.w[self.wid, W_BUSY_N] = 0
 
     def _report_timing(self) -> None:
         """Device time this stage spent on the micro-batches [G_T0, G_T1) (CUDA events on its stream)."""
@@ -481,6 +545,8 @@ class StageWorker:
                 if rec is None:
                     self.state.state = StateEnum.IDLE
                     self._report_timing()
+                    if self._busy_pending:
+                        self._busy_poll()
                     continue
                 if (rec[0] & 0xFF) == KIND_STOP:
                     if self.next_wid >= 0:

@@ -149,13 +149,13 @@ int adapt_stage_read_tensor(adapt_stage_t* stage, int tensor, void* host_dst, si
 int adapt_stage_profile(adapt_stage_t* stage, int slot, int batch, void* stream, int reps, float* ms_per_op,
                         int n_ops);
 
-/* Measurement aid: the ops of ONE kind (ADAPT_OP_*) of (`slot`, `batch`) captured into their own CUDA graph -- same
+/* Measurement aid: the ops whose kind is in `kind_mask` (bit ADAPT_OP_* set) of (`slot`, `batch`) captured into their own CUDA graph -- same
  * launches and launch attributes as inside the stage's graph, so consecutive convolutions keep their programmatic
  * dependent launch overlap -- and timed over `reps` graph launches with one pair of CUDA events on `stream`.
  * *ms_per_rep = device time of that class per step; *n_launches = launches of that kind.  Overwrites the stage's
  * internal activations with meaningless values (inputs of the skipped ops are stale); synchronises.
  * No reference counterpart (bench.py's roofline accounting). */
-int adapt_stage_time_kind(adapt_stage_t* stage, int slot, int batch, void* stream, int kind, int reps,
+int adapt_stage_time_kind(adapt_stage_t* stage, int slot, int batch, void* stream, int kind_mask, int reps,
                           float* ms_per_rep, int* n_launches);
 
 /* Number of kernel launches one enqueue() of `batch` images performs (for bench accounting). */
@@ -259,7 +259,13 @@ int adapt_event_create(int device, void** event_out);
 int adapt_event_record(int device, void* event, void* stream);
 int adapt_event_sync(int device, void* event);
 int adapt_event_elapsed_ms(int device, void* start, void* stop, float* ms_out);
+/* Non-blocking: *done_out = 1 when `event` has completed, 0 otherwise (per-micro-batch busy times of a stage,
+ * folded into the health table for the straggler watchdog -- the reference's `start_time` idea, src/dispatcher.py:193). */
+int adapt_event_query(int device, void* event, int* done_out);
 int adapt_event_destroy(int device, void* event);
+/* Fault injection (tests): occupy `stream` for `microseconds` without touching memory -- a stage that is alive but
+ * slow (clock-capped GPU, noisy neighbour).  No reference counterpart. */
+int adapt_debug_spin(int device, void* stream, int microseconds);
 
 #ifdef __cplusplus
 }

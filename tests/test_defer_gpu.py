@@ -209,6 +209,26 @@ def test_elastic_rejoin_after_failover_gpu(pkg, model50):
     _check(model50, [["conv2_block3_out", "conv4_block1_out"]], inputs, outs, oracle_every=12)  # (re-slices cut at block outputs too)
 
 
+def test_straggler_stage_is_dropped_gpu(pkg, model50, monkeypatch):
+    """A stage that is alive (its heartbeat keeps coming) but slow: from micro-batch 12 on, worker 1's stream is kept
+    busy for 40 ms on top of every micro-batch (a spin kernel, ADAPT_FAULT_INJECT).  The busy-time watchdog (CUDA
+    events around the stage's work -> moving average in the health table) drops it, the model is re-sliced over the
+    other two, and every micro-batch is delivered exactly once, in order, with ITS values."""
+    from adapt_b200.dispatcher import DEFER
+
+    monkeypatch.setenv("ADAPT_FAULT_INJECT", "slow_worker:1:40000:12")
+    devs = [f"cuda:{i % max(1, _ngpu())}" for i in range(3)]
+    inputs = [distinct_images(2, 1000, i) for i in range(48)]
+    defer = DEFER(devs, max_batch=2, heartbeat_timeout=0.25, straggler_factor=6.0, straggler_window=0.15)
+    outs, stats, _ = _run(defer, model50, ["conv2_block3_out", "conv4_block1_out"], inputs, timeout=60)
+    monkeypatch.delenv("ADAPT_FAULT_INJECT")
+    assert stats["stragglers"] == 1 and stats["failovers"] == 1 and stats["delivered"] == len(inputs), stats
+    ev = stats["straggler_events"][0]
+    assert ev["worker"] == 1 and ev["reason"] == "busy time" and ev["ratio"] >= 6.0, ev
+    assert len(defer.part_at) == 1 and 1 not in defer.order
+    _check(model50, [["conv2_block3_out", "conv4_block1_out"], defer.part_at], inputs, outs, oracle_every=12)
+
+
 def test_uint8_inputs_through_defer(pkg, model50):
     """input_format="uint8": pinned and pageable raw RGB batches through a 2-stage pipeline, values against the
     oracle on host-preprocessed images."""

@@ -356,6 +356,80 @@ def test_flag_values_of_different_epochs_never_alias(pkg, model50):
         np.testing.assert_allclose(y, o.predict(x)[0], rtol=1e-5, atol=1e-7)
 
 
+def test_straggler_is_dropped_and_may_rejoin(pkg, model50):
+    """SURVEY 8(f) rank 1, the `start_time` idea (reference src/dispatcher.py:190-194, 302-304): a stage that keeps
+    beating but turns 20x slower is not "dead" -- the busy-time watchdog drops it, the model is re-sliced over the
+    others, every micro-batch is still delivered once and in order; after its quarantine (and once it is fast again)
+    the worker gets a stage back."""
+    import threading
+
+    from adapt_b200.dispatcher import DEFER
+
+    o = oracle_for(model50)
+    inputs = [KO.synthetic_images(1, seed=390 + i, kind="normal") for i in range(26)]
+    d = DEFER([0, 1, 2], mode="fp32", max_batch=1, backend_factory=lambda dev: HostBackend(dev, delay=0.005),
+              heartbeat_timeout=5.0, straggler_factor=4.0, straggler_window=0.3, straggler_quarantine=4.0)
+    in_q, out_q = queue.Queue(4), queue.Queue()
+    t = threading.Thread(target=d.run_defer, args=(model50, ["conv2_block3_out", "conv4_block1_out"], in_q, out_q), daemon=True)
+    t.start()
+    d.wait_ready(60)
+    outs = []
+
+    def pump(items):
+        for x in items:
+            in_q.put(x)
+            outs.append(out_q.get(timeout=60))
+
+    pump(inputs[:12])                                   # healthy: baselines settle (>= 8 samples per stage)
+    assert d.stats["stragglers"] == 0 and d.order == [0, 1, 2]
+    slow = next(w for w in d.workers if w.wid == 1)
+    base_delay = slow.executor.delay
+    slow.executor.delay = 1.0                           # alive, heart beating, 20x+ slower
+    pump(inputs[12:18])
+    assert d.stats["stragglers"] == 1 and d.stats["failovers"] == 1 and d.order == [0, 2], (d.stats, d.order)
+    ev = d.stats["straggler_events"][0]
+    assert ev["worker"] == 1 and ev["reason"] == "busy time" and ev["ratio"] >= 4.0
+    slow.executor.delay = base_delay                    # recovered
+    t0 = time.time()
+    while d.stats["rejoins"] == 0 and time.time() - t0 < 20:
+        time.sleep(0.02)
+    assert d.stats["rejoins"] == 1 and d.order == [0, 1, 2]
+    pump(inputs[18:])
+    assert d.error is None and out_q.empty() and d.stats["stragglers"] == 1
+    d.shutdown()
+    t.join(30)
+    for x, y in zip(inputs, outs):
+        np.testing.assert_allclose(y, o.predict(x)[0], rtol=1e-5, atol=1e-7)
+
+
+def test_task_timeout_names_the_stage_that_sits_on_the_backlog(pkg, model50):
+    """`task_timeout`: an in-flight micro-batch older than the limit (its `start_time` in the in-flight registry) makes
+    the watchdog drop a stage even when no busy-time evidence exists yet (here: the very first micro-batches)."""
+    import threading
+
+    from adapt_b200.dispatcher import DEFER
+
+    o = oracle_for(model50)
+    inputs = [KO.synthetic_images(1, seed=395 + i, kind="normal") for i in range(5)]
+    d = DEFER([0, 1], mode="fp32", max_batch=1, backend_factory=HostBackend, heartbeat_timeout=30.0, straggler_factor=None,
+              task_timeout=1.0)
+    in_q, out_q = queue.Queue(8), queue.Queue()
+    t = threading.Thread(target=d.run_defer, args=(model50, ["conv3_block4_out"], in_q, out_q), daemon=True)
+    t.start()
+    d.wait_ready(60)
+    stuck = next(w for w in d.workers if w.wid == 1)
+    stuck.executor.delay = 4.0                          # the second stage sits on its first micro-batch
+    for x in inputs:
+        in_q.put(x)
+    outs = [out_q.get(timeout=60) for _ in inputs]
+    assert d.stats["stragglers"] == 1 and d.order == [0]
+    assert d.stats["straggler_events"][0]["reason"].startswith("task timeout")
+    d.shutdown()
+    t.join(30)
+    for x, y in zip(inputs, outs):
+        np.testing.assert_allclose(y, o.predict(x)[0], rtol=1e-5, atol=1e-7)
+
+
 def test_cascading_kills(pkg, model50):
     """Two stages die one after the other (3 -> 2 -> 1 stages): each death is detected and re-sliced on its own,
     the stream stays FIFO and exactly-once, and the last survivor runs the whole model."""
