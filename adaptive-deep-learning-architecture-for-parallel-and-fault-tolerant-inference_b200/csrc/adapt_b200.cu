@@ -267,7 +267,7 @@ struct ConvLaunch {
 
 // Launch record of the chained `_2_conv` (3x3) -> `_3_conv` (1x1 + shortcut + ReLU) kernel (conv_chain_sm100.cuh).
 struct ChainLaunch {
-    CUtensorMap tmap_a, tmap_w2, tmap_w3, tmap_res, tmap_out;
+    CUtensorMap tmap_a, tmap_w2, tmap_w3, tmap_res;
     adapt::ConvChainParams p;
     int C = 0;
     int smem = 0;
@@ -797,7 +797,7 @@ int build_chain_launch(ChainLaunch* L, int batch, int H, int W, int C, const voi
     p.ring = env_int("ADAPT_CHAIN_RING", 2);
     if (p.ring < 2) p.ring = 2;
     if (p.ring > adapt::kChainMaxRing) p.ring = adapt::kChainMaxRing;
-    p.l2_prefetch = env_int("ADAPT_CHAIN_L2PF", 1);
+    p.l2_prefetch = env_int("ADAPT_CHAIN_L2PF", 0);
     int stages = env_int("ADAPT_CHAIN_STAGES", adapt::kChainMaxStages);
     if (stages > adapt::kChainMaxStages) stages = adapt::kChainMaxStages;
     auto bytes = [&](int st) {
@@ -823,21 +823,7 @@ int build_chain_launch(ChainLaunch* L, int batch, int H, int W, int C, const voi
     rc = encode_tiled_2d_bf16(&L->tmap_w3, w3, (uint64_t)C, (uint64_t)4 * C, adapt::kBlockK,
                               (uint32_t)(pair ? adapt::kChainBN2 / 2 : adapt::kChainBN2));
     if (rc) return rc;
-    rc = encode_padded_flat_slab_bf16(&L->tmap_res, residual, 4 * C, W, H, batch);
-    if (rc) return rc;
-    // output as (channel, column, image row over all images): 64-channel x 32-column x 1-row boxes, clipped at the edges
-    DriverApi* d;
-    rc = get_driver(&d);
-    if (rc) return rc;
-    cuuint64_t dims[3] = {(cuuint64_t)4 * C, (cuuint64_t)W, (cuuint64_t)batch * H};
-    cuuint64_t strides[2] = {(cuuint64_t)4 * C * 2, (cuuint64_t)W * 4 * C * 2};
-    cuuint32_t box[3] = {(cuuint32_t)adapt::kEpiCols, 32, 1};
-    cuuint32_t estr[3] = {1, 1, 1};
-    CUresult r = d->encodeTiled(&L->tmap_out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, out, dims, strides, box, estr,
-                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) return fail(ADAPT_ECUDA, "conv chain: output tensor map refused (%d)", (int)r);
-    return ADAPT_OK;
+    return encode_padded_flat_slab_bf16(&L->tmap_res, residual, 4 * C, W, H, batch);
 }
 
 template <int C, bool PAIR>
@@ -863,8 +849,7 @@ cudaError_t launch_chain_ex(const ChainLaunch& L, cudaStream_t s) {
     }
     cfg.attrs = attr;
     cfg.numAttrs = n;
-    return cudaLaunchKernelEx(&cfg, adapt::conv_chain_kernel<C, PAIR>, L.tmap_a, L.tmap_w2, L.tmap_w3, L.tmap_res, L.tmap_out,
-                              L.p);
+    return cudaLaunchKernelEx(&cfg, adapt::conv_chain_kernel<C, PAIR>, L.tmap_a, L.tmap_w2, L.tmap_w3, L.tmap_res, L.p);
 }
 
 int run_chain_launch(const ChainLaunch& L, cudaStream_t s) {

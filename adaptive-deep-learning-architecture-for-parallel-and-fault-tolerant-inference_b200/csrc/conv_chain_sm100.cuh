@@ -14,10 +14,10 @@
 // of W + 2 positions, the last two of each row discarded), one im2col load of 136 positions per (filter row, channel
 // block) feeds the three horizontal taps through shifted descriptors.  Phase 2 therefore also runs on padded-flat
 // positions; its residual tile is fetched with an im2col-mode TMA load that walks the same positions (zero-filled
-// where a position is not a pixel) and its output leaves through tiled TMA stores on a (channel, column, image row)
-// view of the output: a warp's 32 consecutive positions touch up to three image rows, so the same slab is stored up to
-// three times with the column coordinate shifted by whole rows -- positions of other rows and the two overhang
-// positions fall outside the tensor and are clipped by the store.
+// where a position is not a pixel) and its output leaves through a coalesced st.global write-out whose position ->
+// pixel offsets are worked out once per unit and warp, not per chunk.  (TMA stores were tried for this and fault on
+// B200 -- "illegal instruction" -- both as tiled stores with a negative start column, the way to express a slab that
+// straddles image rows, and as im2col-mode stores over the padded-flat walk.)
 //
 //   warp 0      TMA producer: per unit, the phase-1 stages (A row segments; the three B tiles of a filter row unless
 //               the 3x3's weights are resident), then one stage per phase-2 n-tile (`_3_conv` weights), all through
@@ -79,7 +79,7 @@ template <int C, bool PAIR>
 __global__ void __launch_bounds__(kChainThreads, 1)
 conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w2,
                   const __grid_constant__ CUtensorMap tmap_w3, const __grid_constant__ CUtensorMap tmap_res,
-                  const __grid_constant__ CUtensorMap tmap_out, const ConvChainParams p) {
+                  const ConvChainParams p) {
     static_assert(C == 64 || C == 128, "chain kernel: C = 64 (single CTA) or 128 (CTA pair)");
     static_assert(PAIR == (C == 128), "C = 128 runs on CTA pairs, C = 64 on single CTAs");
     constexpr int CL = PAIR ? 2 : 1;
@@ -142,9 +142,6 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         ptx::prefetch_tmap(&tmap_w2);
         ptx::prefetch_tmap(&tmap_w3);
         ptx::prefetch_tmap(&tmap_res);
-#ifndef DBG3
-        ptx::prefetch_tmap(&tmap_out);
-#endif
     }
     if (warp_idx == 1) {
         if (PAIR) {
@@ -397,10 +394,25 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         for (int ti = 0; tile_at(ti, m_blk, m_valid); ++ti) {
             const int m_row0 = m_blk * kBlockM + lane_group * 32;
             const bool slab_ok = m_valid && m_row0 < p.M;
-            const int rest_w = m_row0 / p.row_pitch;          // image row (over all images) of this warp's first position
-            const int q_w = m_row0 - rest_w * p.row_pitch;    // ... and its column in the padded-flat row
-            const int n_rows_w = (q_w + 31) / p.row_pitch + 1;  // image rows the 32 positions touch (1..3)
-            if ((p.l2_prefetch & 1) && lane == 0) {
+            // write-out offsets, once per unit: lane (8 r + ch) moves 16-byte piece ch of slab rows 4 i + r (i = 0..7);
+            // out_off[i] = element offset of that row's pixel in the output, or -1 for a position that is not a pixel
+            int out_off[8];
+            {
+                int m = m_row0 + (lane >> 3);
+                int rest = m / p.row_pitch;
+                int q = m - rest * p.row_pitch;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    out_off[i] = (m < p.M && q < p.W) ? (rest * p.W + q) * p.N2 + (lane & 7) * 8 : -1;
+                    m += 4;
+                    q += 4;
+                    if (q >= p.row_pitch) {
+                        q -= p.row_pitch;
+                        ++rest;
+                    }
+                }
+            }
+            if (p.l2_prefetch && lane == 0) {
                 int mb = 0;
                 bool mv = true;
                 if (tile_at(ti + 1, mb, mv) && mv && mb * kBlockM + lane_group * 32 < p.M) {
@@ -475,11 +487,7 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                     const uint32_t slab = slabs_sa + slot * kEpiSlabBytes;
                     const uint32_t this_slot = slot;
                     if (++slot == ring) slot = 0;
-                    uint8_t* slab_ptr = my_slabs + this_slot * kEpiSlabBytes;
                     if (!slab_ok) {
-                        // nothing is stored from this chunk: the newest store group may still be reading the slab the
-                        // prefetch is about to refill
-                        if (lane == 0) ptx::tma_store_wait_read<0>();
                         __syncwarp();
                         issue_residual();
                         continue;
@@ -517,19 +525,17 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                         ov.w = ptx::pack_bf16x2_relu(y[6], y[7]);
                         ptx::sts128(slab + sw, ov);
                     }
-                    ptx::fence_proxy_async_smem();  // slab writes -> visible to the TMA stores
                     __syncwarp();
-                    if (lane == 0) {
-                        // slab row r is position (rest_w, q_w + r): one store per image row the slab touches, the column
-                        // coordinate shifted back by whole padded-flat rows; whatever falls outside [0, W) is clipped
-                        for (int s = 0; s < ((p.l2_prefetch & 4) ? 0 : ((p.l2_prefetch & 2) ? 1 : n_rows_w)); ++s)
-                            ptx::tma_store_3d(&tmap_out, slab_ptr, col0, q_w - s * p.row_pitch, rest_w + s);
-#ifndef DBG2
-                        ptx::tma_store_commit();
-                        // every store group but the one just issued has read its slab: the previous chunk's slab is
-                        // free for the residual `ring - 1` chunks ahead
-                        ptx::tma_store_wait_read<1>();
-#endif
+                    {
+                        // coalesced write-out: 8 lanes cover one 128-byte row segment, 4 rows per instruction
+                        const int ch = lane & 7;
+                        __nv_bfloat16* gcol = p.out + col0;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int row = i * 4 + (lane >> 3);
+                            const uint4 val = ptx::lds128(slab + row * 128 + ((ch ^ (row & 7)) << 4));
+                            if (out_off[i] >= 0) *reinterpret_cast<uint4*>(gcol + out_off[i]) = val;
+                        }
                     }
                     __syncwarp();
                     issue_residual();
@@ -539,9 +545,6 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     }
 
     // ===================== teardown =====================
-#ifndef DBG1
-    if (warp_idx >= 2 && warp_idx < 2 + kEpiWarps && lane == 0) ptx::tma_store_wait<0>();  // bulk stores landed before exit
-#endif
     ptx::tc_fence_before();
     __syncthreads();
     if (CL > 1) ptx::cluster_sync();

@@ -249,13 +249,6 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* s
                  "r"(smem_u32(smem_src)), "r"(x), "r"(y)
                  : "memory");
 }
-// tiled 3-D store (the chain kernel's padded-flat write-out: channel, column, image row; out-of-range parts are clipped)
-__device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, const void* smem_src, int c0, int c1, int c2) {
-    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
-                     reinterpret_cast<uint64_t>(m)),
-                 "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
-                 : "memory");
-}
 // tiled 5-D store (the stem-by-phase epilogue: channel, column phase, unit column, row, image)
 __device__ __forceinline__ void tma_store_5d(const CUtensorMap* m, const void* smem_src, int c0, int c1, int c2, int c3,
                                              int c4) {

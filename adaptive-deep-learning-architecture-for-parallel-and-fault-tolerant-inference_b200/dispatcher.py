@@ -29,7 +29,7 @@ import numpy as np
 
 from . import _native as N
 from .dag_util import PartModel, construct_model, layer_macs
-from .fabric import (G_EPOCH, G_NWORKERS, G_PHASE, G_T0, G_T1, G_TIMING_REQ, KIND_DATA, KIND_PINNED, KIND_RESIDENT, KIND_STOP,
+from .fabric import (G_EPOCH, G_NWORKERS, G_PHASE, G_T0, G_T1, G_TIMING_REQ, KIND_DATA, KIND_FED, KIND_PINNED, KIND_RESIDENT, KIND_STOP,
                      W_ELAPSED_US, W_TIMING_ACK, MAX_WORKERS, PHASE_CONFIGURE, PHASE_INIT,
                      PHASE_QUIESCE, PHASE_RUN, PHASE_SHUTDOWN, FLAG_BASE_STEP, W_ACK_QUIESCE, W_ACK_READY, W_BUSY_N, W_BUSY_US,
                      W_KILL, W_LAST_K, W_STATE,
@@ -416,7 +416,17 @@ class DEFER:
         k = self._k_feed
         self._k_feed += 1
         kind = KIND_DATA | (KIND_PINNED if pinned else 0) | (KIND_RESIDENT if isinstance(arr, ResidentBatch) else 0)
-        if not self.rings[self.order[0]].push((kind, self.health.epoch, k, seq, batch, addr)):
+        first = self.order[0]
+        if self.session.get("ipc", False) and not any(wk.wid == first for wk in self.workers):
+            # One process per GPU and the first stage now lives in ANOTHER process (the dispatcher-local stage was lost):
+            # its worker cannot read this process's host memory, so the dispatcher copies the input into that stage's
+            # slot itself, through the local worker object's copy stream and its CUDA-IPC mapping of the peer's arena.
+            if isinstance(arr, ResidentBatch):
+                raise RuntimeError("device-resident inputs live on the dispatcher-local stage, which is gone")
+            self.workers[0].feed_remote_first_stage(first, self._flag_base, k, batch, addr, pinned)
+            kind |= KIND_FED
+            addr = 0
+        if not self.rings[first].push((kind, self.health.epoch, k, seq, batch, addr)):
             raise RuntimeError("first stage does not drain its control ring")
 
     def _result_server(self, output: queue.Queue):
@@ -523,9 +533,7 @@ class DEFER:
             return None  # nobody to hand the layers to
         h, now = self.health, time.monotonic()
         ratios = {}
-        # (under torchrun the dispatcher-local first stage cannot be handed to another rank: it is never a candidate)
-        candidates = self.order[1:] if self.session.get("ipc", False) else self.order
-        for w in candidates:
+        for w in self.order:
             n, busy = int(h.w[w, W_BUSY_N]), float(h.w[w, W_BUSY_US])
             if n < 8 or busy <= 0:
                 continue
@@ -551,8 +559,7 @@ class DEFER:
                 else:
                     # the stage that sits on the most unprocessed micro-batches of its predecessor
                     lag = {w: int(h.w[p, W_LAST_K]) - int(h.w[w, W_LAST_K]) for p, w in zip(self.order[:-1], self.order[1:])}
-                    if not self.session.get("ipc", False):
-                        lag[self.order[0]] = self._k_feed - 1 - int(h.w[self.order[0], W_LAST_K])
+                    lag[self.order[0]] = self._k_feed - 1 - int(h.w[self.order[0], W_LAST_K])
                     w = max(lag, key=lag.get)
                     why = {"reason": "task timeout, largest backlog", "backlog": lag[w]}
                 why["oldest_task_age_s"] = round(time.time() - oldest, 3)
@@ -573,8 +580,8 @@ class DEFER:
             survivors = sorted(survivors + spares[:len(self.order) - len(survivors)])
             if not survivors:
                 raise RuntimeError("no surviving stage")
-            if self.order[0] in dead and self.session.get("ipc", False):
-                raise RuntimeError("the dispatcher-local first stage died; inputs cannot be re-routed across processes")
+            if self.order[0] in dead and self.session.get("ipc", False) and not self.workers:
+                raise RuntimeError("the dispatcher-local first stage died and no local worker object is left to feed through")
             if len(survivors) == len(self._user_part_at) + 1:
                 part_at = list(self._user_part_at)  # the stage count is whole again: the caller's own cut points
             else:

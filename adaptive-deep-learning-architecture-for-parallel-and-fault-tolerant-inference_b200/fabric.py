@@ -84,6 +84,8 @@ REC_WORDS = 6  # kind, epoch, k (dense index within the epoch), seq (global id),
 KIND_DATA, KIND_STOP = 1, 2
 KIND_PINNED = 0x100  # header flag: `aux` points at pinned host memory (DMA straight from it)
 KIND_RESIDENT = 0x200  # header flag: the first stage's input slots were preloaded (device-resident bench leg)
+KIND_FED = 0x400  # header flag: the dispatcher process itself copies this micro-batch's input into the first stage's
+#                   slot (the first stage lives in another process and cannot read the dispatcher's host memory)
 
 
 class ControlRing:

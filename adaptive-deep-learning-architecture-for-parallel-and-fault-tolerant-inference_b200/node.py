@@ -27,7 +27,7 @@ import numpy as np
 
 from . import _native as N
 from .dag_util import construct_model
-from .fabric import (G_EPOCH, G_PHASE, G_T0, G_T1, G_TIMING_REQ, KIND_DATA, KIND_PINNED, KIND_RESIDENT, KIND_STOP, PHASE_CONFIGURE, PHASE_QUIESCE, PHASE_RUN,
+from .fabric import (G_EPOCH, G_PHASE, G_T0, G_T1, G_TIMING_REQ, KIND_DATA, KIND_FED, KIND_PINNED, KIND_RESIDENT, KIND_STOP, PHASE_CONFIGURE, PHASE_QUIESCE, PHASE_RUN,
                      PHASE_SHUTDOWN, W_ACK_QUIESCE, W_ACK_READY, W_BUSY_N, W_BUSY_US, W_DEVICE, W_ERRORS, W_ELAPSED_US, W_HEARTBEAT, W_KILL, W_LAST_K, W_PID,
                      W_TIMING_ACK,
                      ControlRing, CudaBackend, HealthTable, ResultRing, ShmRegion, StateEnum, poison_value)
@@ -37,6 +37,9 @@ from .fabric import (G_EPOCH, G_PHASE, G_T0, G_T1, G_TIMING_REQ, KIND_DATA, KIND
 # host can overwrite them with plain stores -- which is what lets a reconfiguration release a
 # blocked stream without having to get a copy scheduled behind it.
 F_IN_READY, F_OUT_FREE, F_H2D_DONE, F_IN_CONSUMED, F_OUT_READY, F_OUT_COPIED = 0, 2, 4, 6, 8, 10
+F_XFER_PART = 12   # + 2 * j + slot: piece j (1..XFER_STREAMS-1) of a split hand-off copy has landed
+XFER_STREAMS = 4   # copy-engine streams a large hand-off is split over (several engines in flight on one link)
+XFER_SPLIT_MIN_BYTES = 8 << 20  # a piece of a split hand-off is at least this big
 COPY_HANDOFF_MIN_BYTES = 300 * 1024  # cut tensors at least this big per image go through a copy engine
 FLAG_WORDS = 64
 IMAGE_BYTES = 224 * 224 * 3 * 4
@@ -151,7 +154,11 @@ class StageWorker:
         self.d_out = b.alloc(self.max_batch * OUT_ROW_BYTES)
         self.stream = b.new_stream()
         self.copy_stream = b.new_stream()
-        self.xfer_stream = b.new_stream()  # copy-engine hand-off of large cut tensors
+        # copy-engine hand-off of large cut tensors: one copy per stream, so that a 205 MB conv2-level cut tensor is
+        # moved by several copy engines at once (ADAPT_XFER_STREAMS=1: a single copy)
+        n_x = max(1, min(XFER_STREAMS, int(os.environ.get("ADAPT_XFER_STREAMS", str(XFER_STREAMS)))))
+        self.xfer_streams = [b.new_stream() for _ in range(n_x)]
+        self.xfer_stream = self.xfer_streams[0]
         # pinned staging for pageable inputs (only the first stage of a session uses it)
         stage_bytes = self.max_batch * self.session["in_row_bytes"]
         self._stage_np = np.zeros(2 * stage_bytes + 4096, dtype=np.uint8)
@@ -205,7 +212,7 @@ class StageWorker:
         while True:
             self._write_own_flags(poison_value(self.fb))
             if not (self.backend.busy(self.copy_stream) or self.backend.busy(self.stream)
-                    or self.backend.busy(self.xfer_stream)
+                    or any(self.backend.busy(x) for x in self.xfer_streams)
                     or any(r["backend"].busy(r["stream"]) for r in getattr(self, "rails", []))):
                 return
             if time.monotonic() - t0 > 20:
@@ -318,6 +325,9 @@ class StageWorker:
             # measurement mode: the input batch was preloaded into both input slots (no copy); keep the
             # copy-side flag current so that copied micro-batches can follow resident ones
             b.write_flag(self.stream, self.flag(self.wid, F_H2D_DONE + s), v_done)
+        elif first and (kind & KIND_FED):
+            # the dispatcher process places the input in this slot itself (DEFER._proxy_feed) and raises the flag
+            b.wait_flag(self.stream, self.flag(self.wid, F_H2D_DONE + s), v_done)
         elif first:
             # host -> device copy of the input on the copy stream, double buffered against compute
             nbytes = batch * self.session["in_row_bytes"]
@@ -402,10 +412,20 @@ class StageWorker:
             # with compute instead of stretching the last kernel to NVLink speed).
             x = self.xfer_stream
             b.write_flag(self.stream, self.flag(self.wid, F_OUT_READY + s), v_done)
-            b.wait_flag(x, self.flag(self.wid, F_OUT_READY + s), v_done)
-            if k >= 2:
-                b.wait_flag(x, self.flag(self.wid, F_OUT_FREE + s), v_prev)  # consumer done with its slot s
-            b.d2d(self.in_buf(self.next_wid, s), self.out_buf(s), batch * self.executor.out_bytes_per_image, x)
+            nbytes = batch * self.executor.out_bytes_per_image
+            n_parts = max(1, min(len(self.xfer_streams), nbytes // XFER_SPLIT_MIN_BYTES))
+            step = (nbytes // n_parts + 4095) // 4096 * 4096
+            for j in range(n_parts):
+                xs = self.xfer_streams[j]
+                lo, hi = j * step, min(nbytes, (j + 1) * step)
+                b.wait_flag(xs, self.flag(self.wid, F_OUT_READY + s), v_done)
+                if k >= 2:
+                    b.wait_flag(xs, self.flag(self.wid, F_OUT_FREE + s), v_prev)  # consumer done with its slot s
+                b.d2d(self.in_buf(self.next_wid, s) + lo, self.out_buf(s) + lo, hi - lo, xs)
+                if j > 0:
+                    b.write_flag(xs, self.flag(self.wid, F_XFER_PART + 2 * j + s), v_done)
+            for j in range(1, n_parts):  # the first stream publishes once every piece has landed
+                b.wait_flag(x, self.flag(self.wid, F_XFER_PART + 2 * j + s), v_done)
             b.write_flag(x, self.flag(self.wid, F_OUT_COPIED + s), v_done)
             b.write_flag(x, self.flag(self.next_wid, F_IN_READY + s), v_done)
             self.rings[self.next_wid].push((kind, epoch, k, seq, batch, 0))
@@ -417,6 +437,33 @@ class StageWorker:
             b.event_record(self._timing_events[1], self.stream)
             self._timing_armed = True
         self.health.w[self.wid, W_LAST_K] = k
+
+    # ------------------------------------------------------------------ ingest on behalf of a remote first stage
+    def feed_remote_first_stage(self, target_wid: int, fb: int, k: int, batch: int, host_addr: int, pinned: bool) -> None:
+        """Dispatcher side of KIND_FED (called from the dispatcher's feeder thread, on the dispatcher-local worker
+        object whatever state its own stage is in): copy micro-batch k's input from this process's host memory into
+        input slot k & 1 of worker `target_wid` -- another process's GPU memory, mapped here over CUDA IPC -- on this
+        worker's copy stream, double buffered against that stage's compute with ITS flags."""
+        b = self.backend
+        s = k & 1
+        v_done, v_prev = (fb + k + 1) & 0xFFFFFFFF, (fb + k - 1) & 0xFFFFFFFF
+        nbytes = batch * self.session["in_row_bytes"]
+        src = host_addr
+        if not pinned:
+            fl = self.flags_host[target_wid]
+            t0 = time.monotonic()
+            while k >= 2 and ((int(fl[F_H2D_DONE + s]) - v_prev) & 0xFFFFFFFF) >= 0x80000000:
+                if self.health.phase != PHASE_RUN or self._stop.is_set():
+                    return
+                if time.monotonic() - t0 > 30:
+                    raise TimeoutError("input staging slot never drained")
+                time.sleep(20e-6)
+            ctypes.memmove(self.stage_addr[s], host_addr, nbytes)
+            src = self.stage_addr[s]
+        if k >= 2:
+            b.wait_flag(self.copy_stream, self.flag(target_wid, F_IN_CONSUMED + s), v_prev)
+        b.h2d(self.in_buf(target_wid, s), src, nbytes, self.copy_stream)
+        b.write_flag(self.copy_stream, self.flag(target_wid, F_H2D_DONE + s), v_done)
 
     # ------------------------------------------------------------------ busy time (straggler watchdog input)
     def _busy_begin(self):

@@ -176,6 +176,22 @@ def test_constructor_options_are_validated_and_published(pkg, model50):
         np.testing.assert_allclose(y, o.predict(x)[0], rtol=1e-5, atol=1e-7)
 
 
+def test_split_copy_handoff(pkg, model50, monkeypatch):
+    """Large cut tensors are pushed as several copies on separate streams (node.XFER_STREAMS) and published only once
+    every piece has landed: forced here on small tensors by lowering the split threshold."""
+    from adapt_b200 import node
+    from adapt_b200.dispatcher import DEFER
+
+    monkeypatch.setattr(node, "XFER_SPLIT_MIN_BYTES", 4096)
+    o = oracle_for(model50)
+    inputs = [KO.synthetic_images(b, seed=950 + i, kind="normal") for i, b in enumerate([1, 2, 2, 1, 2])]
+    d = DEFER([0, 1, 2], mode="fp32", max_batch=2, backend_factory=HostBackend, heartbeat_timeout=5.0, handoff="copy")
+    outs, stats = _run(d, model50, ["conv2_block3_out", "conv4_block6_out"], inputs)
+    assert stats["delivered"] == len(inputs)
+    for x, y in zip(inputs, outs):
+        np.testing.assert_allclose(y, o.predict(x)[0], rtol=1e-5, atol=1e-7)
+
+
 def test_bench_cut_selection(pkg, model50):
     """bench.py: N = 1 is the single chunk; N > 1 defaults to the time-balanced cuts, `--cuts config` to the split
     points BASELINE.json names for 2 and 4 stages; every choice is a valid partition."""

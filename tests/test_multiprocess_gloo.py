@@ -52,6 +52,29 @@ def _worker(rank, world, port, q):
             defer.shutdown()
             t.join(30)
             err = max([err] + [float(np.abs(y - o.predict(x)[0]).max()) for x, y in zip(inputs, outs)])
+        # third session: the dispatcher-local FIRST stage is lost.  The surviving stage lives in the other process and
+        # cannot read this process's host inputs: the dispatcher copies them into that stage's slot itself (KIND_FED)
+        inputs = [KO.synthetic_images(1, seed=930 + i, kind="normal") for i in range(7)]
+        defer = DEFER(["10.0.0.1", "10.0.0.2"], mode="fp32", max_batch=1, backend_factory=SharedHostBackend, heartbeat_timeout=0.5)
+        in_q, out_q = queue.Queue(), queue.Queue()
+        t = threading.Thread(target=defer.run_defer, args=(model, ["conv3_block4_out"], in_q, out_q), daemon=True)
+        t.start()
+        defer.wait_ready(120)
+        stream = []
+        for x in inputs[:3]:
+            in_q.put(x)
+            stream.append(out_q.get(timeout=120))
+        defer.inject_kill(0)
+        for x in inputs[3:]:                      # fed while the dead stage is being detected and the model re-sliced
+            in_q.put(x)
+        for _ in inputs[3:]:
+            stream.append(out_q.get(timeout=120))
+        time.sleep(0.05)
+        assert out_q.empty()
+        assert defer.stats["failovers"] == 1 and defer.order == [1] and defer.part_at == [], (defer.stats, defer.order)
+        defer.shutdown()
+        t.join(30)
+        err = max([err] + [float(np.abs(y - o.predict(x)[0]).max()) for x, y in zip(inputs, stream)])   # FIFO, exactly once
         end_sessions()
         q.put((0, "ok", err))
     except Exception as e:  # noqa: BLE001
@@ -88,5 +111,5 @@ def test_two_rank_pipeline_over_gloo():
         if p.is_alive():
             p.kill()
     assert results.get(0, ("missing", None))[0] == "ok", results
-    assert results.get(1, ("missing", None)) == ("ok", 2), results      # the worker rank served both sessions
+    assert results.get(1, ("missing", None)) == ("ok", 3), results      # the worker rank served all three sessions
     assert results[0][1] < 1e-5
