@@ -59,11 +59,30 @@ def block_boundaries(model) -> List[str]:
     return [l.name for l in model.layers if l.name == "pool1_pool" or (l.name.endswith("_out") and "block" in l.name)]
 
 
+# Measured device time of one fused launch at micro-batch 128 on a B200 (CUDA events around single launches,
+# profiles/r2_ops_b128.json), keyed by the Keras layer's shape: (kernel, stride, input height, Cin, Cout, shortcut
+# Add fused into it).  The chained `_2_conv` -> `_3_conv` kernel of conv2 / conv3 is split 1/3 : 2/3 between its layers
+# (cuts never separate them).  Layers of other shapes fall back to the roofline formula below.
+MEASURED_US_B128 = {
+    (7, 2, 230, 3, 64, False): 79.7,
+    (1, 1, 56, 64, 64, False): 22.8, (3, 1, 56, 64, 64, False): 31.0, (1, 1, 56, 64, 256, False): 55.5,
+    (1, 1, 56, 64, 256, True): 62.0, (1, 1, 56, 256, 64, False): 49.0,
+    (1, 2, 56, 256, 128, False): 22.4, (1, 2, 56, 256, 512, False): 43.6, (3, 1, 28, 128, 128, False): 21.0,
+    (1, 1, 28, 128, 512, True): 41.0, (1, 1, 28, 512, 128, False): 33.0,
+    (1, 2, 28, 512, 256, False): 18.4, (1, 2, 28, 512, 1024, False): 30.9, (3, 1, 14, 256, 256, False): 30.7,
+    (1, 1, 14, 256, 1024, True): 31.0, (1, 1, 14, 1024, 256, False): 24.7,
+    (1, 2, 14, 1024, 512, False): 18.6, (1, 2, 14, 1024, 2048, False): 29.0, (3, 1, 7, 512, 512, False): 36.6,
+    (1, 1, 7, 512, 2048, True): 24.5, (1, 1, 7, 2048, 512, False): 22.8,
+}
+IN_GRAPH_OVERLAP = 0.85   # consecutive launches overlap inside the stage's CUDA graph (programmatic dependent launch)
+MIN_LAUNCH_US = 6.0       # what a launch costs however small the batch
+
+
 def estimate_layer_seconds(model, l, batch: int = 128) -> float:
-    """Roofline estimate of one Keras layer's time on a B200 inside a fused stage program (bf16):
-    max(FLOPs / sustained tensor rate, HBM bytes / sustained bandwidth) for convolutions, bytes /
-    bandwidth for the pooling layers, 0 for layers that are fused away.  Constants calibrated on
-    profiles/ (within ~15% of the measured per-layer times)."""
+    """Estimate of one Keras layer's time on a B200 inside a fused stage program (bf16): the measured table above
+    where the layer's shape is in it (scaled with the micro-batch, floored at a launch's fixed cost), else
+    max(FLOPs / tensor rate, HBM bytes / bandwidth) for convolutions and bytes / bandwidth for the pooling layers;
+    0 for layers that are fused away."""
     cons = [c for c in model.layers if l.name in c.inbound_names]
     if l.class_name in ("Conv2D", "Dense"):
         macs = layer_macs(model, l) * batch
@@ -74,25 +93,29 @@ def estimate_layer_seconds(model, l, batch: int = 128) -> float:
         out_elems = float(np.prod(l.output_shape[1:]))
         bn = cons[0] if len(cons) == 1 and cons[0].class_name == "BatchNormalization" else None
         fused_add = bn is not None and any(c.class_name == "Add" for c in model.layers if bn.name in c.inbound_names)
+        if l.class_name == "Dense":
+            return max(34.1e-6 * batch / 128, 2 * MIN_LAUNCH_US * 1e-6) * IN_GRAPH_OVERLAP   # Dense + softmax launches
+        key = (k, stride, int(src.output_shape[1]), int(src.output_shape[-1]), int(l.output_shape[-1]), bool(fused_add))
+        if key in MEASURED_US_B128:
+            return max(MEASURED_US_B128[key] * batch / 128, MIN_LAUNCH_US) * 1e-6 * IN_GRAPH_OVERLAP
         byts = 2.0 * batch * (in_elems + out_elems * (2 if fused_add else 1))
         rate = 400e12 if (k == 3 and l.output_shape[-1] <= 64) else (650e12 if k == 3 else 700e12)
-        if k == 7:  # stem: space-to-depth form, 0.14 ms measured at batch 128
-            return 1.1e-6 * batch
         return max(2.0 * macs / rate, byts / 5.0e12) + 4e-6
     if l.class_name == "MaxPooling2D":
-        return 2.0 * batch * float(np.prod(model.get_layer(l.inbound_names[0]).output_shape[1:])) / 3.2e12
+        return 2.0 * batch * float(np.prod(model.get_layer(l.inbound_names[0]).output_shape[1:])) / 2.95e12
     if l.class_name == "InputLayer":
-        return 0.27e-6 * batch  # ingest
+        return 0.24e-6 * batch  # ingest
     if l.class_name == "GlobalAveragePooling2D":
-        return 15e-6
+        return 14.6e-6 * max(batch / 128, 0.4)
     return 0.0
 
 
-def balanced_part_at(model, n_stages: int, cost_model: str = "time", batch: int = 128, link_gbs: float = 650.0) -> List[str]:
+def balanced_part_at(model, n_stages: int, cost_model: str = "time", batch: int = 128, link_gbs: float = 700.0) -> List[str]:
     """`part_at` for `n_stages` stages minimising the slowest stage: dynamic programme over
     residual-block boundaries.  cost_model "time": a stage costs max(sum of its layers' estimated
-    times, its hand-off bytes / NVLink bandwidth) (the hand-off is overlapped with compute);
-    "macs": multiply-accumulates only."""
+    times + the HBM time its hand-offs steal from them, its hand-off bytes / NVLink bandwidth) (the hand-off is
+    overlapped with compute, but a copy-engine hand-off reads the cut tensor out of the producer's HBM and writes it
+    into the consumer's while both compute); "macs": multiply-accumulates only."""
     if n_stages <= 1:
         return []
     cands = block_boundaries(model)
@@ -107,10 +130,19 @@ def balanced_part_at(model, n_stages: int, cost_model: str = "time", batch: int 
     idx = [order[c] for c in cands]
     last = len(model.layers) - 1
 
+    def cut_bytes(i: int) -> float:
+        return 2.0 * batch * float(np.prod(model.layers[i].output_shape[1:]))
+
+    def hbm_tax(i: int) -> float:  # a copy-engine hand-off's pass over HBM (large cut tensors only: node.COPY_HANDOFF_MIN_BYTES)
+        return cut_bytes(i) / 6.0e12 if cut_bytes(i) / batch >= 300 * 1024 else 0.0
+
     def cost(a: int, b: int, emits: bool) -> float:  # layers (a, b]
         c = pref[b] - pref[a]
-        if emits and cost_model != "macs":
-            c = max(c, 2.0 * batch * float(np.prod(model.layers[b].output_shape[1:])) / (link_gbs * 1e9))
+        if cost_model != "macs":
+            if a > 0:
+                c += hbm_tax(a)
+            if emits:
+                c = max(c + hbm_tax(b), cut_bytes(b) / (link_gbs * 1e9))
         return c
 
     INF = float("inf")

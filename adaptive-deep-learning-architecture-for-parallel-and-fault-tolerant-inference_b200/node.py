@@ -38,7 +38,10 @@ from .fabric import (G_EPOCH, G_PHASE, G_T0, G_T1, G_TIMING_REQ, KIND_DATA, KIND
 # blocked stream without having to get a copy scheduled behind it.
 F_IN_READY, F_OUT_FREE, F_H2D_DONE, F_IN_CONSUMED, F_OUT_READY, F_OUT_COPIED = 0, 2, 4, 6, 8, 10
 F_XFER_PART = 12   # + 2 * j + slot: piece j (1..XFER_STREAMS-1) of a split hand-off copy has landed
-XFER_STREAMS = 4   # copy-engine streams a large hand-off is split over (several engines in flight on one link)
+XFER_STREAMS = 1   # copy streams a large hand-off may be split over.  Measured on B200 (tools/handoff_bench.py, 205 MB
+#                    GPU 0 -> GPU 1): ONE copy reaches 737 GB/s, split in 2 / 4 / 8 concurrent pieces 693 / 602 / 488 GB/s
+#                    -- several copy engines on one link get in each other's way -- so the default is a single copy;
+#                    ADAPT_XFER_STREAMS=n keeps the split path available.
 XFER_SPLIT_MIN_BYTES = 8 << 20  # a piece of a split hand-off is at least this big
 COPY_HANDOFF_MIN_BYTES = 300 * 1024  # cut tensors at least this big per image go through a copy engine
 FLAG_WORDS = 64
@@ -154,9 +157,8 @@ class StageWorker:
         self.d_out = b.alloc(self.max_batch * OUT_ROW_BYTES)
         self.stream = b.new_stream()
         self.copy_stream = b.new_stream()
-        # copy-engine hand-off of large cut tensors: one copy per stream, so that a 205 MB conv2-level cut tensor is
-        # moved by several copy engines at once (ADAPT_XFER_STREAMS=1: a single copy)
-        n_x = max(1, min(XFER_STREAMS, int(os.environ.get("ADAPT_XFER_STREAMS", str(XFER_STREAMS)))))
+        # copy-engine hand-off of large cut tensors (optionally split over several streams, see XFER_STREAMS)
+        n_x = max(1, min(4, int(os.environ.get("ADAPT_XFER_STREAMS", str(XFER_STREAMS)))))
         self.xfer_streams = [b.new_stream() for _ in range(n_x)]
         self.xfer_stream = self.xfer_streams[0]
         # pinned staging for pageable inputs (only the first stage of a session uses it)

@@ -177,12 +177,13 @@ def test_constructor_options_are_validated_and_published(pkg, model50):
 
 
 def test_split_copy_handoff(pkg, model50, monkeypatch):
-    """Large cut tensors are pushed as several copies on separate streams (node.XFER_STREAMS) and published only once
-    every piece has landed: forced here on small tensors by lowering the split threshold."""
+    """A hand-off copy can be split over several streams (ADAPT_XFER_STREAMS; off by default: measured slower on one
+    NVLink) and is then published only once every piece has landed: forced here on small tensors."""
     from adapt_b200 import node
     from adapt_b200.dispatcher import DEFER
 
     monkeypatch.setattr(node, "XFER_SPLIT_MIN_BYTES", 4096)
+    monkeypatch.setenv("ADAPT_XFER_STREAMS", "4")
     o = oracle_for(model50)
     inputs = [KO.synthetic_images(b, seed=950 + i, kind="normal") for i, b in enumerate([1, 2, 2, 1, 2])]
     d = DEFER([0, 1, 2], mode="fp32", max_batch=2, backend_factory=HostBackend, heartbeat_timeout=5.0, handoff="copy")
