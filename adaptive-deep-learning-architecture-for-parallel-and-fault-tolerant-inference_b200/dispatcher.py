@@ -31,7 +31,7 @@ from . import _native as N
 from .dag_util import PartModel, construct_model, layer_macs
 from .fabric import (G_EPOCH, G_NWORKERS, G_PHASE, G_T0, G_T1, G_TIMING_REQ, KIND_DATA, KIND_FED, KIND_PINNED, KIND_RESIDENT, KIND_STOP,
                      W_ELAPSED_US, W_TIMING_ACK, MAX_WORKERS, PHASE_CONFIGURE, PHASE_INIT,
-                     PHASE_QUIESCE, PHASE_RUN, PHASE_SHUTDOWN, FLAG_BASE_STEP, W_ACK_QUIESCE, W_ACK_READY, W_BUSY_N, W_BUSY_US,
+                     PHASE_QUIESCE, PHASE_RUN, PHASE_SHUTDOWN, FLAG_BASE_STEP, W_ACK_QUIESCE, W_ACK_READY, W_BUSY_MIN_US, W_BUSY_N, W_BUSY_US,
                      W_KILL, W_LAST_K, W_STATE,
                      ControlRing, CudaBackend, HealthTable, ResultRing, ShmRegion, StateEnum, poison_value)
 from .node import IMAGE_BYTES, OUT_ROW_BYTES, StageWorker, arena_slot_bytes
@@ -559,7 +559,7 @@ class DEFER:
     def _find_straggler(self):
         """(worker, evidence) of a stage that is alive but slow, or None.  Two signals, both self-calibrating:
         the stage's busy time per micro-batch (moving average its worker publishes, CUDA events around the stage's
-        work) against the LOWEST value that same stage showed in this epoch, and the age of the oldest in-flight
+        work) against the FASTEST micro-batch that same stage ran in this epoch, and the age of the oldest in-flight
         micro-batch (`inflight_tasks[seq]["start_time"]`) against `task_timeout`."""
         if len(self.order) < 2:
             return None  # nobody to hand the layers to
@@ -569,7 +569,9 @@ class DEFER:
             n, busy = int(h.w[w, W_BUSY_N]), float(h.w[w, W_BUSY_US])
             if n < 8 or busy <= 0:
                 continue
-            base = min(self._busy_base.get(w, busy), busy)
+            # baseline: the fastest micro-batch this stage ran in this epoch (published by its worker), or -- for a
+            # worker that was dropped as a straggler before -- what it did when healthy, whichever is lower
+            base = min(self._busy_base.get(w, busy), busy, float(h.w[w, W_BUSY_MIN_US]) or busy)
             self._busy_base[w] = base
             ratios[w] = busy / max(base, 1.0)
         if self.straggler_factor:

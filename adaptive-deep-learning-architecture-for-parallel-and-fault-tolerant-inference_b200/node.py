@@ -28,7 +28,7 @@ import numpy as np
 from . import _native as N
 from .dag_util import construct_model
 from .fabric import (G_EPOCH, G_PHASE, G_T0, G_T1, G_TIMING_REQ, KIND_DATA, KIND_FED, KIND_PINNED, KIND_RESIDENT, KIND_STOP, PHASE_CONFIGURE, PHASE_QUIESCE, PHASE_RUN,
-                     PHASE_SHUTDOWN, W_ACK_QUIESCE, W_ACK_READY, W_BUSY_N, W_BUSY_US, W_DEVICE, W_ERRORS, W_ELAPSED_US, W_HEARTBEAT, W_KILL, W_LAST_K, W_PID,
+                     PHASE_SHUTDOWN, W_ACK_QUIESCE, W_ACK_READY, W_BUSY_MIN_US, W_BUSY_N, W_BUSY_US, W_DEVICE, W_ERRORS, W_ELAPSED_US, W_HEARTBEAT, W_KILL, W_LAST_K, W_PID,
                      W_TIMING_ACK,
                      ControlRing, CudaBackend, HealthTable, ResultRing, ShmRegion, StateEnum, poison_value)
 
@@ -143,6 +143,7 @@ class StageWorker:
         self._busy_events: List[tuple] = []
         self._busy_pending: List[tuple] = []
         self._busy_ewma = 0.0
+        self._busy_min = 0.0
         self._busy_n = 0
         if hasattr(self.backend, "abort_check"):  # synchronous test backends must be able to give up a wait
             self.backend.abort_check = lambda: (self.health.phase != PHASE_RUN or bool(self.health.w[self.wid, W_KILL])
@@ -500,14 +501,17 @@ class StageWorker:
     def _busy_fold(self, us: float) -> None:
         self._busy_n += 1
         self._busy_ewma = us if self._busy_n == 1 else 0.75 * self._busy_ewma + 0.25 * us
+        self._busy_min = us if self._busy_n == 1 else min(self._busy_min, us)
         self.health.w[self.wid, W_BUSY_US] = int(self._busy_ewma)
+        self.health.w[self.wid, W_BUSY_MIN_US] = max(1, int(self._busy_min))
         self.health.w[self.wid, W_BUSY_N] = self._busy_n
 
     def _busy_reset(self) -> None:
         self._busy_events += self._busy_pending  # (streams are drained when this runs)
         self._busy_pending = []
-        self._busy_ewma, self._busy_n = 0.0, 0
+        self._busy_ewma, self._busy_n, self._busy_min = 0.0, 0, 0.0
         self.health.w[self.wid, W_BUSY_US] = 0
+        self.health.w[self.wid, W_BUSY_MIN_US] = 0
         self.health.w[self.wid, W_BUSY_N] = 0
 
     def _report_timing(self) -> None:

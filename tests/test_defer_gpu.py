@@ -72,7 +72,7 @@ def test_reference_driver_shape(pkg, model50):
     _check(model50, [], [x], outs[:1], oracle_tol="absolute")
     for o in outs[1:]:
         np.testing.assert_array_equal(o, outs[0])
-    assert launches >= 10 * 58
+    assert launches == 10 * 51          # 58 fused groups, 7 bottleneck tails chained (3x3 -> 1x1) into one launch each
 
 
 @pytest.mark.parametrize("part_at", [["conv3_block4_out"], ["conv2_block3_out", "conv3_block4_out", "conv4_block6_out"]])
@@ -222,7 +222,7 @@ def test_straggler_stage_is_dropped_gpu(pkg, model50, monkeypatch):
     defer = DEFER(devs, max_batch=2, heartbeat_timeout=0.25, straggler_factor=6.0, straggler_window=0.15)
     outs, stats, _ = _run(defer, model50, ["conv2_block3_out", "conv4_block1_out"], inputs, timeout=60)
     monkeypatch.delenv("ADAPT_FAULT_INJECT")
-    assert stats["stragglers"] == 1 and stats["failovers"] == 1 and stats["delivered"] == len(inputs), stats
+    assert stats["stragglers"] == 1 and stats["failovers"] == 1 and stats["delivered"] == len(inputs), repr(sorted(stats.items()))
     ev = stats["straggler_events"][0]
     assert ev["worker"] == 1 and ev["reason"] == "busy time" and ev["ratio"] >= 6.0, ev
     assert len(defer.part_at) == 1 and 1 not in defer.order
