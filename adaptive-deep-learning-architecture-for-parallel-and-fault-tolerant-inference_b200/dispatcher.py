@@ -31,7 +31,7 @@ from . import _native as N
 from .dag_util import PartModel, construct_model, layer_macs
 from .fabric import (G_EPOCH, G_NWORKERS, G_PHASE, G_T0, G_T1, G_TIMING_REQ, KIND_DATA, KIND_FED, KIND_PINNED, KIND_RESIDENT, KIND_STOP,
                      W_ELAPSED_US, W_TIMING_ACK, MAX_WORKERS, PHASE_CONFIGURE, PHASE_INIT,
-                     PHASE_QUIESCE, PHASE_RUN, PHASE_SHUTDOWN, FLAG_BASE_STEP, W_ACK_QUIESCE, W_ACK_READY, W_BUSY_MIN_US, W_BUSY_N, W_BUSY_US,
+                     PHASE_QUIESCE, PHASE_RUN, PHASE_SHUTDOWN, FLAG_BASE_STEP, W_ACK_QUIESCE, W_ACK_READY, W_BUSY_MIN_US, W_BUSY_N, W_BUSY_US, W_PID,
                      W_KILL, W_LAST_K, W_STATE,
                      ControlRing, CudaBackend, HealthTable, ResultRing, ShmRegion, StateEnum, poison_value)
 from .node import IMAGE_BYTES, OUT_ROW_BYTES, StageWorker, arena_slot_bytes
@@ -336,11 +336,12 @@ class DEFER:
             # stage will never write (e.g. a pageable host-to-device copy ordered behind such a wait), so
             # the dispatcher releases every flag wait centrally while it collects the acknowledgements.
             self._wait_acks(active, W_ACK_QUIESCE, epoch, 30.0, poison=poison_value(old_base))
-            # Workers that lost their stage but whose process still beats (declared dead on a late heartbeat, or
-            # never part of the order) drain too; they are given a bounded moment to say so.  Whoever stays silent
-            # is covered by the flag base above.
-            others = [w for w in range(self._n_workers) if w not in active and not int(h.w[w, W_KILL])
-                      and h.age_ms(w) <= 4 * self.heartbeat_timeout * 1e3 and int(h.w[w, W_STATE]) != StateEnum.ERROR]
+            # Workers outside the new order whose PROCESS still exists -- declared dead on a late heartbeat, killed by
+            # injection (their queued GPU work was left blocked, node.StageWorker._die), or never part of the order --
+            # flush their streams too; they are given a bounded moment to say so.  Whoever stays silent (a process
+            # that is really gone has no GPU work left) is covered by the flag base above.
+            others = [w for w in range(self._n_workers) if w not in active and int(h.w[w, W_STATE]) != StateEnum.ERROR
+                      and StageWorker.pid_alive(int(h.w[w, W_PID]))]
             if others:
                 try:
                     self._wait_acks(others, W_ACK_QUIESCE, epoch, max(0.25, 4 * self.heartbeat_timeout),

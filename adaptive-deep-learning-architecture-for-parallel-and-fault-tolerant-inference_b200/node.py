@@ -547,18 +547,40 @@ class StageWorker:
             self._hb_native = None
 
     def _die(self) -> None:
-        """Injected stage kill: go silent (no more heartbeats, no more work, in-flight micro-batches
-        are lost) after draining the GPU queue so a zombie cannot scribble on live peers."""
+        """Injected stage kill: go silent -- no more heartbeats, no more work enqueued; in-flight micro-batches are
+        lost.  What is already queued on the GPU is NOT flushed here: releasing its flag waits would let it run on
+        inputs that have not arrived and hand garbage to the next stage, whose results the collector would deliver
+        until the heartbeat time-out fires (a crashed process's queued work simply disappears).  It finishes on real
+        inputs or stays blocked, and is flushed when the dispatcher quiesces the pipeline (`run`, below)."""
         self.dead = True
         self._stop_heartbeat()
         if not self.session.get("silent_kill", False):
             self.state.state = StateEnum.DEAD  # a crash would not announce itself; see `silent_kill`
         if self.on_kill is not None:
             self.on_kill()
+
+    @staticmethod
+    def pid_alive(pid: int) -> bool:
+        if pid <= 0:
+            return False
+        if pid == os.getpid():
+            return True
         try:
-            self._drain()
-        except Exception:
-            pass
+            os.kill(pid, 0)
+            return True
+        except OSError:
+            return False
+
+    def _await_peers_drained(self, timeout: float = 2.0) -> None:
+        """Shutdown: nobody frees its arena while a peer whose process is alive may still have GPU work queued that
+        writes into it (every worker marks W_ACK_READY = -1 once its streams are idle for good)."""
+        t0 = time.monotonic()
+        while time.monotonic() - t0 < timeout:
+            pending = [w for w in range(self.session["n_workers"]) if w != self.wid and int(self.health.w[w, W_ACK_READY]) != -1
+                       and self.pid_alive(int(self.health.w[w, W_PID]))]
+            if not pending:
+                return
+            time.sleep(1e-3)
 
     def run(self) -> None:
         """Blocking worker loop (the reference's `Node.run`, src/node.py:181-194)."""
@@ -574,6 +596,13 @@ class StageWorker:
                     # silent until shut down -- or revived (DEFER.revive clears the kill word): then the heartbeat
                     # resumes and the worker idles without a stage until the dispatcher re-slices it back in
                     while int(h.w[self.wid, W_KILL]) and not self._stop.is_set() and h.phase != PHASE_SHUTDOWN:
+                        if h.phase == PHASE_QUIESCE and int(h.w[self.wid, W_ACK_QUIESCE]) != h.epoch:
+                            # the pipeline is being re-sliced: flush what this dead stage still has queued, like
+                            # everyone else (whatever it writes now carries the old epoch's flag values)
+                            try:
+                                self._quiesce(h.epoch)
+                            except Exception:  # noqa: BLE001
+                                pass
                         time.sleep(1e-3)
                     if self._stop.is_set() or h.phase == PHASE_SHUTDOWN:
                         break
@@ -617,7 +646,13 @@ class StageWorker:
         finally:
             self._stop_heartbeat()
             try:
+                if self.arena:
+                    self._drain()  # (a stage killed shortly before shutdown may still have work blocked on its flags)
                 self.backend.sync(self.stream)
+            except Exception:
+                pass
+            try:
+                self.health.w[self.wid, W_ACK_READY] = -1  # streams idle for good: peers may free what they own
             except Exception:
                 pass
 
@@ -632,6 +667,12 @@ class StageWorker:
 
     def close(self) -> None:
         self.stop()
+        try:
+            if self.health is not None:
+                self.health.w[self.wid, W_ACK_READY] = -1
+                self._await_peers_drained()
+        except Exception:
+            pass
         if self.executor is not None:
             self.executor.close()
             self.executor = None

@@ -170,6 +170,24 @@ def test_failover_resliced_and_replayed(pkg, model50):
     assert stats["failover_ms"] and stats["failover_ms"][0] < 1000.0   # sub-second recovery (north_star)
 
 
+def test_killed_stage_with_queued_work_forwards_nothing_wrong(pkg, model50, monkeypatch):
+    """A stage dies while several micro-batches are queued on its stream (the last stage is slowed down so that the
+    pipeline backs up).  Its queued GPU work must not be released early: it would run on inputs that have not arrived
+    and hand garbage downstream, which the collector would deliver until the heartbeat time-out fires.  Every result
+    -- before, during and after the fail-over -- must be that of ITS input."""
+    from adapt_b200.dispatcher import DEFER
+
+    monkeypatch.setenv("ADAPT_FAULT_INJECT", "slow_worker:3:3000:0")     # last stage: +3 ms per micro-batch
+    devs = [f"cuda:{i % max(1, _ngpu())}" for i in range(4)]
+    part_at = ["conv2_block3_out", "conv3_block4_out", "conv4_block6_out"]
+    inputs = [distinct_images(4, 1100, i) for i in range(36)]
+    defer = DEFER(devs, max_batch=4, heartbeat_timeout=0.05, straggler_factor=None)
+    outs, stats, _ = _run(defer, model50, part_at, inputs, kill_after=8, kill_stage=1, timeout=60)
+    monkeypatch.delenv("ADAPT_FAULT_INJECT")
+    assert stats["failovers"] == 1 and stats["delivered"] == len(inputs), repr(sorted(stats.items()))
+    _check(model50, [part_at, defer.part_at], inputs, outs, oracle_every=9)
+
+
 def test_elastic_rejoin_after_failover_gpu(pkg, model50):
     """Kill a stage mid-stream (3 -> 2 stages), revive it, and the watchdog re-slices it back in (2 -> 3) while
     inputs keep flowing: FIFO and exactly once across both reconfigurations, values against the oracle."""
