@@ -58,38 +58,30 @@ struct ConvChainParams {
 };
 
 constexpr int kChainBN2 = 128;      // phase-2 n-tile width
-constexpr int kChainMaxEpiWarps = 16;
-__host__ __device__ constexpr int conv_chain_threads(int epi_warps) { return 64 + 32 * epi_warps; }  // TMA + MMA + epilogue
+constexpr int kChainThreads = 320;  // TMA + MMA + 8 epilogue warps
 constexpr int kChainMaxStages = 6;
 constexpr int kChainMaxRing = 4;
 
 template <int C, bool PAIR>
-__host__ __device__ constexpr int conv_chain_smem_bytes(int stages, int ring, int epi_warps = 8) {
+__host__ __device__ constexpr int conv_chain_smem_bytes(int stages, int ring) {
     constexpr int b1 = (PAIR ? C / 2 : C) * 128;  // one k-block of the 3x3's weights held by this CTA
     constexpr bool resident = !PAIR;
     constexpr int c_blocks = C / 64;
     // (a phase-2 stage -- one n-tile of the 1x1's weights, 16 KiB per CTA -- lives in the A slot of a ring stage)
     const int ring1 = stages * kRow3ABytes + (resident ? 9 * c_blocks * b1 : stages * 3 * b1);
     const int a2 = c_blocks * kABytes;
-    const int slabs = epi_warps * ring * kEpiSlabBytes;
+    const int slabs = kEpiWarps * ring * kEpiSlabBytes;
     const int sb = 2 * (C + 4 * C) * 4;
-    return ring1 + a2 + slabs + sb + 2048 /*barriers*/ + 1024 /*alignment*/;
+    return ring1 + a2 + slabs + sb + 1024 /*barriers*/ + 1024 /*alignment*/;
 }
 
-// EW = epilogue warps: 8 (two per scheduler; every warp drains both 64-column chunks of its group's n-tiles) or 16 (four
-// per scheduler, twice the latency hiding in the instruction-bound epilogue: each warp drains ONE chunk per n-tile and
-// converts 16-column units of acc1; one residual slab per warp, refilled as soon as it has been written out).
-template <int C, bool PAIR, int EW>
-__global__ void __launch_bounds__(conv_chain_threads(EW), 1)
+template <int C, bool PAIR>
+__global__ void __launch_bounds__(kChainThreads, 1)
 conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w2,
                   const __grid_constant__ CUtensorMap tmap_w3, const __grid_constant__ CUtensorMap tmap_res,
                   const ConvChainParams p) {
     static_assert(C == 64 || C == 128, "chain kernel: C = 64 (single CTA) or 128 (CTA pair)");
     static_assert(PAIR == (C == 128), "C = 128 runs on CTA pairs, C = 64 on single CTAs");
-    static_assert(EW == 8 || EW == 16, "8 or 16 epilogue warps");
-    constexpr int HALVES = EW / 8;               // warps sharing one (group, lane quarter): they split the n-tile's chunks
-    constexpr int UW = 32 / HALVES;              // columns of acc1 a warp converts per step
-    constexpr int NC = EW / 4;                   // warps per lane quarter
     constexpr int CL = PAIR ? 2 : 1;
     constexpr bool RESIDENT = !PAIR;             // the 3x3's weights stay in shared memory
     constexpr int c_blocks = C / 64;             // k-blocks per tap (phase 1) = k-blocks of phase 2
@@ -110,7 +102,7 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     uint8_t* smem_b1 = smem_a + kStages * kRow3ABytes;
     uint8_t* smem_a2 = smem_b1 + (RESIDENT ? 9 * c_blocks * kB1 : kStages * 3 * kB1);
     uint8_t* smem_epi = smem_a2 + c_blocks * kABytes;
-    float* smem_sb = reinterpret_cast<float*>(smem_epi + EW * p.ring * kEpiSlabBytes);  // scale1 bias1 scale2 bias2
+    float* smem_sb = reinterpret_cast<float*>(smem_epi + kEpiWarps * p.ring * kEpiSlabBytes);  // scale1 bias1 scale2 bias2
     uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(smem_sb) + 2 * (C + 4 * C) * 4);
     uint64_t* full_bar = bars;                               // [kChainMaxStages]
     uint64_t* empty_bar = bars + kChainMaxStages;            // [kChainMaxStages]
@@ -119,9 +111,9 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     uint64_t* acc2_full = a2_full + 1;                       // [2]
     uint64_t* acc2_empty = acc2_full + 2;                    // [2]
     uint64_t* w_full = acc2_empty + 2;                       // [1] resident weights
-    uint64_t* res_bar = w_full + 1;                          // [EW][kChainMaxRing]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + EW * kChainMaxRing);
-    constexpr int kNumBars = 2 * kChainMaxStages + 1 + 1 + 2 + 2 + 1 + EW * kChainMaxRing;
+    uint64_t* res_bar = w_full + 1;                          // [kEpiWarps][kChainMaxRing]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + kEpiWarps * kChainMaxRing);
+    constexpr int kNumBars = 2 * kChainMaxStages + 1 + 1 + 2 + 2 + 1 + kEpiWarps * kChainMaxRing;
 
     const int warp_idx = __shfl_sync(0xffffffff, threadIdx.x / 32, 0);
     const int lane = threadIdx.x % 32;
@@ -140,8 +132,8 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     if (warp_idx == 0) {
         for (int i = lane; i < kNumBars; i += 32) {
             uint32_t count = 1;
-            if (&bars[i] == a2_full) count = EW * CL;                            // every epilogue warp (of both CTAs)
-            if (&bars[i] == acc2_empty || &bars[i] == acc2_empty + 1) count = (EW / 2) * CL;  // the draining group (of both CTAs)
+            if (&bars[i] == a2_full) count = kEpiWarps * CL;                     // every epilogue warp (of both CTAs)
+            if (&bars[i] == acc2_empty || &bars[i] == acc2_empty + 1) count = 4 * CL;  // the draining group (of both CTAs)
             ptx::mbar_init(&bars[i], count);
         }
         ptx::fence_mbar_init();
@@ -345,12 +337,10 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                 }
             }
         }
-    } else if (warp_idx < 2 + EW) {
+    } else if (warp_idx < 2 + kEpiWarps) {
         // ===================== epilogue =====================
         const int epi_warp = warp_idx - 2;
-        const int combo = epi_warp >> 2;          // 0 .. NC-1: which of the warps of this lane quarter
-        const int group = combo / HALVES;         // accumulator acc2[group]: n-tiles group, group + 2, ...
-        const int half = combo % HALVES;          // chunks half, half + HALVES, .. of each of those n-tiles
+        const int group = epi_warp >> 2;
         const int lane_group = warp_idx & 3;  // TMEM lanes this warp may touch: [32 * lane_group, +32)
         uint8_t* my_slabs = smem_epi + epi_warp * p.ring * kEpiSlabBytes;
         const uint32_t slabs_sa = ptx::smem_u32(my_slabs);
@@ -361,7 +351,7 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         const uint32_t taddr_lane = tmem_base + (static_cast<uint32_t>(lane_group * 32) << 16);
 
         // residual prefetch cursor: this warp's chunks in consumption order (tile, n-tile = group, group + 2, .., chunk)
-        int ri_ti = 0, ri_n2 = group, ri_c = half, ri_q = 0, ri_p = 0, ri_img = 0;
+        int ri_ti = 0, ri_n2 = group, ri_c = 0, ri_q = 0, ri_p = 0, ri_img = 0;
         uint32_t ri_slot = 0;
         bool ri_live = false, ri_more = true;
         auto ri_locate = [&]() {
@@ -385,9 +375,8 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                                         ri_n2 * kChainBN2 + ri_c * kEpiCols, ri_q, ri_p, ri_img, 0, 0);
             }
             if (++ri_slot == ring) ri_slot = 0;
-            ri_c += HALVES;
-            if (ri_c >= kChainBN2 / kEpiCols) {
-                ri_c = half;
+            if (++ri_c == kChainBN2 / kEpiCols) {
+                ri_c = 0;
                 ri_n2 += 2;
                 if (ri_n2 >= n2_tiles) {
                     ri_n2 = group;
@@ -397,9 +386,7 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             }
         };
         ri_locate();
-        // prime: ring - 1 chunks in flight (a ring of one: the chunk about to be worked on; its slab is refilled as
-        // soon as it has been written out)
-        for (uint32_t i = 0; i < (ring > 1 ? ring - 1 : 1); ++i) issue_residual();
+        for (uint32_t i = 0; i + 1 < ring; ++i) issue_residual();  // prime: ring - 1 chunks in flight
 
         int m_blk = 0;
         bool m_valid = true;
@@ -435,7 +422,7 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                     const int img = rest / p.H;
                     const int pr = rest - img * p.H;
                     for (int n2 = group; n2 < n2_tiles; n2 += 2)
-                        for (int c = half; c < kChainBN2 / kEpiCols; c += HALVES)
+                        for (int c = 0; c < kChainBN2 / kEpiCols; ++c)
                             ptx::tma_prefetch_im2col_4d(&tmap_res, n2 * kChainBN2 + c * kEpiCols, q, pr, img, 0, 0);
                 }
             }
@@ -445,18 +432,14 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             {
                 const int row = lane_group * 32 + lane;
 #pragma unroll 1
-                for (int u = combo; u < C / UW; u += NC) {  // UW-column units are dealt round-robin to the NC warps
-                    uint32_t v[UW];
-                    if constexpr (UW == 32)
-                        ptx::tmem_ld_32x32b_x32(taddr_lane + u * UW, v);
-                    else
-                        ptx::tmem_ld_32x32b_x16(taddr_lane + u * UW, v);
+                for (int u = group; u < C / 32; u += 2) {  // 32-column units alternate between the two groups
+                    uint32_t v[32];
+                    ptx::tmem_ld_32x32b_x32(taddr_lane + u * 32, v);
                     ptx::tmem_ld_wait();
-                    const int col = u * UW;
-                    const uint32_t sc = sb_sa + col * 4, bi = sb_sa + (C + col) * 4;
-                    const uint32_t dst = a2_sa + (col >> 6) * kABytes + row * 128;
+                    const uint32_t sc = sb_sa + u * 32 * 4, bi = sb_sa + (C + u * 32) * 4;
+                    const uint32_t dst = a2_sa + (u >> 1) * kABytes + row * 128;
 #pragma unroll
-                    for (int jj = 0; jj < UW / 8; ++jj) {  // 8 columns = one 16-byte unit of this thread's row
+                    for (int jj = 0; jj < 4; ++jj) {  // 8 columns = one 16-byte unit of this thread's row
                         const float4 s0 = ptx::lds128f(sc + jj * 32), s1 = ptx::lds128f(sc + jj * 32 + 16);
                         const float4 b0 = ptx::lds128f(bi + jj * 32), b1 = ptx::lds128f(bi + jj * 32 + 16);
                         const uint32_t* vv = &v[jj * 8];
@@ -465,7 +448,7 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                         ov.y = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[2]), s0.z, b0.z), fmaf(__uint_as_float(vv[3]), s0.w, b0.w));
                         ov.z = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[4]), s1.x, b1.x), fmaf(__uint_as_float(vv[5]), s1.y, b1.y));
                         ov.w = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[6]), s1.z, b1.z), fmaf(__uint_as_float(vv[7]), s1.w, b1.w));
-                        const int unit16 = ((col & 63) >> 3) + jj;
+                        const int unit16 = (u & 1) * 4 + jj;
                         ptx::sts128(dst + ((unit16 ^ (row & 7)) << 4), ov);
                     }
                 }
