@@ -1571,7 +1571,33 @@ int adapt_conv_chain_bf16(int device, const void* in, const void* w2, const floa
     ChainLaunch L;
     rc = build_chain_launch(&L, batch, H, W, C, in, w2, scale1, bias1, w3, scale2, bias2, residual, out, num_sms);
     if (rc) return rc;
-    return run_chain_launch(L, reinterpret_cast<cudaStream_t>(stream));
+    // Developer timeline (tools/chain_trace.py): with ADAPT_TRACE_FILE set (trace build only) the call runs
+    // synchronously and appends the per-CTA, per-unit role timestamps to that file.
+    static const char* trace_file = ADAPT_ENABLE_TRACE ? getenv("ADAPT_TRACE_FILE") : nullptr;
+    if (trace_file == nullptr || trace_file[0] == 0) return run_chain_launch(L, reinterpret_cast<cudaStream_t>(stream));
+    const size_t n_stamps = (size_t)L.grid * adapt::kTraceTiles * adapt::kChainTraceEvents;
+    long long* dtrace = nullptr;
+    CUDA_TRY(cudaMalloc(&dtrace, n_stamps * sizeof(long long)));
+    CUDA_TRY(cudaMemset(dtrace, 0, n_stamps * sizeof(long long)));
+    L.p.trace = dtrace;
+    rc = run_chain_launch(L, reinterpret_cast<cudaStream_t>(stream));
+    if (rc == ADAPT_OK) {
+        std::vector<long long> host(n_stamps);
+        cudaError_t e = cudaStreamSynchronize(reinterpret_cast<cudaStream_t>(stream));
+        if (e == cudaSuccess) e = cudaMemcpy(host.data(), dtrace, n_stamps * sizeof(long long), cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) {
+            rc = fail(ADAPT_ECUDA, "trace read-back: %s", cudaGetErrorString(e));
+        } else if (FILE* f = fopen(trace_file, "a")) {
+            fprintf(f, "{\"kernel\": \"chain\", \"C\": %d, \"grid\": %d, \"m_tiles\": %d, \"stages\": %d, \"ring\": %d, "
+                       "\"tiles\": %d, \"events\": %d, \"stamps\": [",
+                    C, L.grid, L.p.m_tiles, L.p.stages, L.p.ring, adapt::kTraceTiles, adapt::kChainTraceEvents);
+            for (size_t i = 0; i < n_stamps; ++i) fprintf(f, i ? ",%lld" : "%lld", host[i]);
+            fprintf(f, "]}\n");
+            fclose(f);
+        }
+    }
+    cudaFree(dtrace);
+    return rc;
 }
 
 // ---------------------------------------------------------------- classifier head without allocations

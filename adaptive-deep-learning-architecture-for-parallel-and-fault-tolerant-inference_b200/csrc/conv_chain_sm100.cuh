@@ -55,6 +55,24 @@ struct ConvChainParams {
     int ring;             // residual slabs per epilogue warp (2..4)
     int l2_prefetch;      // 1: every epilogue warp pulls its residual rows of the NEXT unit towards L2 while it works
                           // on this one (HBM latency is then hidden by L2, not by the depth of the slab ring)
+    long long* trace;     // developer timeline (nullptr in production): [grid][kTraceTiles][kChainTraceEvents] SM clocks
+};
+
+// Timeline slots of the chain kernel (developer build, tools/chain_trace.py)
+constexpr int kChainTraceEvents = 12;
+enum : int {
+    CT_CTA_START = 0,    // (unit 0 only) kernel entry
+    CT_PROD_FIRST = 1,   // producer: first phase-1 load of the unit issued
+    CT_PROD_LAST = 2,    // producer: last phase-2 weight tile of the unit issued
+    CT_MMA1_FIRST = 3,   // MMA warp: first operand stage of the unit arrived
+    CT_MMA1_DONE = 4,    // MMA warp: acc1 commit issued
+    CT_A2_READY = 5,     // MMA warp: A2 tile complete (every epilogue warp arrived)
+    CT_MMA2_DONE = 6,    // MMA warp: last n-tile's commit issued
+    CT_EPI1_START = 7,   // epilogue warp 0: acc1 ready
+    CT_EPI1_DONE = 8,    // epilogue warp 0: its part of A2 written and announced
+    CT_EPI2_FIRST = 9,   // epilogue warp 0: first acc2 of the unit ready
+    CT_EPI2_DONE = 10,   // epilogue warp 0: last chunk of the unit written out
+    CT_EPI2_G1_DONE = 11,  // epilogue warp 4 (group 1): last chunk of the unit written out
 };
 
 constexpr int kChainBN2 = 128;      // phase-2 n-tile width
@@ -129,6 +147,17 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         return true;
     };
 
+    auto stamp = [&](int unit, int ev) {
+#if ADAPT_ENABLE_TRACE
+        if (p.trace != nullptr && unit < kTraceTiles)
+            p.trace[(static_cast<long long>(blockIdx.x) * kTraceTiles + unit) * kChainTraceEvents + ev] = clock64();
+#else
+        (void)unit;
+        (void)ev;
+#endif
+    };
+    if (threadIdx.x == 0) stamp(0, CT_CTA_START);
+
     if (warp_idx == 0) {
         for (int i = lane; i < kNumBars; i += 32) {
             uint32_t count = 1;
@@ -192,6 +221,7 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             for (int it = 0; it < k_iters; ++it) {
                 ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
                 if (ptx::elect_one()) {
+                    if (it == 0) stamp(ti, CT_PROD_FIRST);
                     uint8_t* a_dst = smem_a + stage * kRow3ABytes;
                     if (PAIR) {
                         if (cl_rank == 0) ptx::mbar_expect_tx(&full_bar[stage], 2 * (kRow3ABytes + 3 * kB1));
@@ -223,6 +253,7 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             for (int n2 = 0; n2 < n2_tiles; ++n2) {
                 ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
                 if (ptx::elect_one()) {
+                    if (n2 == n2_tiles - 1) stamp(ti, CT_PROD_LAST);
                     uint8_t* w_dst = smem_a + stage * kRow3ABytes;
                     if (PAIR) {
                         if (cl_rank == 0) ptx::mbar_expect_tx(&full_bar[stage], 2 * kW3Tile);
@@ -262,6 +293,7 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             for (int it = 0; it < k_iters; ++it) {
                 ptx::mbar_wait(&full_bar[stage], phase);
                 ptx::tc_fence_after();
+                if (it == 0 && lane == 0) stamp(ti, CT_MMA1_FIRST);
                 if (ptx::elect_one()) {
                     const uint32_t a_base = ptx::smem_u32(smem_a + stage * kRow3ABytes);
 #pragma unroll
@@ -285,6 +317,7 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                         ptx::umma_commit(&empty_bar[stage]);
                         if (it == k_iters - 1) ptx::umma_commit(acc1_full);
                     }
+                    if (it == k_iters - 1) stamp(ti, CT_MMA1_DONE);
                 }
                 __syncwarp();
                 if (++cb == c_blocks) {
@@ -302,6 +335,7 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             else
                 ptx::mbar_wait(a2_full, static_cast<uint32_t>(ti) & 1);
             ptx::tc_fence_after();
+            if (lane == 0) stamp(ti, CT_A2_READY);
             for (int n2 = 0; n2 < n2_tiles; ++n2, ++j) {
                 const uint32_t buf = j & 1, use = j >> 1;
                 ptx::mbar_wait(&acc2_empty[buf], (use & 1) ^ 1);
@@ -329,6 +363,7 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                         ptx::umma_commit(&empty_bar[stage]);
                         ptx::umma_commit(&acc2_full[buf]);
                     }
+                    if (n2 == n2_tiles - 1) stamp(ti, CT_MMA2_DONE);
                 }
                 __syncwarp();
                 if (++stage == kStages) {
@@ -429,6 +464,7 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             // ---- epilogue 1: acc1 -> relu(acc * s + b) -> bf16 -> the A2 operand tile (K-major, 128-byte swizzle)
             ptx::mbar_wait(acc1_full, static_cast<uint32_t>(ti) & 1);
             ptx::tc_fence_after();
+            if (epi_warp == 0 && lane == 0) stamp(ti, CT_EPI1_START);
             {
                 const int row = lane_group * 32 + lane;
 #pragma unroll 1
@@ -460,6 +496,7 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                         ptx::mbar_arrive_remote_release(a2_full, 0);
                     else
                         ptx::mbar_arrive(a2_full);
+                    if (epi_warp == 0) stamp(ti, CT_EPI1_DONE);
                 }
             }
             // ---- epilogue 2: this group's n-tiles
@@ -467,6 +504,7 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             for (int n2 = group; n2 < n2_tiles; n2 += 2, ++uses) {
                 ptx::mbar_wait(&acc2_full[group], uses & 1);
                 ptx::tc_fence_after();
+                if (epi_warp == 0 && lane == 0 && n2 == group) stamp(ti, CT_EPI2_FIRST);
                 const uint32_t taddr = taddr_lane + kAcc2Col + group * kChainBN2;
 #pragma unroll 1
                 for (int c = 0; c < kChainBN2 / kEpiCols; ++c) {
@@ -541,6 +579,7 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                     issue_residual();
                 }
             }
+            if ((epi_warp & 3) == 0 && lane == 0) stamp(ti, epi_warp == 0 ? CT_EPI2_DONE : CT_EPI2_G1_DONE);
         }
     }
 
