@@ -1119,7 +1119,13 @@ int run_steps(adapt_stage* st, const std::vector<Step>& steps, cudaStream_t stre
                 const long long total = (long long)B * o.Ho * o.Wo * (o.Cin / 8);
                 const int threads = 256;
                 const unsigned blocks = (unsigned)((total + threads - 1) / threads);
-                if (st->mode == ADAPT_MODE_BF16)
+                if (st->mode == ADAPT_MODE_BF16 && o.kh == 3 && o.stride == 2 && o.pad == 1) {
+                    // the ResNet stem's pool: 2 x 2 outputs per thread from a shared 5 x 5 window
+                    const long long blocks2 = ((long long)B * ((o.Ho + 1) / 2) * ((o.Wo + 1) / 2) * (o.Cin / 8) + threads - 1) / threads;
+                    adapt::maxpool3x3s2p1_bf16_kernel<<<(unsigned)blocks2, threads, 0, stream>>>(
+                        reinterpret_cast<const __nv_bfloat16*>(s.in), reinterpret_cast<__nv_bfloat16*>(s.out), B, o.H, o.W, o.Cin,
+                        o.Ho, o.Wo);
+                } else if (st->mode == ADAPT_MODE_BF16)
                     adapt::maxpool_zeropad_bf16_kernel<<<blocks, threads, 0, stream>>>(
                         reinterpret_cast<const __nv_bfloat16*>(s.in), reinterpret_cast<__nv_bfloat16*>(s.out), B, o.H,
                         o.W, o.Cin, o.Ho, o.Wo, o.kh, o.stride, o.pad);
@@ -1134,9 +1140,9 @@ int run_steps(adapt_stage* st, const std::vector<Step>& steps, cudaStream_t stre
                 const int threads = 128;
                 const unsigned blocks = (unsigned)((total + threads - 1) / threads);
                 if (st->mode == ADAPT_MODE_BF16)
-                    adapt::global_avgpool_kernel<__nv_bfloat16, __nv_bfloat16><<<blocks, threads, 0, stream>>>(
-                        reinterpret_cast<const __nv_bfloat16*>(s.in), reinterpret_cast<__nv_bfloat16*>(s.out), B,
-                        o.H * o.W, o.Cin);
+                    adapt::global_avgpool_bf16_kernel<<<(unsigned)((total + 63) / 64), 64, 0, stream>>>(
+                        reinterpret_cast<const __nv_bfloat16*>(s.in), reinterpret_cast<__nv_bfloat16*>(s.out), B, o.H * o.W,
+                        o.Cin);
                 else
                     adapt::global_avgpool_kernel<float, float><<<blocks, threads, 0, stream>>>(
                         reinterpret_cast<const float*>(s.in), reinterpret_cast<float*>(s.out), B, o.H * o.W, o.Cin);

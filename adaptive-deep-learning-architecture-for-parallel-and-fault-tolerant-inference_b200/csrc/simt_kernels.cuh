@@ -239,6 +239,93 @@ __global__ void maxpool_zeropad_bf16_kernel(const __nv_bfloat16* __restrict__ in
     *reinterpret_cast<uint4*>(out + ((static_cast<long long>(b) * Ho + po) * Wo + qo) * C + cv * 8) = o;
 }
 
+// The ResNet stem's pool (3x3 / stride 2 / pad 1, even H and W): each thread produces a 2 x 2 block of outputs for 8
+// channels from the 5 x 5 input window they share -- 25 loads instead of 36, column maxima of a row reused by the
+// two horizontally adjacent outputs.  Same packed bf16x2 maximum (exact), same treatment of the padding zeros.
+__global__ void maxpool3x3s2p1_bf16_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, int B, int H,
+                                           int W, int C, int Ho, int Wo) {
+    const int cvecs = C / 8;
+    const int Hb = (Ho + 1) / 2, Wb = (Wo + 1) / 2;
+    const long long total = static_cast<long long>(B) * Hb * Wb * cvecs;
+    const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+    if (i >= total) return;
+    const unsigned per_img = static_cast<unsigned>(Hb * Wb * cvecs);
+    const int b = static_cast<int>(i / per_img);
+    unsigned rem = static_cast<unsigned>(i - static_cast<long long>(b) * per_img);
+    const int cv = static_cast<int>(rem % static_cast<unsigned>(cvecs));
+    rem /= static_cast<unsigned>(cvecs);
+    const int qb = static_cast<int>(rem % static_cast<unsigned>(Wb));
+    const int pb = static_cast<int>(rem / static_cast<unsigned>(Wb));
+    const int po0 = 2 * pb, qo0 = 2 * qb;          // top-left output of this thread's 2 x 2 block
+    const int h0 = 2 * po0 - 1, w0 = 2 * qo0 - 1;  // top-left input of the 5 x 5 window
+    const __nv_bfloat162 neg_inf = __float2bfloat162_rn(-INFINITY);
+    const __nv_bfloat162 zero = __float2bfloat162_rn(0.0f);
+    const __nv_bfloat16* img = in + static_cast<long long>(b) * H * W * C + cv * 8;
+    __nv_bfloat162 acc[2][2][4];
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int c = 0; c < 2; ++c)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) acc[a][c][k] = neg_inf;
+    bool pad_row[2] = {false, false}, pad_col[2] = {false, false};
+#pragma unroll
+    for (int r = 0; r < 5; ++r) {
+        const int hi = h0 + r;
+        const bool row_ok = hi >= 0 && hi < H;
+        if (!row_ok) {  // a padding row: takes part in the windows of the outputs it belongs to as zeros
+            if (r <= 2) pad_row[0] = true;
+            if (r >= 2) pad_row[1] = true;
+            continue;
+        }
+        __nv_bfloat162 left[4], right[4];  // row maxima over columns 0..2 (left output) and 2..4 (right output)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) left[k] = right[k] = neg_inf;
+#pragma unroll
+        for (int t = 0; t < 5; ++t) {
+            const int wi = w0 + t;
+            if (wi < 0 || wi >= W) {
+                if (t <= 2) pad_col[0] = true;
+                if (t >= 2) pad_col[1] = true;
+                continue;
+            }
+            const uint4 v = __ldg(reinterpret_cast<const uint4*>(img + (hi * W + wi) * C));
+            const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (t <= 2) left[k] = __hmax2(left[k], h2[k]);
+                if (t >= 2) right[k] = __hmax2(right[k], h2[k]);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if (r <= 2) {
+                acc[0][0][k] = __hmax2(acc[0][0][k], left[k]);
+                acc[0][1][k] = __hmax2(acc[0][1][k], right[k]);
+            }
+            if (r >= 2) {
+                acc[1][0][k] = __hmax2(acc[1][0][k], left[k]);
+                acc[1][1][k] = __hmax2(acc[1][1][k], right[k]);
+            }
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+        const int po = po0 + a;
+        if (po >= Ho) continue;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            const int qo = qo0 + c;
+            if (qo >= Wo) continue;
+            uint4 o;
+            __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) o2[k] = (pad_row[a] || pad_col[c]) ? __hmax2(acc[a][c][k], zero) : acc[a][c][k];
+            *reinterpret_cast<uint4*>(out + ((static_cast<long long>(b) * Ho + po) * Wo + qo) * C + cv * 8) = o;
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Stand-alone per-channel affine (+ReLU): a BatchNormalization / Activation that a cut separated
 // from its convolution.  scale == nullptr means ReLU only.  8 channels per thread.
@@ -309,6 +396,62 @@ __global__ void global_avgpool_kernel(const TIn* __restrict__ in, TOut* __restri
     for (int j = 0; j < 8; ++j) acc[j] *= inv;
     Vec8<TOut> o;
     o.from_float(acc);
+    o.store(out + static_cast<long long>(b) * C + cv * 8);
+}
+
+// bf16 form used by the stage programs: one thread per (image, 8 channels) as above, but the pixel loop is unrolled by
+// seven with independent accumulators, so that seven 16-byte loads are in flight per thread (HW = 49 for ResNet).
+__global__ void global_avgpool_bf16_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, int B, int HW,
+                                           int C) {
+    const int cvecs = C / 8;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= B * cvecs) return;
+    const int b = i / cvecs;
+    const int cv = i - b * cvecs;
+    constexpr int U = 7;
+    float acc[U][8];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[u][j] = 0.0f;
+    const __nv_bfloat16* base = in + static_cast<long long>(b) * HW * C + cv * 8;
+    int px = 0;
+    for (; px + U <= HW; px += U) {
+        uint4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) v[u] = __ldg(reinterpret_cast<const uint4*>(base + static_cast<long long>(px + u) * C));
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v[u]);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 t = __bfloat1622float2(h[j]);
+                acc[u][2 * j] += t.x;
+                acc[u][2 * j + 1] += t.y;
+            }
+        }
+    }
+    for (; px < HW; ++px) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(base + static_cast<long long>(px) * C));
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float2 t = __bfloat1622float2(h[j]);
+            acc[0][2 * j] += t.x;
+            acc[0][2 * j + 1] += t.y;
+        }
+    }
+    const float inv = 1.0f / static_cast<float>(HW);
+    float f[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        float sum = 0.0f;
+#pragma unroll
+        for (int u = 0; u < U; ++u) sum += acc[u][j];
+        f[j] = sum * inv;
+    }
+    Vec8<__nv_bfloat16> o;
+    o.from_float(f);
     o.store(out + static_cast<long long>(b) * C + cv * 8);
 }
 
