@@ -31,7 +31,7 @@ from . import _native as N
 from .dag_util import PartModel, construct_model, layer_macs
 from .fabric import (G_EPOCH, G_NWORKERS, G_PHASE, G_T0, G_T1, G_TIMING_REQ, KIND_DATA, KIND_FED, KIND_PINNED, KIND_RESIDENT, KIND_STOP,
                      W_ELAPSED_US, W_TIMING_ACK, MAX_WORKERS, PHASE_CONFIGURE, PHASE_INIT,
-                     PHASE_QUIESCE, PHASE_RUN, PHASE_SHUTDOWN, FLAG_BASE_STEP, W_ACK_QUIESCE, W_ACK_READY, W_BUSY_MIN_US, W_BUSY_N, W_BUSY_US, W_PID,
+                     PHASE_QUIESCE, PHASE_RUN, PHASE_SHUTDOWN, FLAG_BASE_STEP, W_ACK_QUIESCE, W_ACK_READY, W_BUSY_MIN_US, W_BUSY_N, W_BUSY_US, W_XFER_BYTES, W_XFER_NS, W_PID,
                      W_KILL, W_LAST_K, W_STATE,
                      ControlRing, CudaBackend, HealthTable, ResultRing, ShmRegion, StateEnum, poison_value)
 from .node import IMAGE_BYTES, OUT_ROW_BYTES, StageWorker, arena_slot_bytes
@@ -239,6 +239,7 @@ class DEFER:
         self.workers: List[StageWorker] = []
         self.models_to_dispatch: List[PartModel] = []
         self.part_at: List[str] = []
+        self.handoff_gbs: List[Optional[float]] = []   # per cut, filled by collect_timing
         self.stats = {"delivered": 0, "replayed": 0, "failovers": 0, "failover_ms": [], "dropped_stale": 0, "rejoins": 0,
                       "stragglers": 0}
         self.latencies_ms: List[float] = []
@@ -681,6 +682,9 @@ class DEFER:
                 raise TimeoutError("stages did not report their timing")
             time.sleep(1e-3)
         self.health.g[G_TIMING_REQ] = 0
+        # copy-engine hand-offs of the window's last micro-batch, one entry per cut (None: stored by the last kernel)
+        self.handoff_gbs = [round(int(self.health.w[w, W_XFER_BYTES]) / int(self.health.w[w, W_XFER_NS]), 1)
+                            if int(self.health.w[w, W_XFER_NS]) > 0 else None for w in self.order[:-1]]
         return [int(self.health.w[w, W_ELAPSED_US]) / 1000.0 for w in self.order]
 
     @property

@@ -149,11 +149,13 @@ _TABLE_BYTES = 8192    # JSON partition table
 G_EPOCH, G_PHASE, G_NWORKERS, G_TABLE_LEN, G_T0, G_T1, G_TIMING_REQ = 0, 1, 2, 3, 4, 5, 6
 # per-worker words
 (W_HEARTBEAT, W_STATE, W_KILL, W_ACK_QUIESCE, W_ACK_READY, W_LAST_K, W_PID, W_DEVICE, W_ERRORS, W_ELAPSED_US,
- W_TIMING_ACK, W_BUSY_US, W_BUSY_N, W_BUSY_MIN_US) = range(14)
+ W_TIMING_ACK, W_BUSY_US, W_BUSY_N, W_BUSY_MIN_US, W_XFER_NS, W_XFER_BYTES) = range(16)
 # W_BUSY_US: moving average of the device time this worker's stage spends per micro-batch (microseconds, this epoch);
 # W_BUSY_N: micro-batches folded into it; W_BUSY_MIN_US: the fastest single micro-batch of the epoch (the stage's own
 # healthy baseline -- kept by the worker, so that it does not depend on when the dispatcher happens to look).
 # Read by the dispatcher's straggler watchdog.
+# W_XFER_NS / W_XFER_BYTES: duration (CUDA events on the transfer stream, waits excluded) and size of the copy-engine
+# hand-off of the last micro-batch of the timing window; 0 for a stage whose last kernel stores into the peer's slot.
 
 
 class HealthTable:

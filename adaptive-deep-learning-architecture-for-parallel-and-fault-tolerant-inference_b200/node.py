@@ -28,7 +28,7 @@ import numpy as np
 from . import _native as N
 from .dag_util import construct_model
 from .fabric import (G_EPOCH, G_PHASE, G_T0, G_T1, G_TIMING_REQ, KIND_DATA, KIND_FED, KIND_PINNED, KIND_RESIDENT, KIND_STOP, PHASE_CONFIGURE, PHASE_QUIESCE, PHASE_RUN,
-                     PHASE_SHUTDOWN, W_ACK_QUIESCE, W_ACK_READY, W_BUSY_MIN_US, W_BUSY_N, W_BUSY_US, W_DEVICE, W_ERRORS, W_ELAPSED_US, W_HEARTBEAT, W_KILL, W_LAST_K, W_PID,
+                     PHASE_SHUTDOWN, W_ACK_QUIESCE, W_ACK_READY, W_BUSY_MIN_US, W_BUSY_N, W_BUSY_US, W_XFER_BYTES, W_XFER_NS, W_DEVICE, W_ERRORS, W_ELAPSED_US, W_HEARTBEAT, W_KILL, W_LAST_K, W_PID,
                      W_TIMING_ACK,
                      ControlRing, CudaBackend, HealthTable, ResultRing, ShmRegion, StateEnum, poison_value)
 
@@ -120,6 +120,8 @@ class StageWorker:
         self._hb_thread: Optional[threading.Thread] = None
         self.launches = 0
         self._timing_events = None
+        self._xfer_events = None
+        self._xfer_timed_bytes = 0
         self._timing_armed = False
         self.handoff_copy = False
         self.rails: List[dict] = []          # ingest rails ever created (other GPUs' PCIe links)
@@ -170,6 +172,7 @@ class StageWorker:
         self.stage_addr = [base, base + stage_bytes]
         if hasattr(b, "event_create"):
             self._timing_events = (b.event_create(), b.event_create())
+            self._xfer_events = (b.event_create(), b.event_create())
         # the whole control segment (flags + result ring) is pinned and mapped into this device
         self.ctl_dev = b.register_host(self.region.addr, self.region.size)
         self.results_dev = self.ctl_dev + self.session["result_off"]
@@ -424,7 +427,13 @@ class StageWorker:
                 b.wait_flag(xs, self.flag(self.wid, F_OUT_READY + s), v_done)
                 if k >= 2:
                     b.wait_flag(xs, self.flag(self.wid, F_OUT_FREE + s), v_prev)  # consumer done with its slot s
+                time_it = timed and j == 0 and k == int(self.health.g[G_T1]) - 1
+                if time_it:
+                    b.event_record(self._xfer_events[0], xs)
                 b.d2d(self.in_buf(self.next_wid, s) + lo, self.out_buf(s) + lo, hi - lo, xs)
+                if time_it:
+                    b.event_record(self._xfer_events[1], xs)
+                    self._xfer_timed_bytes = hi - lo
                 if j > 0:
                     b.write_flag(xs, self.flag(self.wid, F_XFER_PART + 2 * j + s), v_done)
             for j in range(1, n_parts):  # the first stream publishes once every piece has landed
@@ -522,6 +531,15 @@ class StageWorker:
         self.backend.event_sync(self._timing_events[1])
         ms = self.backend.event_elapsed_ms(self._timing_events[0], self._timing_events[1])
         self.health.w[self.wid, W_ELAPSED_US] = int(ms * 1000.0)
+        if self._xfer_timed_bytes:
+            self.backend.event_sync(self._xfer_events[1])
+            xms = self.backend.event_elapsed_ms(self._xfer_events[0], self._xfer_events[1])
+            self.health.w[self.wid, W_XFER_NS] = int(xms * 1e6)
+            self.health.w[self.wid, W_XFER_BYTES] = self._xfer_timed_bytes
+            self._xfer_timed_bytes = 0
+        else:
+            self.health.w[self.wid, W_XFER_NS] = 0
+            self.health.w[self.wid, W_XFER_BYTES] = 0
         self._timing_armed = False
         self.health.w[self.wid, W_TIMING_ACK] = token
 

@@ -351,6 +351,56 @@ def reference_style_ours(model, devices, part_at, np) -> dict:
                      "(reference test/test.py:25-37)"}
 
 
+def replica_comparison(args, model, rank, world, want0, np, torch) -> dict:
+    """SURVEY 8e's comparison line (every rank of a torchrun launch calls this after the pipeline sessions ended):
+    the same N GPUs as R independent replicas of an S-stage pipeline, R x S = N, i.e. what the reference's pure
+    pipeline design costs against data parallelism on this box.  Rank r with r % S == 0 leads a replica: an
+    in-process DEFER session over GPUs r .. r + S - 1 (its own dispatcher, queues and ingest), the other ranks idle.
+    All replicas start their timed window together (barrier); value = R * K * B / the slowest replica's device time."""
+    import torch.distributed as dist
+
+    n, B, K, W = args.gpus, args.batch, args.steps, args.warmup
+    os.environ["ADAPT_MULTIPROCESS"] = "0"    # sessions below are in-process (worker threads), not rendezvous
+    out = {}
+    for S in sorted({1, n // 2}):
+        R = n // S
+        lead = rank % S == 0
+        rec = None
+        if lead:
+            devices = [f"cuda:{rank + i}" for i in range(S)]
+            part_at = part_at_for(model, S, args.cuts)
+            ses = Session(model, devices, part_at, B, args)
+            x = synthetic_batch(np, B, 0)
+            ses.defer.preload_input(x)
+            from adapt_b200.dispatcher import ResidentBatch
+
+            drive(ses.defer, ses.in_q, ses.out_q, [ResidentBatch(B)] * W)
+        dist.barrier()
+        if lead:
+            outs, stage_ms, _ = ses.resident_window(K)
+            pinned = [torch.from_numpy(synthetic_batch(np, B, i)).pin_memory() for i in range(3)]
+        dist.barrier()
+        if lead:
+            e_outs, e_wall, _ = drive_steady(ses.defer, ses.in_q, ses.out_q, [pinned[i % 3] for i in range(W + K)], W)
+            ses.close()
+            rec = {"ms": max(stage_ms), "e2e_wall": e_wall, "part_at": part_at, "last": outs[-1], "e2e_first": e_outs[0]}
+        got = [None] * world
+        dist.all_gather_object(got, rec)
+        if rank == 0:
+            reps = [g for g in got if g is not None]
+            ms = max(g["ms"] for g in reps)
+            wall = max(g["e2e_wall"] for g in reps)
+            bad = sum(0 if (np.array_equal(g["last"], want0) and np.array_equal(g["e2e_first"], want0)) else 1 for g in reps)
+            out[f"{R}x{S}"] = {"replicas": R, "stages": S, "part_at": reps[0]["part_at"], "value": round(R * K * B / (ms / 1e3), 1),
+                               "ms_per_step_slowest_replica": round(ms / K, 4), "e2e": round(R * K * B / wall, 1), "unit": "img/s",
+                               "replicas_with_wrong_values": int(bad)}
+    os.environ.pop("ADAPT_MULTIPROCESS", None)
+    if rank == 0:
+        out["note"] = ("replicas x stages on the same GPUs; the headline `value` is the reference's design (1 x N: one "
+                       "pipeline over all N GPUs); e2e = pinned fp32 host batches per replica, slowest replica's wall clock")
+    return out
+
+
 def run_ours(args) -> int:
     import numpy as np
     import torch
@@ -379,6 +429,8 @@ def run_ours(args) -> int:
 
     if world > 1 and rank > 0:
         Node(model, device=local_rank).run()      # worker role: serves every session of the bench, then returns
+        if not args.no_replica_comparison:
+            replica_comparison(args, model, rank, world, None, np, torch)
         dist.barrier()
         dist.destroy_process_group()
         return 0
@@ -398,6 +450,7 @@ def run_ours(args) -> int:
     torch.cuda.synchronize()
     launches0 = defer.gpu_launches
     outs, stage_ms, wall_resident = main.resident_window(K)
+    handoff_gbs = list(defer.handoff_gbs)
     torch.cuda.synchronize()
     local_launches = defer.gpu_launches - launches0
     ms_total = max(stage_ms)
@@ -548,6 +601,9 @@ def run_ours(args) -> int:
                   "mismatched_micro_batches": int(sum(0 if np.array_equal(o, w8[i % 3]) else 1 for i, o in enumerate(o8))),
                   "input": "raw uint8 RGB (B,224,224,3), caffe preprocess_input fused into the ingest kernel"}
     end_sessions()
+    replicas = None
+    if world > 1 and not args.no_replica_comparison:
+        replicas = replica_comparison(args, model, rank, world, want[0], np, torch)
 
     # ---------------- CPU baseline on a bounded sample (N=1 only) ----------------
     cpu = None
@@ -569,7 +625,10 @@ def run_ours(args) -> int:
         "config": bench_config(n, B, part_at),
         "timing": {"l2": "per-step working set (activations of 53 convolutions x micro-batch, > 5 GB at B=128) far exceeds the "
                          "126 MB L2; input slots alternate", "handoff": "peer stores / copy engines over NVLink + stream memory ops",
-                   "stage_ms_per_step": [round(m / K, 4) for m in stage_ms], "how": "CUDA events per stage stream, max over stages"},
+                   "stage_ms_per_step": [round(m / K, 4) for m in stage_ms], "how": "CUDA events per stage stream, max over stages",
+                   "handoff_gbs": handoff_gbs,
+                   "handoff_gbs_how": "per cut: bytes / CUDA-event time of the copy-engine hand-off of the window's last "
+                                      "micro-batch (waits excluded); null = the last kernel stores straight into the peer's slot"},
         "clocks": clock_info,
         "e2e": {"value": round(e2e_value, 1), "unit": "img/s", "h2d_bytes_per_step": int(x.nbytes),
                 "d2h_bytes_per_step": B * 1000 * 4, "p50_latency_ms": p50_unloaded, "p50_latency_ms_saturated": p50, "p99_latency_ms_saturated": p99,
@@ -585,6 +644,7 @@ def run_ours(args) -> int:
         "cpu_baseline": cpu,
         "failover": failover,
         "baseline_configs": baseline_configs,
+        "replica_comparison": replicas,
         "checks": checks,
     }
     print(json.dumps(line), flush=True)
@@ -612,6 +672,8 @@ def main() -> int:
     ap.add_argument("--no-failover", action="store_true")
     ap.add_argument("--no-uint8-leg", action="store_true", help="skip the extra end-to-end leg with raw uint8 inputs")
     ap.add_argument("--no-baseline-configs", action="store_true", help="skip the sessions that measure BASELINE configs 1-3")
+    ap.add_argument("--no-replica-comparison", action="store_true",
+                    help="torchrun, N>1: skip the R replicas x S stages comparison sessions (SURVEY 8e)")
     ap.add_argument("--dump-ops", default=None, help="write the per-launch timing table (JSON) here")
     args = ap.parse_args()
     if args.warmup < 3:
