@@ -19,12 +19,19 @@
 // B200 -- "illegal instruction" -- both as tiled stores with a negative start column, the way to express a slab that
 // straddles image rows, and as im2col-mode stores over the padded-flat walk.)
 //
-//   warp 0      TMA producer: per unit, the phase-1 stages (A row segments; the three B tiles of a filter row unless
-//               the 3x3's weights are resident), then one stage per phase-2 n-tile (`_3_conv` weights), all through
+//   warp 0      TMA producer: the phase-1 stages of a unit (A row segments; the three B tiles of a filter row unless
+//               the 3x3's weights are resident) and one stage per phase-2 n-tile (`_3_conv` weights), all through
 //               ONE operand ring in the order the MMA warp consumes them
-//   warp 1      MMA issuer (phase 1 into acc1, then phase 2 per 128-column n-tile into acc2[n & 1])
+//   warp 1      MMA issuer (phase 1 into acc1, phase 2 per 128-column n-tile into acc2[n & 1]); in the peer CTA of a
+//               pair it forwards that CTA's "A2 half written" to the leader (one cluster-scope release instead of
+//               one per epilogue warp, each of which would wait for that warp's outstanding global stores)
 //   warps 2..9  epilogue, two groups of four.  Both groups turn acc1 into the A2 tile (32-column units alternate
 //               between the groups); group g then drains acc2[g], i.e. n-tiles g, g+2, ...
+//
+// Order on the tensor pipe:  M1(0) | N[0,1](u)  M1(u+1)  N[2..](u) | ...   (M1 = 3x3 of a unit, N[k] = n-tile k of its
+// 1x1): the next unit's 3x3 runs while the first two n-tiles are drained.  The epilogue warps build the A2 tile of
+// unit u+1 BEFORE their last chunk of unit u, so that the first n-tiles of u+1 are computed while that chunk is
+// written out and no epilogue warp idles on the tensor pipe between units.
 //
 //   C = 64  (conv2): single CTA, N1 = 64; the 3x3's weights (72 KiB) stay resident in shared memory
 //   C = 128 (conv3): CTA pair (tcgen05 cta_group::2, 256 positions per unit), all weights streamed
@@ -59,7 +66,7 @@ struct ConvChainParams {
 };
 
 // Timeline slots of the chain kernel (developer build, tools/chain_trace.py)
-constexpr int kChainTraceEvents = 12;
+constexpr int kChainTraceEvents = 21;
 enum : int {
     CT_CTA_START = 0,    // (unit 0 only) kernel entry
     CT_PROD_FIRST = 1,   // producer: first phase-1 load of the unit issued
@@ -73,6 +80,16 @@ enum : int {
     CT_EPI2_FIRST = 9,   // epilogue warp 0: first acc2 of the unit ready
     CT_EPI2_DONE = 10,   // epilogue warp 0: last chunk of the unit written out
     CT_EPI2_G1_DONE = 11,  // epilogue warp 4 (group 1): last chunk of the unit written out
+    // inside epilogue warp 0's first chunk of the unit
+    CT_C0_START = 12,    // before the TMEM loads
+    CT_C0_TMEM = 13,     // accumulator chunk in registers
+    CT_C0_RES = 14,      // residual slab arrived
+    CT_C0_MATH = 15,     // scale / bias / add / ReLU / pack done, slab rewritten
+    CT_C0_OUT = 16,      // write-out instructions issued
+    CT_C0_END = 17,      // next residual load issued
+    CT_C1_END = 18,      // second chunk finished
+    CT_C0_SYNC = 19,     // warp re-converged after the write-out
+    CT_C0_EXPECT = 20,   // expect-tx of the next residual load posted
 };
 
 constexpr int kChainBN2 = 128;      // phase-2 n-tile width
@@ -129,9 +146,11 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     uint64_t* acc2_full = a2_full + 1;                       // [2]
     uint64_t* acc2_empty = acc2_full + 2;                    // [2]
     uint64_t* w_full = acc2_empty + 2;                       // [1] resident weights
-    uint64_t* res_bar = w_full + 1;                          // [kEpiWarps][kChainMaxRing]
+    uint64_t* a2_free = w_full + 1;                          // [1] the unit's 1x1 has read the A2 tile (MMA commit)
+    uint64_t* a2_local = a2_free + 1;                        // [1] pair, peer CTA: its epilogue warps' A2 arrivals
+    uint64_t* res_bar = a2_local + 1;                        // [kEpiWarps][kChainMaxRing]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + kEpiWarps * kChainMaxRing);
-    constexpr int kNumBars = 2 * kChainMaxStages + 1 + 1 + 2 + 2 + 1 + kEpiWarps * kChainMaxRing;
+    constexpr int kNumBars = 2 * kChainMaxStages + 1 + 1 + 2 + 2 + 1 + 2 + kEpiWarps * kChainMaxRing;
 
     const int warp_idx = __shfl_sync(0xffffffff, threadIdx.x / 32, 0);
     const int lane = threadIdx.x % 32;
@@ -161,7 +180,8 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     if (warp_idx == 0) {
         for (int i = lane; i < kNumBars; i += 32) {
             uint32_t count = 1;
-            if (&bars[i] == a2_full) count = kEpiWarps * CL;                     // every epilogue warp (of both CTAs)
+            if (&bars[i] == a2_full) count = kEpiWarps + (PAIR ? 1 : 0);         // own epilogue warps (+ the peer's forwarder)
+            if (&bars[i] == a2_local) count = kEpiWarps;
             if (&bars[i] == acc2_empty || &bars[i] == acc2_empty + 1) count = 4 * CL;  // the draining group (of both CTAs)
             ptx::mbar_init(&bars[i], count);
         }
@@ -204,13 +224,23 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     }
     ptx::griddep_wait();
 
+    // Schedule (u = unit): the tensor pipe runs  M1(0) | N[0,1](u) M1(u+1) N[2..](u) | ...  -- the next unit's 3x3 sits
+    // between the early and the late n-tiles of this unit's 1x1, so it overlaps the drain of acc2 -- and the epilogue
+    // warps turn acc1(u+1) into the A2 tile BEFORE their last chunk of unit u ("splice"): by the time that chunk is
+    // written out, the first n-tiles of unit u+1 are in acc2 and no epilogue warp waits for the tensor pipe.
+    constexpr int n2_early = 2;  // n-tiles issued before the next unit's phase 1 (one per accumulator buffer)
+
     if (warp_idx == 0) {
-        // ===================== phase-1 producer =====================
+        // ===================== producer: operand stages in the order the MMA warp consumes them =====================
         int stage = 0;
         uint32_t phase = 0;
-        int m_blk_raw = 0;
-        bool m_valid = true;
-        for (int ti = 0; tile_at(ti, m_blk_raw, m_valid); ++ti) {
+        auto advance = [&]() {
+            if (++stage == kStages) {
+                stage = 0;
+                phase ^= 1;
+            }
+        };
+        auto load_phase1 = [&](int ti, int m_blk_raw, bool m_valid) {
             const int m_blk = m_valid ? m_blk_raw : p.m_tiles - 1;
             const int m0 = m_blk * kBlockM;
             const int rest = m0 / p.row_pitch;
@@ -244,100 +274,102 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                     cb = 0;
                     ++tap_r;
                 }
-                if (++stage == kStages) {
-                    stage = 0;
-                    phase ^= 1;
+                advance();
+            }
+        };
+        // one n-tile of the 1x1's weights, in the A slot of a ring stage
+        auto load_w3 = [&](int ti, int n2) {
+            ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+            if (ptx::elect_one()) {
+                if (n2 == n2_tiles - 1) stamp(ti, CT_PROD_LAST);
+                uint8_t* w_dst = smem_a + stage * kRow3ABytes;
+                if (PAIR) {
+                    if (cl_rank == 0) ptx::mbar_expect_tx(&full_bar[stage], 2 * kW3Tile);
+#pragma unroll
+                    for (int kb = 0; kb < c_blocks; ++kb)
+                        ptx::tma_load_2d_pair(w_dst + kb * kB2, &tmap_w3, &full_bar[stage], kb * kBlockK,
+                                              n2 * kChainBN2 + cl_rank * (kChainBN2 / 2));
+                } else {
+                    ptx::mbar_expect_tx(&full_bar[stage], kW3Tile);
+#pragma unroll
+                    for (int kb = 0; kb < c_blocks; ++kb)
+                        ptx::tma_load_2d(w_dst + kb * kB2, &tmap_w3, &full_bar[stage], kb * kBlockK, n2 * kChainBN2);
                 }
             }
-            // phase-2 stages: one n-tile of the 1x1's weights each, in the A slot of the stage
-            for (int n2 = 0; n2 < n2_tiles; ++n2) {
-                ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-                if (ptx::elect_one()) {
-                    if (n2 == n2_tiles - 1) stamp(ti, CT_PROD_LAST);
-                    uint8_t* w_dst = smem_a + stage * kRow3ABytes;
-                    if (PAIR) {
-                        if (cl_rank == 0) ptx::mbar_expect_tx(&full_bar[stage], 2 * kW3Tile);
-#pragma unroll
-                        for (int kb = 0; kb < c_blocks; ++kb)
-                            ptx::tma_load_2d_pair(w_dst + kb * kB2, &tmap_w3, &full_bar[stage], kb * kBlockK,
-                                                  n2 * kChainBN2 + cl_rank * (kChainBN2 / 2));
-                    } else {
-                        ptx::mbar_expect_tx(&full_bar[stage], kW3Tile);
-#pragma unroll
-                        for (int kb = 0; kb < c_blocks; ++kb)
-                            ptx::tma_load_2d(w_dst + kb * kB2, &tmap_w3, &full_bar[stage], kb * kBlockK, n2 * kChainBN2);
-                    }
-                }
-                __syncwarp();
-                if (++stage == kStages) {
-                    stage = 0;
-                    phase ^= 1;
-                }
-            }
+            __syncwarp();
+            advance();
+        };
+        int m_blk = 0, m_next = 0;
+        bool m_valid = true, v_next = true;
+        bool have = tile_at(0, m_blk, m_valid);
+        if (have) load_phase1(0, m_blk, m_valid);
+        for (int ti = 0; have; ++ti) {
+            const bool more = tile_at(ti + 1, m_next, v_next);
+            for (int n2 = 0; n2 < n2_early; ++n2) load_w3(ti, n2);
+            if (more) load_phase1(ti + 1, m_next, v_next);
+            for (int n2 = n2_early; n2 < n2_tiles; ++n2) load_w3(ti, n2);
+            have = more;
         }
     } else if (warp_idx == 1) {
-        // ===================== MMA issuer =====================
-        constexpr uint32_t idesc1 = ptx::make_idesc_bf16_f32(PAIR ? 2 * kBlockM : kBlockM, C);
-        constexpr uint32_t idesc2 = ptx::make_idesc_bf16_f32(PAIR ? 2 * kBlockM : kBlockM, kChainBN2);
-        int stage = 0;
-        uint32_t phase = 0;
-        int m_blk = 0;
-        bool m_valid = true;
-        uint32_t j = 0;
-        if (RESIDENT) ptx::mbar_wait(w_full, 0);
-        for (int ti = 0; !(PAIR && cl_rank != 0) && tile_at(ti, m_blk, m_valid); ++ti) {
-            // ---- phase 1: acc1 = im2col(x) . W2^T   (acc1 is free: the A2 tile of the previous unit was complete,
-            // i.e. acc1 fully read, before that unit's phase 2 was issued)
-            ptx::tc_fence_after();
-            int tap_r = 0, cb = 0;
-            for (int it = 0; it < k_iters; ++it) {
-                ptx::mbar_wait(&full_bar[stage], phase);
-                ptx::tc_fence_after();
-                if (it == 0 && lane == 0) stamp(ti, CT_MMA1_FIRST);
-                if (ptx::elect_one()) {
-                    const uint32_t a_base = ptx::smem_u32(smem_a + stage * kRow3ABytes);
-#pragma unroll
-                    for (int s3 = 0; s3 < 3; ++s3) {
-                        const int kbi = (tap_r * 3 + s3) * c_blocks + cb;
-                        const uint64_t a_desc = ptx::make_kmajor_sw128_desc(a_base + s3 * (kBlockK * 2));
-                        const uint64_t b_desc =
-                            ptx::make_kmajor_sw128_desc(ptx::smem_u32(smem_b1 + (RESIDENT ? kbi : stage * 3 + s3) * kB1));
-#pragma unroll
-                        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-                            if (PAIR)
-                                ptx::umma_bf16_ss_pair(tmem_base, a_desc + 2 * k, b_desc + 2 * k, idesc1, (it | s3 | k) != 0 ? 1u : 0u);
-                            else
-                                ptx::umma_bf16_ss(tmem_base, a_desc + 2 * k, b_desc + 2 * k, idesc1, (it | s3 | k) != 0 ? 1u : 0u);
-                        }
-                    }
-                    if (PAIR) {
-                        ptx::umma_commit_pair(&empty_bar[stage], kClusterMask);
-                        if (it == k_iters - 1) ptx::umma_commit_pair(acc1_full, kClusterMask);
-                    } else {
-                        ptx::umma_commit(&empty_bar[stage]);
-                        if (it == k_iters - 1) ptx::umma_commit(acc1_full);
-                    }
-                    if (it == k_iters - 1) stamp(ti, CT_MMA1_DONE);
-                }
-                __syncwarp();
-                if (++cb == c_blocks) {
-                    cb = 0;
-                    ++tap_r;
-                }
+        if (!(PAIR && cl_rank != 0)) {
+            // ===================== MMA issuer =====================
+            constexpr uint32_t idesc1 = ptx::make_idesc_bf16_f32(PAIR ? 2 * kBlockM : kBlockM, C);
+            constexpr uint32_t idesc2 = ptx::make_idesc_bf16_f32(PAIR ? 2 * kBlockM : kBlockM, kChainBN2);
+            int stage = 0;
+            uint32_t phase = 0;
+            auto advance = [&]() {
                 if (++stage == kStages) {
                     stage = 0;
                     phase ^= 1;
                 }
-            }
-            // ---- phase 2: acc2[n & 1] = A2 . W3[n]^T for every 128-column n-tile
-            if (PAIR)
-                ptx::mbar_wait_cluster(a2_full, static_cast<uint32_t>(ti) & 1);  // the peer CTA's warps arrive too
-            else
-                ptx::mbar_wait(a2_full, static_cast<uint32_t>(ti) & 1);
-            ptx::tc_fence_after();
-            if (lane == 0) stamp(ti, CT_A2_READY);
-            for (int n2 = 0; n2 < n2_tiles; ++n2, ++j) {
+            };
+            // acc1 = im2col(x) . W2^T.  acc1 is free: the A2 tile of the previous unit was complete, i.e. acc1 fully
+            // read, before that unit's phase 2 was issued.
+            auto mma_phase1 = [&](int ti) {
+                ptx::tc_fence_after();
+                int tap_r = 0, cb = 0;
+                for (int it = 0; it < k_iters; ++it) {
+                    ptx::mbar_wait(&full_bar[stage], phase);
+                    ptx::tc_fence_after();
+                    if (it == 0 && lane == 0) stamp(ti, CT_MMA1_FIRST);
+                    if (ptx::elect_one()) {
+                        const uint32_t a_base = ptx::smem_u32(smem_a + stage * kRow3ABytes);
+#pragma unroll
+                        for (int s3 = 0; s3 < 3; ++s3) {
+                            const int kbi = (tap_r * 3 + s3) * c_blocks + cb;
+                            const uint64_t a_desc = ptx::make_kmajor_sw128_desc(a_base + s3 * (kBlockK * 2));
+                            const uint64_t b_desc =
+                                ptx::make_kmajor_sw128_desc(ptx::smem_u32(smem_b1 + (RESIDENT ? kbi : stage * 3 + s3) * kB1));
+#pragma unroll
+                            for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+                                if (PAIR)
+                                    ptx::umma_bf16_ss_pair(tmem_base, a_desc + 2 * k, b_desc + 2 * k, idesc1, (it | s3 | k) != 0 ? 1u : 0u);
+                                else
+                                    ptx::umma_bf16_ss(tmem_base, a_desc + 2 * k, b_desc + 2 * k, idesc1, (it | s3 | k) != 0 ? 1u : 0u);
+                            }
+                        }
+                        if (PAIR) {
+                            ptx::umma_commit_pair(&empty_bar[stage], kClusterMask);
+                            if (it == k_iters - 1) ptx::umma_commit_pair(acc1_full, kClusterMask);
+                        } else {
+                            ptx::umma_commit(&empty_bar[stage]);
+                            if (it == k_iters - 1) ptx::umma_commit(acc1_full);
+                        }
+                        if (it == k_iters - 1) stamp(ti, CT_MMA1_DONE);
+                    }
+                    __syncwarp();
+                    if (++cb == c_blocks) {
+                        cb = 0;
+                        ++tap_r;
+                    }
+                    advance();
+                }
+            };
+            // acc2[j & 1] = A2 . W3[n2]^T (j counts n-tiles over the whole kernel)
+            uint32_t j = 0;
+            auto mma_ntile = [&](int ti, int n2) {
                 const uint32_t buf = j & 1, use = j >> 1;
+                ++j;
                 ptx::mbar_wait(&acc2_empty[buf], (use & 1) ^ 1);
                 ptx::mbar_wait(&full_bar[stage], phase);
                 ptx::tc_fence_after();
@@ -359,17 +391,47 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                     if (PAIR) {
                         ptx::umma_commit_pair(&empty_bar[stage], kClusterMask);
                         ptx::umma_commit_pair(&acc2_full[buf], kClusterMask);
+                        if (n2 == n2_tiles - 1) ptx::umma_commit_pair(a2_free, kClusterMask);  // A2 of this unit fully read
                     } else {
                         ptx::umma_commit(&empty_bar[stage]);
                         ptx::umma_commit(&acc2_full[buf]);
+                        if (n2 == n2_tiles - 1) ptx::umma_commit(a2_free);
                     }
                     if (n2 == n2_tiles - 1) stamp(ti, CT_MMA2_DONE);
                 }
                 __syncwarp();
-                if (++stage == kStages) {
-                    stage = 0;
-                    phase ^= 1;
-                }
+                advance();
+            };
+            int m_blk = 0;
+            bool m_valid = true;
+            if (RESIDENT) ptx::mbar_wait(w_full, 0);
+            bool have = tile_at(0, m_blk, m_valid);
+            if (have) mma_phase1(0);
+            for (int ti = 0; have; ++ti) {
+                const bool more = tile_at(ti + 1, m_blk, m_valid);
+                if (PAIR)
+                    ptx::mbar_wait_cluster(a2_full, static_cast<uint32_t>(ti) & 1);  // (the peer CTA's arrival is forwarded)
+                else
+                    ptx::mbar_wait(a2_full, static_cast<uint32_t>(ti) & 1);
+                ptx::tc_fence_after();
+                if (lane == 0) stamp(ti, CT_A2_READY);
+                for (int n2 = 0; n2 < n2_early; ++n2) mma_ntile(ti, n2);
+                if (more) mma_phase1(ti + 1);
+                for (int n2 = n2_early; n2 < n2_tiles; ++n2) mma_ntile(ti, n2);
+                have = more;
+            }
+        } else {
+            // ===================== peer CTA of a pair: forward "my half of the A2 tile is written" =====================
+            // The eight epilogue warps of this CTA arrive on a LOCAL barrier (release at CTA scope: cheap); this
+            // otherwise idle warp acquires that and performs the ONE cluster-scope release towards the leader's
+            // barrier.  (A release at cluster scope from every epilogue warp costs each of them a MEMBAR.GPU that
+            // waits for the global stores of their previous chunk.)
+            int m_blk = 0;
+            bool m_valid = true;
+            for (int ti = 0; tile_at(ti, m_blk, m_valid); ++ti) {
+                ptx::mbar_wait(a2_local, static_cast<uint32_t>(ti) & 1);
+                if (lane == 0) ptx::mbar_arrive_remote_release(a2_full, 0);
+                __syncwarp();
             }
         }
     } else if (warp_idx < 2 + kEpiWarps) {
@@ -403,9 +465,10 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                 ri_live = mv && m0 < p.M;
             }
         };
-        auto issue_residual = [&]() {
+        auto issue_residual = [&](int st_unit) {
             if (ri_live && lane == 0) {
                 ptx::mbar_expect_tx(&my_res_bar[ri_slot], kEpiSlabBytes);
+                if (st_unit >= 0) stamp(st_unit, CT_C0_EXPECT);
                 ptx::tma_load_im2col_4d(my_slabs + ri_slot * kEpiSlabBytes, &tmap_res, &my_res_bar[ri_slot],
                                         ri_n2 * kChainBN2 + ri_c * kEpiCols, ri_q, ri_p, ri_img, 0, 0);
             }
@@ -421,12 +484,59 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             }
         };
         ri_locate();
-        for (uint32_t i = 0; i + 1 < ring; ++i) issue_residual();  // prime: ring - 1 chunks in flight
+        // prime every slot: a chunk's write-out is synchronous (st.global from the slab), so at the end of chunk c its
+        // slot is free and takes the load of chunk c + ring
+        for (uint32_t i = 0; i < ring; ++i) issue_residual(-1);
 
-        int m_blk = 0;
-        bool m_valid = true;
+        // ---- epilogue 1 of unit `ti`: acc1 -> relu(acc * s + b) -> bf16 -> the A2 operand tile (K-major, 128-byte swizzle)
+        auto epilogue1 = [&](int ti) {
+            if (ti > 0) {
+                ptx::mbar_wait(a2_free, static_cast<uint32_t>(ti - 1) & 1);  // the previous unit's 1x1 has read the tile
+            }
+            ptx::mbar_wait(acc1_full, static_cast<uint32_t>(ti) & 1);
+            ptx::tc_fence_after();
+            if (epi_warp == 0 && lane == 0) stamp(ti, CT_EPI1_START);
+            const int row = lane_group * 32 + lane;
+#pragma unroll 1
+            for (int u = group; u < C / 32; u += 2) {  // 32-column units alternate between the two groups
+                uint32_t v[32];
+                ptx::tmem_ld_32x32b_x32(taddr_lane + u * 32, v);
+                ptx::tmem_ld_wait();
+                const uint32_t sc = sb_sa + u * 32 * 4, bi = sb_sa + (C + u * 32) * 4;
+                const uint32_t dst = a2_sa + (u >> 1) * kABytes + row * 128;
+#pragma unroll
+                for (int jj = 0; jj < 4; ++jj) {  // 8 columns = one 16-byte unit of this thread's row
+                    const float4 s0 = ptx::lds128f(sc + jj * 32), s1 = ptx::lds128f(sc + jj * 32 + 16);
+                    const float4 b0 = ptx::lds128f(bi + jj * 32), b1 = ptx::lds128f(bi + jj * 32 + 16);
+                    const uint32_t* vv = &v[jj * 8];
+                    uint4 ov;
+                    ov.x = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[0]), s0.x, b0.x), fmaf(__uint_as_float(vv[1]), s0.y, b0.y));
+                    ov.y = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[2]), s0.z, b0.z), fmaf(__uint_as_float(vv[3]), s0.w, b0.w));
+                    ov.z = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[4]), s1.x, b1.x), fmaf(__uint_as_float(vv[5]), s1.y, b1.y));
+                    ov.w = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[6]), s1.z, b1.z), fmaf(__uint_as_float(vv[7]), s1.w, b1.w));
+                    const int unit16 = (u & 1) * 4 + jj;
+                    ptx::sts128(dst + ((unit16 ^ (row & 7)) << 4), ov);
+                }
+            }
+            ptx::fence_proxy_async_smem();  // generic-proxy writes -> visible to the tensor core's reads
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                if (PAIR && cl_rank != 0)
+                    ptx::mbar_arrive(a2_local);  // forwarded to the leader by this CTA's warp 1
+                else
+                    ptx::mbar_arrive(a2_full);
+                if (epi_warp == 0) stamp(ti, CT_EPI1_DONE);
+            }
+        };
+
+        int m_blk = 0, m_next = 0;
+        bool m_valid = true, v_next = true;
         uint32_t uses = 0;  // n-tiles this group has drained so far (accumulator phase)
-        for (int ti = 0; tile_at(ti, m_blk, m_valid); ++ti) {
+        bool have = tile_at(0, m_blk, m_valid);
+        if (have) epilogue1(0);
+        for (int ti = 0; have; ++ti) {
+            const bool more = tile_at(ti + 1, m_next, v_next);
             const int m_row0 = m_blk * kBlockM + lane_group * 32;
             const bool slab_ok = m_valid && m_row0 < p.M;
             // write-out offsets, once per unit: lane (8 r + ch) moves 16-byte piece ch of slab rows 4 i + r (i = 0..7);
@@ -448,10 +558,8 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                 }
             }
             if (p.l2_prefetch && lane == 0) {
-                int mb = 0;
-                bool mv = true;
-                if (tile_at(ti + 1, mb, mv) && mv && mb * kBlockM + lane_group * 32 < p.M) {
-                    const int m0 = mb * kBlockM + lane_group * 32;
+                if (more && v_next && m_next * kBlockM + lane_group * 32 < p.M) {
+                    const int m0 = m_next * kBlockM + lane_group * 32;
                     const int rest = m0 / p.row_pitch;
                     const int q = m0 - rest * p.row_pitch;
                     const int img = rest / p.H;
@@ -461,45 +569,7 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                             ptx::tma_prefetch_im2col_4d(&tmap_res, n2 * kChainBN2 + c * kEpiCols, q, pr, img, 0, 0);
                 }
             }
-            // ---- epilogue 1: acc1 -> relu(acc * s + b) -> bf16 -> the A2 operand tile (K-major, 128-byte swizzle)
-            ptx::mbar_wait(acc1_full, static_cast<uint32_t>(ti) & 1);
-            ptx::tc_fence_after();
-            if (epi_warp == 0 && lane == 0) stamp(ti, CT_EPI1_START);
-            {
-                const int row = lane_group * 32 + lane;
-#pragma unroll 1
-                for (int u = group; u < C / 32; u += 2) {  // 32-column units alternate between the two groups
-                    uint32_t v[32];
-                    ptx::tmem_ld_32x32b_x32(taddr_lane + u * 32, v);
-                    ptx::tmem_ld_wait();
-                    const uint32_t sc = sb_sa + u * 32 * 4, bi = sb_sa + (C + u * 32) * 4;
-                    const uint32_t dst = a2_sa + (u >> 1) * kABytes + row * 128;
-#pragma unroll
-                    for (int jj = 0; jj < 4; ++jj) {  // 8 columns = one 16-byte unit of this thread's row
-                        const float4 s0 = ptx::lds128f(sc + jj * 32), s1 = ptx::lds128f(sc + jj * 32 + 16);
-                        const float4 b0 = ptx::lds128f(bi + jj * 32), b1 = ptx::lds128f(bi + jj * 32 + 16);
-                        const uint32_t* vv = &v[jj * 8];
-                        uint4 ov;
-                        ov.x = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[0]), s0.x, b0.x), fmaf(__uint_as_float(vv[1]), s0.y, b0.y));
-                        ov.y = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[2]), s0.z, b0.z), fmaf(__uint_as_float(vv[3]), s0.w, b0.w));
-                        ov.z = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[4]), s1.x, b1.x), fmaf(__uint_as_float(vv[5]), s1.y, b1.y));
-                        ov.w = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[6]), s1.z, b1.z), fmaf(__uint_as_float(vv[7]), s1.w, b1.w));
-                        const int unit16 = (u & 1) * 4 + jj;
-                        ptx::sts128(dst + ((unit16 ^ (row & 7)) << 4), ov);
-                    }
-                }
-                ptx::fence_proxy_async_smem();  // generic-proxy writes -> visible to the tensor core's reads
-                ptx::tc_fence_before();
-                __syncwarp();
-                if (lane == 0) {
-                    if (PAIR)
-                        ptx::mbar_arrive_remote_release(a2_full, 0);
-                    else
-                        ptx::mbar_arrive(a2_full);
-                    if (epi_warp == 0) stamp(ti, CT_EPI1_DONE);
-                }
-            }
-            // ---- epilogue 2: this group's n-tiles
+            // ---- epilogue 2: this group's n-tiles; the next unit's epilogue 1 is spliced in before the last chunk
 #pragma unroll 1
             for (int n2 = group; n2 < n2_tiles; n2 += 2, ++uses) {
                 ptx::mbar_wait(&acc2_full[group], uses & 1);
@@ -508,10 +578,15 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                 const uint32_t taddr = taddr_lane + kAcc2Col + group * kChainBN2;
 #pragma unroll 1
                 for (int c = 0; c < kChainBN2 / kEpiCols; ++c) {
+                    const bool last_chunk = n2 + 2 >= n2_tiles && c == kChainBN2 / kEpiCols - 1;
+                    if (last_chunk && more) epilogue1(ti + 1);
+                    const bool st_c0 = epi_warp == 0 && lane == 0 && n2 == group && c == 0;
+                    if (st_c0) stamp(ti, CT_C0_START);
                     uint32_t v0[32], v1[32];
                     ptx::tmem_ld_32x32b_x32(taddr + c * kEpiCols, v0);
                     ptx::tmem_ld_32x32b_x32(taddr + c * kEpiCols + 32, v1);
                     ptx::tmem_ld_wait();
+                    if (st_c0) stamp(ti, CT_C0_TMEM);
                     if (c == kChainBN2 / kEpiCols - 1) {
                         ptx::tc_fence_before();
                         __syncwarp();
@@ -527,11 +602,12 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                     if (++slot == ring) slot = 0;
                     if (!slab_ok) {
                         __syncwarp();
-                        issue_residual();
+                        issue_residual(-1);
                         continue;
                     }
                     ptx::mbar_wait(&my_res_bar[this_slot], (res_par >> this_slot) & 1);
                     res_par ^= (1u << this_slot);
+                    if (st_c0) stamp(ti, CT_C0_RES);
                     const int col0 = n2 * kChainBN2 + c * kEpiCols;
                     const uint32_t sc = sb_sa + (2 * C + col0) * 4, bi = sb_sa + (2 * C + 4 * C + col0) * 4;
 #pragma unroll
@@ -564,22 +640,34 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                         ptx::sts128(slab + sw, ov);
                     }
                     __syncwarp();
+                    if (st_c0) stamp(ti, CT_C0_MATH);
                     {
-                        // coalesced write-out: 8 lanes cover one 128-byte row segment, 4 rows per instruction
+                        // coalesced write-out: 8 lanes cover one 128-byte row segment, 4 rows per instruction (all
+                        // loads first: a store behind each load serialises on the shared-memory latency)
                         const int ch = lane & 7;
                         __nv_bfloat16* gcol = p.out + col0;
+                        uint4 val[8];
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
                             const int row = i * 4 + (lane >> 3);
-                            const uint4 val = ptx::lds128(slab + row * 128 + ((ch ^ (row & 7)) << 4));
-                            if (out_off[i] >= 0) *reinterpret_cast<uint4*>(gcol + out_off[i]) = val;
+                            val[i] = ptx::lds128(slab + row * 128 + ((ch ^ (row & 7)) << 4));
                         }
+#pragma unroll
+                        for (int i = 0; i < 8; ++i)
+                            if (out_off[i] >= 0) *reinterpret_cast<uint4*>(gcol + out_off[i]) = val[i];
                     }
+                    if (st_c0) stamp(ti, CT_C0_OUT);
                     __syncwarp();
-                    issue_residual();
+                    if (st_c0) stamp(ti, CT_C0_SYNC);
+                    issue_residual(st_c0 ? ti : -1);
+                    if (st_c0) stamp(ti, CT_C0_END);
+                    if (epi_warp == 0 && lane == 0 && n2 == group && c == 1) stamp(ti, CT_C1_END);
                 }
             }
             if ((epi_warp & 3) == 0 && lane == 0) stamp(ti, epi_warp == 0 ? CT_EPI2_DONE : CT_EPI2_G1_DONE);
+            have = more;
+            m_blk = m_next;
+            m_valid = v_next;
         }
     }
 

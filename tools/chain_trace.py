@@ -31,7 +31,7 @@ for C in (64, 128):
         N.check(lib.adapt_conv_chain_bf16(0, x.data_ptr(), w2.data_ptr(), s1.data_ptr(), b1.data_ptr(), w3.data_ptr(), s2.data_ptr(),
                                           b2.data_ptr(), res.data_ptr(), out.data_ptr(), B, H, W, C, None))
     torch.cuda.synchronize()
-EV = dict(cta=0, p0=1, p1=2, m1f=3, m1d=4, a2=5, m2d=6, e1s=7, e1d=8, e2f=9, e2d=10, e2g1=11)
+EV = dict(cta=0, p0=1, p1=2, m1f=3, m1d=4, a2=5, m2d=6, e1s=7, e1d=8, e2f=9, e2d=10, e2g1=11, c0s=12, c0t=13, c0r=14, c0m=15, c0o=16, c0e=17, c1e=18, c0y=19, c0x=20)
 for line in list(open(tf.name))[1::2]:   # second (warm) launch of each geometry
     r = json.loads(line)
     T, E, G, s = r["tiles"], r["events"], r["grid"], r["stamps"]
@@ -52,17 +52,24 @@ for line in list(open(tf.name))[1::2]:   # second (warm) launch of each geometry
         add("first_load_to_data", at(c, 0, "m1f") - at(c, 0, "p0"))
         for t in range(n):
             add("mma1_issue", at(c, t, "m1d") - at(c, t, "m1f"))
-            add("mma1_done_to_epi1_start", at(c, t, "e1s") - at(c, t, "m1d"))
+            add("mma1_done_to_epi1_start", at(c, t, "e1s") - at(c, t, "m1d"))   # (epilogue 1 of unit t runs inside unit t-1's drain)
             add("epi1", at(c, t, "e1d") - at(c, t, "e1s"))
             add("epi1_done_to_a2_ready", at(c, t, "a2") - at(c, t, "e1d"))
             add("mma2_issue", at(c, t, "m2d") - at(c, t, "a2"))
             add("a2_ready_to_epi2_first", at(c, t, "e2f") - at(c, t, "a2"))
             add("epi2_g0", at(c, t, "e2d") - at(c, t, "e2f"))
+            add("chunk0_tmem_ld", at(c, t, "c0t") - at(c, t, "c0s"))
+            add("chunk0_residual_wait", at(c, t, "c0r") - at(c, t, "c0t"))
+            add("chunk0_math", at(c, t, "c0m") - at(c, t, "c0r"))
+            add("chunk0_write_out", at(c, t, "c0o") - at(c, t, "c0m"))
+            add("chunk0_syncwarp", at(c, t, "c0y") - at(c, t, "c0o"))
+            add("chunk0_expect_tx", at(c, t, "c0x") - at(c, t, "c0y"))
+            add("chunk0_tma_issue", at(c, t, "c0e") - at(c, t, "c0x"))
+            add("chunk1_total", at(c, t, "c1e") - at(c, t, "c0e"))
             add("epi2_g1_end_after_g0", at(c, t, "e2g1") - at(c, t, "e2d"))
             if t:
                 add("unit_period", at(c, t, "e2d") - at(c, t - 1, "e2d"))
-                add("mma1_start_after_prev_mma2", at(c, t, "m1f") - at(c, t - 1, "m2d"))
-                add("epi1_start_after_prev_epi2_done", at(c, t, "e1s") - at(c, t - 1, "e2d"))
+                add("epi1_start_before_prev_epi2_done", at(c, t - 1, "e2d") - at(c, t, "e1s"))
         spans.append(max(at(c, n - 1, "e2d"), at(c, n - 1, "e2g1")) - t0)
     print(json.dumps({"C": r["C"], "grid": G, "m_tiles": r["m_tiles"], "stages": r["stages"], "ring": r["ring"],
                       **{k: round(st.median(v)) for k, v in agg.items()}, "span_median": round(st.median(spans)), "span_max": max(spans)}))
