@@ -504,16 +504,21 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                 ptx::tmem_ld_wait();
                 const uint32_t sc = sb_sa + u * 32 * 4, bi = sb_sa + (C + u * 32) * 4;
                 const uint32_t dst = a2_sa + (u >> 1) * kABytes + row * 128;
+                float4 s0 = ptx::lds128f(sc), s1 = ptx::lds128f(sc + 16);
+                float4 b0 = ptx::lds128f(bi), b1 = ptx::lds128f(bi + 16);
 #pragma unroll
                 for (int jj = 0; jj < 4; ++jj) {  // 8 columns = one 16-byte unit of this thread's row
-                    const float4 s0 = ptx::lds128f(sc + jj * 32), s1 = ptx::lds128f(sc + jj * 32 + 16);
-                    const float4 b0 = ptx::lds128f(bi + jj * 32), b1 = ptx::lds128f(bi + jj * 32 + 16);
+                    const float4 cs0 = s0, cs1 = s1, cb0 = b0, cb1 = b1;
+                    if (jj < 3) {  // next piece's constants before this piece's arithmetic
+                        s0 = ptx::lds128f(sc + (jj + 1) * 32), s1 = ptx::lds128f(sc + (jj + 1) * 32 + 16);
+                        b0 = ptx::lds128f(bi + (jj + 1) * 32), b1 = ptx::lds128f(bi + (jj + 1) * 32 + 16);
+                    }
                     const uint32_t* vv = &v[jj * 8];
                     uint4 ov;
-                    ov.x = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[0]), s0.x, b0.x), fmaf(__uint_as_float(vv[1]), s0.y, b0.y));
-                    ov.y = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[2]), s0.z, b0.z), fmaf(__uint_as_float(vv[3]), s0.w, b0.w));
-                    ov.z = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[4]), s1.x, b1.x), fmaf(__uint_as_float(vv[5]), s1.y, b1.y));
-                    ov.w = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[6]), s1.z, b1.z), fmaf(__uint_as_float(vv[7]), s1.w, b1.w));
+                    ov.x = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[0]), cs0.x, cb0.x), fmaf(__uint_as_float(vv[1]), cs0.y, cb0.y));
+                    ov.y = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[2]), cs0.z, cb0.z), fmaf(__uint_as_float(vv[3]), cs0.w, cb0.w));
+                    ov.z = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[4]), cs1.x, cb1.x), fmaf(__uint_as_float(vv[5]), cs1.y, cb1.y));
+                    ov.w = ptx::pack_bf16x2_relu(fmaf(__uint_as_float(vv[6]), cs1.z, cb1.z), fmaf(__uint_as_float(vv[7]), cs1.w, cb1.w));
                     const int unit16 = (u & 1) * 4 + jj;
                     ptx::sts128(dst + ((unit16 ^ (row & 7)) << 4), ov);
                 }
@@ -610,23 +615,31 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                     if (st_c0) stamp(ti, CT_C0_RES);
                     const int col0 = n2 * kChainBN2 + c * kEpiCols;
                     const uint32_t sc = sb_sa + (2 * C + col0) * 4, bi = sb_sa + (2 * C + 4 * C + col0) * 4;
+                    // (the loads of 16-byte piece jj + 1 -- constants and shortcut -- are issued before the arithmetic of
+                    // piece jj: the shared-memory accesses are ordered asm statements, the compiler cannot hoist them)
+                    float4 s0 = ptx::lds128f(sc), s1 = ptx::lds128f(sc + 16);
+                    float4 b0 = ptx::lds128f(bi), b1 = ptx::lds128f(bi + 16);
+                    uint4 rv = ptx::lds128(slab + ((0 ^ (lane & 7)) << 4) + lane * 128);
 #pragma unroll
                     for (int jj = 0; jj < 8; ++jj) {
                         const uint32_t* vv = (jj < 4) ? &v0[jj * 8] : &v1[(jj - 4) * 8];
-                        const float4 s0 = ptx::lds128f(sc + jj * 32), s1 = ptx::lds128f(sc + jj * 32 + 16);
-                        const float4 b0 = ptx::lds128f(bi + jj * 32), b1 = ptx::lds128f(bi + jj * 32 + 16);
-                        float y[8];
-                        y[0] = fmaf(__uint_as_float(vv[0]), s0.x, b0.x);
-                        y[1] = fmaf(__uint_as_float(vv[1]), s0.y, b0.y);
-                        y[2] = fmaf(__uint_as_float(vv[2]), s0.z, b0.z);
-                        y[3] = fmaf(__uint_as_float(vv[3]), s0.w, b0.w);
-                        y[4] = fmaf(__uint_as_float(vv[4]), s1.x, b1.x);
-                        y[5] = fmaf(__uint_as_float(vv[5]), s1.y, b1.y);
-                        y[6] = fmaf(__uint_as_float(vv[6]), s1.z, b1.z);
-                        y[7] = fmaf(__uint_as_float(vv[7]), s1.w, b1.w);
-                        const uint32_t sw = ((jj ^ (lane & 7)) << 4) + lane * 128;
-                        const uint4 rv = ptx::lds128(slab + sw);
+                        const float4 cs0 = s0, cs1 = s1, cb0 = b0, cb1 = b1;
                         const uint32_t r[4] = {rv.x, rv.y, rv.z, rv.w};
+                        const uint32_t sw = ((jj ^ (lane & 7)) << 4) + lane * 128;
+                        if (jj < 7) {
+                            s0 = ptx::lds128f(sc + (jj + 1) * 32), s1 = ptx::lds128f(sc + (jj + 1) * 32 + 16);
+                            b0 = ptx::lds128f(bi + (jj + 1) * 32), b1 = ptx::lds128f(bi + (jj + 1) * 32 + 16);
+                            rv = ptx::lds128(slab + (((jj + 1) ^ (lane & 7)) << 4) + lane * 128);
+                        }
+                        float y[8];
+                        y[0] = fmaf(__uint_as_float(vv[0]), cs0.x, cb0.x);
+                        y[1] = fmaf(__uint_as_float(vv[1]), cs0.y, cb0.y);
+                        y[2] = fmaf(__uint_as_float(vv[2]), cs0.z, cb0.z);
+                        y[3] = fmaf(__uint_as_float(vv[3]), cs0.w, cb0.w);
+                        y[4] = fmaf(__uint_as_float(vv[4]), cs1.x, cb1.x);
+                        y[5] = fmaf(__uint_as_float(vv[5]), cs1.y, cb1.y);
+                        y[6] = fmaf(__uint_as_float(vv[6]), cs1.z, cb1.z);
+                        y[7] = fmaf(__uint_as_float(vv[7]), cs1.w, cb1.w);
 #pragma unroll
                         for (int e = 0; e < 4; ++e) {
                             y[2 * e] += __uint_as_float(r[e] << 16);

@@ -700,24 +700,33 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     const uint32_t bi = bias_sa + (S2DP ? 0 : c * kEpiCols * 4);
                     auto drain = [&](auto relu_tag) {
                         constexpr bool kRelu = decltype(relu_tag)::value;
+                        // (the shared-memory loads of piece j + 1 -- constants and shortcut -- are issued before the
+                        // arithmetic of piece j: they are ordered asm statements, the compiler cannot hoist them)
+                        float4 s0 = ptx::lds128f(sc), s1 = ptx::lds128f(sc + 16);
+                        float4 b0 = ptx::lds128f(bi), b1 = ptx::lds128f(bi + 16);
+                        uint4 rv = make_uint4(0u, 0u, 0u, 0u);
+                        if (has_res) rv = ptx::lds128(slab + ((0 ^ (lane & 7)) << 4) + lane * 128);
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {  // 8 columns = one 16-byte unit of this thread's row
                             const uint32_t* vv = (j < 4) ? &v0[j * 8] : &v1[(j - 4) * 8];
-                            const float4 s0 = ptx::lds128f(sc + j * 32), s1 = ptx::lds128f(sc + j * 32 + 16);
-                            const float4 b0 = ptx::lds128f(bi + j * 32), b1 = ptx::lds128f(bi + j * 32 + 16);
-                            float y[8];
-                            y[0] = fmaf(__uint_as_float(vv[0]), s0.x, b0.x);
-                            y[1] = fmaf(__uint_as_float(vv[1]), s0.y, b0.y);
-                            y[2] = fmaf(__uint_as_float(vv[2]), s0.z, b0.z);
-                            y[3] = fmaf(__uint_as_float(vv[3]), s0.w, b0.w);
-                            y[4] = fmaf(__uint_as_float(vv[4]), s1.x, b1.x);
-                            y[5] = fmaf(__uint_as_float(vv[5]), s1.y, b1.y);
-                            y[6] = fmaf(__uint_as_float(vv[6]), s1.z, b1.z);
-                            y[7] = fmaf(__uint_as_float(vv[7]), s1.w, b1.w);
+                            const float4 cs0 = s0, cs1 = s1, cb0 = b0, cb1 = b1;
+                            const uint32_t r[4] = {rv.x, rv.y, rv.z, rv.w};
                             const uint32_t sw = ((j ^ (lane & 7)) << 4) + lane * 128;
+                            if (j < 7) {
+                                s0 = ptx::lds128f(sc + (j + 1) * 32), s1 = ptx::lds128f(sc + (j + 1) * 32 + 16);
+                                b0 = ptx::lds128f(bi + (j + 1) * 32), b1 = ptx::lds128f(bi + (j + 1) * 32 + 16);
+                                if (has_res) rv = ptx::lds128(slab + (((j + 1) ^ (lane & 7)) << 4) + lane * 128);
+                            }
+                            float y[8];
+                            y[0] = fmaf(__uint_as_float(vv[0]), cs0.x, cb0.x);
+                            y[1] = fmaf(__uint_as_float(vv[1]), cs0.y, cb0.y);
+                            y[2] = fmaf(__uint_as_float(vv[2]), cs0.z, cb0.z);
+                            y[3] = fmaf(__uint_as_float(vv[3]), cs0.w, cb0.w);
+                            y[4] = fmaf(__uint_as_float(vv[4]), cs1.x, cb1.x);
+                            y[5] = fmaf(__uint_as_float(vv[5]), cs1.y, cb1.y);
+                            y[6] = fmaf(__uint_as_float(vv[6]), cs1.z, cb1.z);
+                            y[7] = fmaf(__uint_as_float(vv[7]), cs1.w, cb1.w);
                             if (has_res) {
-                                const uint4 rv = ptx::lds128(slab + sw);
-                                const uint32_t r[4] = {rv.x, rv.y, rv.z, rv.w};
 #pragma unroll
                                 for (int e = 0; e < 4; ++e) {  // bf16 pair -> two fp32: shift / mask, no permute
                                     y[2 * e] += __uint_as_float(r[e] << 16);
