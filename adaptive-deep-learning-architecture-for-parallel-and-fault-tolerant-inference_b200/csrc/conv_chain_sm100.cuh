@@ -587,6 +587,9 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                     if (last_chunk && more) epilogue1(ti + 1);
                     const bool st_c0 = epi_warp == 0 && lane == 0 && n2 == group && c == 0;
                     if (st_c0) stamp(ti, CT_C0_START);
+                    // (the barrier probe takes ~200 cycles to answer even when the load has landed: it is issued
+                    // ahead of the TMEM loads, its answer is looked at after them)
+                    const bool res_landed = slab_ok && ptx::mbar_try_wait(&my_res_bar[slot], (res_par >> slot) & 1);
                     uint32_t v0[32], v1[32];
                     ptx::tmem_ld_32x32b_x32(taddr + c * kEpiCols, v0);
                     ptx::tmem_ld_32x32b_x32(taddr + c * kEpiCols + 32, v1);
@@ -610,7 +613,7 @@ conv_chain_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                         issue_residual(-1);
                         continue;
                     }
-                    ptx::mbar_wait(&my_res_bar[this_slot], (res_par >> this_slot) & 1);
+                    if (!res_landed) ptx::mbar_wait(&my_res_bar[this_slot], (res_par >> this_slot) & 1);
                     res_par ^= (1u << this_slot);
                     if (st_c0) stamp(ti, CT_C0_RES);
                     const int col0 = n2 * kChainBN2 + c * kEpiCols;

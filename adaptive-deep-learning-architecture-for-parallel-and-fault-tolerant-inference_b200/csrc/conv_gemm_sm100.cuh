@@ -660,6 +660,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 if ((epi_warp & 3) == 0 && lane == 0) stamp(tile_iter, TR_EPI_START);
 #pragma unroll 1
                 for (int c = 0; c < kChunks; ++c) {
+                    // (a barrier probe takes ~200 cycles to answer even when the load has landed: issued ahead of the
+                    // TMEM loads, looked at after them)
+                    const bool res_landed = has_res && slab_ok && ptx::mbar_try_wait(&my_res_bar[slot], (res_par >> slot) & 1);
                     uint32_t v0[32], v1[32];
                     ptx::tmem_ld_32x32b_x32(taddr + c * kEpiCols, v0);
                     ptx::tmem_ld_32x32b_x32(taddr + c * kEpiCols + 32, v1);
@@ -689,7 +692,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         continue;
                     }
                     if (has_res) {
-                        ptx::mbar_wait(&my_res_bar[this_slot], (res_par >> this_slot) & 1);
+                        if (!res_landed) ptx::mbar_wait(&my_res_bar[this_slot], (res_par >> this_slot) & 1);
                         res_par ^= (1u << this_slot);
                     } else {
                         // the TMA store issued from this slab `ring` chunks ago must have read it
