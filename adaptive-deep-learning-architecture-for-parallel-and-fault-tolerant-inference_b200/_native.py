@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libadapt_b200.so")
 # mirror of include/adapt_b200.h -------------------------------------------------------------
 OK, EINVAL, ECUDA, ENODEV, ENOMEM, ESTATE = 0, -1, -2, -3, -4, -5
 MODE_BF16, MODE_FP32_CHECK = 0, 1
-OP_INGEST, OP_CONV, OP_MAXPOOL, OP_GAP, OP_SOFTMAX, OP_AFFINE, OP_ZEROPAD, OP_CONV_CHAIN = 0, 1, 2, 3, 4, 5, 6, 7
+OP_INGEST, OP_CONV, OP_MAXPOOL, OP_GAP, OP_SOFTMAX, OP_AFFINE, OP_ZEROPAD, OP_CONV_CHAIN, OP_STEM_POOL = 0, 1, 2, 3, 4, 5, 6, 7, 8
 T_INTERNAL, T_INPUT, T_OUTPUT = 0, 1, 2
 DT_WORK, DT_F32, DT_U8 = 0, 1, 2
 IN_F32, IN_U8_RGB_CAFFE = 0, 1  # INGEST input formats (include/adapt_b200.h)
@@ -84,6 +84,7 @@ SYMBOLS = {
     "adapt_conv2d_bf16": (_I, [_I, _VP, _VP, _VP, _VP, _VP, _VP, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I,
                                _VP]),
     "adapt_conv_chain_bf16": (_I, [_I, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _I, _I, _I, _I, _VP]),
+    "adapt_stem_pool_bf16": (_I, [_I, _VP, _VP, _VP, _VP, _VP, _I, _I, _I, _I, _I, _VP]),
     "adapt_dense_softmax_noalloc": (_I, [_I, _VP, _VP, _VP, _VP, _VP, _I, _I, _I, _VP]),
     "adapt_device_alloc": (_I, [_I, _SZ, C.POINTER(_VP)]),
     "adapt_device_free": (_I, [_I, _VP]),

@@ -23,6 +23,7 @@
 
 #include "conv_gemm_sm100.cuh"
 #include "conv_chain_sm100.cuh"
+#include "stem_pool_sm100.cuh"
 #include "simt_kernels.cuh"
 
 namespace {
@@ -274,6 +275,14 @@ struct ChainLaunch {
     int grid = 0;
 };
 
+// Launch record of the fused stem + max-pool kernel (stem_pool_sm100.cuh).
+struct StemPoolLaunch {
+    CUtensorMap tmap_a, tmap_b;
+    adapt::StemPoolParams p;
+    int smem = 0;
+    int grid = 0;
+};
+
 int g_force_a_mode = -2;  // -2 = read env lazily
 int g_force_block_n = -2;
 
@@ -346,6 +355,7 @@ int init_conv_kernels_for_device() {
                                   cudaFuncAttributeMaxDynamicSharedMemorySize, adapt::kMaxSmemBytes));
     SETP(128, A_TILED) SETP(256, A_TILED) SETP(128, A_IM2COL) SETP(256, A_IM2COL)
 #undef SETP
+    CUDA_TRY(cudaFuncSetAttribute(adapt::stem_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, adapt::kMaxSmemBytes));
     CUDA_TRY(cudaFuncSetAttribute(adapt::conv_chain_kernel<64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   adapt::kMaxSmemBytes));
     CUDA_TRY(cudaFuncSetAttribute(adapt::conv_chain_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -771,6 +781,59 @@ int run_conv_launch(const ConvLaunch& L, cudaStream_t s) {
 
 // Chain eligibility: 3x3 / stride 1 / pad 1 with C in {64, 128} on a map the row-reuse walk pays for (W >= 28), followed by
 // a 1x1 to 4C channels with a shortcut.
+// Stem (space-to-depth form: 4x4 / stride 1 / VALID over 16-channel pixels stored in rows of 32 units, 64 output
+// channels, +BN +ReLU) followed by the 3x3 / stride 2 / zero-pad 1 max-pool, in one kernel.
+bool stem_pool_shape_ok(int H, int W, int Cin, int Ho, int Wo, int Cout) {
+    return Cin == 16 && Cout == 64 && W == 128 && Ho % 4 == 0 && Wo % 4 == 0 && Wo / 4 <= 32 && Ho >= 4 && Ho <= H - 3 && Wo <= W - 3;
+}
+
+int build_stem_pool_launch(StemPoolLaunch* L, int batch, int H, int W, int Ho, int Wo, const void* in, const void* w_bf16,
+                           const float* scale, const float* bias, void* out, int num_sms) {
+    if (!stem_pool_shape_ok(H, W, 16, Ho, Wo, 64)) return fail(ADAPT_EINVAL, "stem+pool: unsupported shape H=%d W=%d Ho=%d Wo=%d", H, W, Ho, Wo);
+    const long long units = (long long)batch * H * (W / 4);
+    if (batch <= 0 || units > 0x7fffffffLL) return fail(ADAPT_EINVAL, "stem+pool: bad batch %d", batch);
+    adapt::StemPoolParams& p = L->p;
+    memset(&p, 0, sizeof(p));
+    p.batch = batch;
+    p.H = H;
+    p.Ho = Ho;
+    p.Wo = Wo;
+    p.tiles_per_image = Ho / 4;
+    p.total_tiles = batch * p.tiles_per_image;
+    p.scale = scale;
+    p.bias = bias;
+    p.out = reinterpret_cast<__nv_bfloat16*>(out);
+    int stages = env_int("ADAPT_STEM_POOL_STAGES", adapt::kStemPoolMaxStages);
+    if (stages > adapt::kStemPoolMaxStages) stages = adapt::kStemPoolMaxStages;
+    while (stages > 2 && adapt::stem_pool_smem_bytes(stages) > adapt::kMaxSmemBytes) --stages;
+    if (stages < 2) stages = 2;
+    p.stages = stages;
+    L->smem = adapt::stem_pool_smem_bytes(stages);
+    L->grid = p.total_tiles < num_sms ? p.total_tiles : num_sms;
+    int rc = encode_tiled_2d_bf16(&L->tmap_b, w_bf16, 256, 64, adapt::kBlockK, 64);
+    if (rc) return rc;
+    return encode_tiled_2d_bf16(&L->tmap_a, in, adapt::kBlockK, (uint64_t)units, adapt::kBlockK, adapt::kRow3Rows);
+}
+
+int run_stem_pool_launch(const StemPoolLaunch& L, cudaStream_t s) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)L.grid);
+    cfg.blockDim = dim3((unsigned)adapt::kStemPoolThreads);
+    cfg.dynamicSmemBytes = (size_t)L.smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    unsigned n = 0;
+    if (pdl_enabled()) {
+        attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[n].val.programmaticStreamSerializationAllowed = 1;
+        ++n;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = n;
+    CUDA_TRY(cudaLaunchKernelEx(&cfg, adapt::stem_pool_kernel, L.tmap_a, L.tmap_b, L.p));
+    return ADAPT_OK;
+}
+
 bool chain_shape_ok(int C, int H, int W) { return (C == 64 || C == 128) && W >= 28 && H >= 1; }
 
 int build_chain_launch(ChainLaunch* L, int batch, int H, int W, int C, const void* in, const void* w2, const float* scale1,
@@ -876,6 +939,7 @@ struct Step {
     int kind = 0;
     ConvLaunch conv;  // bf16 CONV
     ChainLaunch chain;  // bf16 CONV_CHAIN
+    StemPoolLaunch stem_pool;  // bf16 STEM_POOL
     // generic pointers / geometry for the SIMT kernels
     const void* in = nullptr;
     const void* res = nullptr;
@@ -980,7 +1044,15 @@ int install_program(adapt_stage* st, const adapt_tensor_desc* tensors, int n_ten
                 !chain_shape_ok(o.Cin, o.H, o.W) || o.Ho != o.H || o.Wo != o.W)
                 return fail(ADAPT_EINVAL, "op %d: not a chainable 3x3 -> 1x1 block (C=%d H=%d W=%d Cout=%d)", i, o.Cin, o.H, o.W,
                             o.Cout);
-        } else if (o.kind < ADAPT_OP_INGEST || o.kind > ADAPT_OP_CONV_CHAIN) {
+        } else if (o.kind == ADAPT_OP_STEM_POOL) {
+            if (st->mode != ADAPT_MODE_BF16) return fail(ADAPT_EINVAL, "op %d: STEM_POOL exists in bf16 mode only", i);
+            if (o.weight < 0 || o.weight >= (int)st->weights.size()) return fail(ADAPT_EINVAL, "op %d: weight index out of range", i);
+            const WeightDev& w = st->weights[o.weight];
+            if (w.kh != 4 || w.kw != 4 || w.cin_store != 16 || w.cout != 64 || o.kh != 4 || o.kw != 4 || o.stride != 1 || o.pad != 0 ||
+                !o.relu || !stem_pool_shape_ok(o.H, o.W, o.Cin, o.Ho, o.Wo, o.Cout))
+                return fail(ADAPT_EINVAL, "op %d: not the space-to-depth stem followed by its 3x3/2 max-pool (H=%d W=%d Cin=%d Ho=%d Wo=%d)", i,
+                            o.H, o.W, o.Cin, o.Ho, o.Wo);
+        } else if (o.kind < ADAPT_OP_INGEST || o.kind > ADAPT_OP_STEM_POOL) {
             return fail(ADAPT_EINVAL, "op %d: unknown kind %d", i, o.kind);
         }
     }
@@ -1041,6 +1113,11 @@ int build_steps(adapt_stage* st, Plan* plan, int slot) {
             const WeightDev& w3 = st->weights[o.weight2];
             int rc = build_chain_launch(&s.chain, plan->batch, o.H, o.W, o.Cin, s.in, w2.kernel, w2.scale, w2.bias, w3.kernel,
                                         w3.scale, w3.bias, s.res, s.out, st->num_sms);
+            if (rc) return rc;
+        } else if (o.kind == ADAPT_OP_STEM_POOL) {
+            const WeightDev& w = st->weights[o.weight];
+            int rc = build_stem_pool_launch(&s.stem_pool, plan->batch, o.H, o.W, o.Ho, o.Wo, s.in, w.kernel, w.scale, w.bias, s.out,
+                                            st->num_sms);
             if (rc) return rc;
         }
         steps.push_back(s);
@@ -1112,6 +1189,11 @@ int run_steps(adapt_stage* st, const std::vector<Step>& steps, cudaStream_t stre
             }
             case ADAPT_OP_CONV_CHAIN: {
                 int rc = run_chain_launch(s.chain, stream);
+                if (rc) return rc;
+                break;
+            }
+            case ADAPT_OP_STEM_POOL: {
+                int rc = run_stem_pool_launch(s.stem_pool, stream);
                 if (rc) return rc;
                 break;
             }
@@ -1560,6 +1642,21 @@ int adapt_conv2d_bf16(int device, const void* in, const void* w, const float* sc
     }
     cudaFree(dtrace);
     return rc;
+}
+
+int adapt_stem_pool_bf16(int device, const void* in, const void* w, const float* scale, const float* bias, void* out, int batch,
+                         int H, int W, int Ho, int Wo, void* stream) {
+    if (!in || !w || !scale || !bias || !out) return fail(ADAPT_EINVAL, "stem_pool: null pointer");
+    int rc = require_device(device);
+    if (rc) return rc;
+    rc = init_conv_kernels_once(device);
+    if (rc) return rc;
+    int num_sms = 0;
+    CUDA_TRY(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, device));
+    StemPoolLaunch L;
+    rc = build_stem_pool_launch(&L, batch, H, W, Ho, Wo, in, w, scale, bias, out, num_sms);
+    if (rc) return rc;
+    return run_stem_pool_launch(L, reinterpret_cast<cudaStream_t>(stream));
 }
 
 int adapt_conv_chain_bf16(int device, const void* in, const void* w2, const float* scale1, const float* bias1,

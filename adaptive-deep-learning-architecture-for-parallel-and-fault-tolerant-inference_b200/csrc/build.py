@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB = os.path.join(HERE, "libadapt_b200.so")
 TRACE_LIB = os.path.join(HERE, "libadapt_b200_trace.so")  # developer build with the role timeline compiled in
 SOURCES = ["adapt_b200.cu"]
-HEADERS = ["conv_gemm_sm100.cuh", "conv_chain_sm100.cuh", "ptx_sm100.cuh", "simt_kernels.cuh", os.path.join("..", "..", "include", "adapt_b200.h")]
+HEADERS = ["conv_gemm_sm100.cuh", "conv_chain_sm100.cuh", "stem_pool_sm100.cuh", "ptx_sm100.cuh", "simt_kernels.cuh", os.path.join("..", "..", "include", "adapt_b200.h")]
 
 
 def _nvcc() -> str:

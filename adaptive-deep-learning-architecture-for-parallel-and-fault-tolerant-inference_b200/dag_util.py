@@ -333,6 +333,31 @@ def _chain_bottleneck_tails(ops: List["Op"], vt: List["VTensor"]) -> List["Op"]:
     return [repl.get(i, o) for i, o in enumerate(ops) if i not in drop]
 
 
+def _fuse_stem_pool(ops: List["Op"], vt: List["VTensor"]) -> List["Op"]:
+    """Fuse the space-to-depth stem convolution (conv1_conv+bn+relu as 4x4 / stride 1 over 16-channel pixels) with the
+    3x3 / stride 2 / pad 1 max-pool that is its only consumer into one STEM_POOL op (csrc/stem_pool_sm100.cuh): the
+    112 x 112 x 64 map stays on chip."""
+    uses: Dict[int, List[int]] = {}
+    for i, o in enumerate(ops):
+        for t in (o.inp, o.res):
+            if t >= 0:
+                uses.setdefault(t, []).append(i)
+    for i, a in enumerate(ops):
+        if not (a.kind == N.OP_CONV and a.kh == 4 and a.kw == 4 and a.stride == 1 and a.pad == 0 and a.Cin == 16 and a.Cout == 64
+                and a.relu == 1 and a.res < 0 and a.out_f32 == 0 and a.W == 128 and a.Ho % 4 == 0 and a.Wo % 4 == 0
+                and vt[a.out].role == N.T_INTERNAL and len(uses.get(a.out, [])) == 1):
+            continue
+        j = uses[a.out][0]
+        b = ops[j]
+        if not (b.kind == N.OP_MAXPOOL and b.kh == 3 and b.stride == 2 and b.pad == 1 and b.inp == a.out and b.Cin == 64
+                and (b.H, b.W) == (a.Ho, a.Wo) and (b.Ho, b.Wo) == (a.Ho // 2, a.Wo // 2) and j == i + 1):
+            continue
+        fused = Op(N.OP_STEM_POOL, a.inp, b.out, H=a.H, W=a.W, Cin=a.Cin, Ho=a.Ho, Wo=a.Wo, Cout=64, kh=4, kw=4, stride=1, pad=0,
+                   relu=1, weight=a.weight, layers=a.layers + b.layers)
+        return ops[:i] + [fused] + ops[j + 1:]
+    return ops
+
+
 def compile_part(part: PartModel, windex: Dict[str, int], mode: int = N.MODE_BF16,
                  input_format: int = N.IN_F32) -> StageProgram:
     """Fuse the Keras layers of `part` into stage ops and assign activation buffers.  `input_format` (N.IN_*) only
@@ -530,6 +555,8 @@ def compile_part(part: PartModel, windex: Dict[str, int], mode: int = N.MODE_BF1
     vt[t_out].role = N.T_OUTPUT
     if mode == N.MODE_BF16 and os.environ.get("ADAPT_CHAIN", "1") != "0":
         ops = _chain_bottleneck_tails(ops, vt)
+    if mode == N.MODE_BF16 and os.environ.get("ADAPT_STEM_POOL", "1") != "0":
+        ops = _fuse_stem_pool(ops, vt)
 
     # ---- liveness-based physical buffer assignment (internal tensors only)
     for i, o in enumerate(ops):

@@ -102,7 +102,7 @@ class StageExecutor:
         for op, t in zip(self.program.ops, ms):
             # algorithmic work = the Keras layer's own MAC count (not the padded / space-to-depth form it runs in)
             macs = 0
-            if op.kind in (N.OP_CONV, N.OP_CONV_CHAIN):
+            if op.kind in (N.OP_CONV, N.OP_CONV_CHAIN, N.OP_STEM_POOL):
                 macs = batch * sum(layer_macs(self.model, self.model.get_layer(n)) for n in op.layers
                                    if n in self.model._by_name)
             out.append({"layers": op.layers, "kind": op.kind, "ms": float(t), "macs": int(macs),

@@ -52,6 +52,12 @@ extern "C" {
                             /* _2_relu tensor never reaches HBM.  C in {64, 128}, map width >= 28.               */
                             /* weight = the 3x3's entry, weight2 = the 1x1's; Cin = C, Cout = 4C                  */
 
+#define ADAPT_OP_STEM_POOL 8 /* bf16 mode: conv1_conv+bn+relu in its space-to-depth form (4x4 / stride 1 / VALID over   */
+                            /* 16-channel pixels stored 128 wide, 64 output channels) fused with pool1_pad +        */
+                            /* pool1_pool (3x3 / stride 2 / zero pad 1): the 112x112x64 map never reaches HBM.     */
+                            /* H, W, Cin = stored input; Ho, Wo = the CONVOLUTION's output size (the op's output    */
+                            /* tensor is (Ho/2, Wo/2, 64)); kh = kw = 4, stride 1, pad 0, relu 1                    */
+
 /* tensor roles inside a stage program */
 #define ADAPT_T_INTERNAL 0  /* library-owned scratch activation                       */
 #define ADAPT_T_INPUT 1     /* stage input, caller-owned, bound per slot (bind_io)    */
@@ -190,6 +196,15 @@ int adapt_conv2d_bf16(int device, const void* in, const void* w, const float* sc
 int adapt_conv_chain_bf16(int device, const void* in, const void* w2, const float* scale1, const float* bias1,
                           const void* w3, const float* scale2, const float* bias2, const void* residual, void* out,
                           int batch, int H, int W, int C, void* stream);
+
+/* Single-op entry point of ADAPT_OP_STEM_POOL (kernel-level parity tests and micro-benchmarks), DEVICE pointers:
+ *   y   = relu(conv4x4_valid(in, w) * scale + bias)     (never stored)
+ *   out = maxpool3x3_stride2(zero_pad1(y))
+ *   in : bf16 [batch][H][W = 128][16] (the ingest kernel's space-to-depth image)   w : bf16 [64][4][4][16]
+ *   out: bf16 NHWC [batch][Ho/2][Wo/2][64];  Ho, Wo = size of y (multiples of 4, Wo <= 128, Ho <= H - 3).
+ * Stands in for the layers conv1_conv ... pool1_pool inside `model.predict` (reference src/node.py:177). */
+int adapt_stem_pool_bf16(int device, const void* in, const void* w, const float* scale, const float* bias, void* out, int batch,
+                         int H, int W, int Ho, int Wo, void* stream);
 
 /* Classifier head (Dense + softmax) for callers that must not allocate device memory.
  * This entry point has NO counterpart in the reference; it exists for users of this library whose

@@ -72,7 +72,7 @@ def test_reference_driver_shape(pkg, model50):
     _check(model50, [], [x], outs[:1], oracle_tol="absolute")
     for o in outs[1:]:
         np.testing.assert_array_equal(o, outs[0])
-    assert launches == 10 * 51          # 58 fused groups, 7 bottleneck tails chained (3x3 -> 1x1) into one launch each
+    assert launches == 10 * 50          # 58 fused groups; 7 bottleneck tails chained (3x3 -> 1x1), stem + max-pool fused: one launch each
 
 
 @pytest.mark.parametrize("part_at", [["conv3_block4_out"], ["conv2_block3_out", "conv3_block4_out", "conv4_block6_out"]])

@@ -183,6 +183,28 @@ def test_chained_and_unchained_programs_agree(model50, monkeypatch):
     assert rel_err(outs["1"][1], outs["0"][1]) <= 1e-3
 
 
+@pytest.mark.parametrize("batch,kind", [(1, "caffe"), (3, "normal"), (37, "caffe"), (128, "caffe")])
+def test_fused_stem_pool_is_bit_identical_to_conv_then_pool(model50, monkeypatch, batch, kind):
+    """`stem_pool_kernel` (conv1_conv .. pool1_pool in one launch, default) against the stem convolution and the max-pool
+    as two launches (ADAPT_STEM_POOL=0): max commutes with ReLU and with rounding to bf16, so `pool1_pool` must agree bit
+    for bit -- for one image, for ranges of tiles that start inside an image (37 images over 148 CTAs: 7 tiles per CTA,
+    every range but the first few needs the row handed over from the tile before it) and for the bench's batch."""
+    from adapt_b200 import _native as N
+
+    x = KO.synthetic_images(batch, seed=5, kind=kind)
+    outs = {}
+    for fused in ("1", "0"):
+        monkeypatch.setenv("ADAPT_STEM_POOL", fused)
+        p = _predictor(model50, mode="bf16", max_batch=batch, end="pool1_pool")
+        kinds = [o.kind for o in p.ex.program.ops]
+        assert (N.OP_STEM_POOL in kinds) == (fused == "1") and (N.OP_MAXPOOL in kinds) == (fused == "0")
+        outs[fused] = p.run(x)
+        p.close()
+    assert outs["1"].shape == (batch, 56, 56, 64)
+    assert np.array_equal(outs["1"], outs["0"])
+    assert float(outs["1"].max()) > 0.0
+
+
 # ------------------------------------------------------------------ whole network
 @pytest.mark.parametrize("kind,batch", [("caffe", 4), ("normal", 3), ("normal", 1)])
 def test_full_model_bf16(model50, oracle, kind, batch):
