@@ -64,15 +64,15 @@ def block_boundaries(model) -> List[str]:
 # Add fused into it).  The chained `_2_conv` -> `_3_conv` kernel of conv2 / conv3 is split 1/3 : 2/3 between its layers
 # (cuts never separate them).  Layers of other shapes fall back to the roofline formula below.
 MEASURED_US_B128 = {
-    (7, 2, 230, 3, 64, False): 79.7,
-    (1, 1, 56, 64, 64, False): 22.8, (3, 1, 56, 64, 64, False): 31.0, (1, 1, 56, 64, 256, False): 55.5,
-    (1, 1, 56, 64, 256, True): 62.0, (1, 1, 56, 256, 64, False): 49.0,
-    (1, 2, 56, 256, 128, False): 22.4, (1, 2, 56, 256, 512, False): 43.6, (3, 1, 28, 128, 128, False): 21.0,
-    (1, 1, 28, 128, 512, True): 41.0, (1, 1, 28, 512, 128, False): 33.0,
-    (1, 2, 28, 512, 256, False): 18.4, (1, 2, 28, 512, 1024, False): 30.9, (3, 1, 14, 256, 256, False): 30.7,
-    (1, 1, 14, 256, 1024, True): 31.0, (1, 1, 14, 1024, 256, False): 24.7,
-    (1, 2, 14, 1024, 512, False): 18.6, (1, 2, 14, 1024, 2048, False): 29.0, (3, 1, 7, 512, 512, False): 36.6,
-    (1, 1, 7, 512, 2048, True): 24.5, (1, 1, 7, 2048, 512, False): 22.8,
+    (7, 2, 230, 3, 64, False): 73.6,   # conv1_conv .. pool1_pool: the fused stem + max-pool kernel
+    (1, 1, 56, 64, 64, False): 21.9, (3, 1, 56, 64, 64, False): 30.0, (1, 1, 56, 64, 256, False): 55.7,
+    (1, 1, 56, 64, 256, True): 59.5, (1, 1, 56, 256, 64, False): 48.7,
+    (1, 2, 56, 256, 128, False): 22.5, (1, 2, 56, 256, 512, False): 45.5, (3, 1, 28, 128, 128, False): 21.0,
+    (1, 1, 28, 128, 512, True): 41.8, (1, 1, 28, 512, 128, False): 33.8,
+    (1, 2, 28, 512, 256, False): 19.7, (1, 2, 28, 512, 1024, False): 31.3, (3, 1, 14, 256, 256, False): 31.6,
+    (1, 1, 14, 256, 1024, True): 30.6, (1, 1, 14, 1024, 256, False): 25.2,
+    (1, 2, 14, 1024, 512, False): 19.7, (1, 2, 14, 1024, 2048, False): 29.3, (3, 1, 7, 512, 512, False): 37.0,
+    (1, 1, 7, 512, 2048, True): 24.8, (1, 1, 7, 2048, 512, False): 23.2,
 }
 IN_GRAPH_OVERLAP = 0.85   # consecutive launches overlap inside the stage's CUDA graph (programmatic dependent launch)
 MIN_LAUNCH_US = 6.0       # what a launch costs however small the batch
@@ -102,7 +102,7 @@ def estimate_layer_seconds(model, l, batch: int = 128) -> float:
         rate = 400e12 if (k == 3 and l.output_shape[-1] <= 64) else (650e12 if k == 3 else 700e12)
         return max(2.0 * macs / rate, byts / 5.0e12) + 4e-6
     if l.class_name == "MaxPooling2D":
-        return 2.0 * batch * float(np.prod(model.get_layer(l.inbound_names[0]).output_shape[1:])) / 2.95e12
+        return 0.0   # fused into the stem kernel (cut candidates never separate conv1_relu from pool1_pool)
     if l.class_name == "InputLayer":
         return 0.24e-6 * batch  # ingest
     if l.class_name == "GlobalAveragePooling2D":
