@@ -30,19 +30,19 @@ out.append(f"{len(step)} launches per step, {tot / 1e3:.1f} us summed device tim
 out.append("| kernel | launches | us | share |\n|---|---:|---:|---:|")
 for n, v in agg.most_common():
     out.append(f"| `{n}` | {cnt[n]} | {v / 1e3:.1f} | {100 * v / tot:.1f}% |")
-conv = sum(v for n, v in agg.items() if "conv_gemm" in n or "conv_chain" in n)
-out.append(f"\n`conv_gemm_kernel` + `conv_chain_kernel` (all instantiations): **{100 * conv / tot:.1f}%** of the step.\n")
+conv = sum(v for n, v in agg.items() if "conv_gemm" in n or "conv_chain" in n or "stem_pool" in n)
+out.append(f"\n`conv_gemm_kernel` + `conv_chain_kernel` + `stem_pool_kernel` (all instantiations): **{100 * conv / tot:.1f}%** of the step.\n")
 shutil.copy(launches_csv, f"profiles/{tag}_launches.csv")
 
 # ---- ncu --set full capture of conv_gemm launches inside the same command
 rows = list(csv.reader(open(full_csv)))
 hdr, units, data = rows[0], rows[1], rows[2:]
 col = {h: i for i, h in enumerate(hdr)}
-out.append(f"## `ncu --set full` capture of the conv_gemm_kernel / conv_chain_kernel launches of one step (`{full_csv}`)\n")
+out.append(f"## `ncu --set full` capture of the conv_gemm_kernel / conv_chain_kernel / stem_pool_kernel launches of one step (`{full_csv}`)\n")
 out.append("| # | instantiation | grid | regs | us | DRAM read MB | DRAM write MB | DRAM % of peak | tensor pipe % |\n"
            "|---|---|---:|---:|---:|---:|---:|---:|---:|")
 for r in data:
-    inst = re.search(r"conv_(?:gemm|chain)_kernel<[^>]*>", r[col["Kernel Name"]]).group(0)
+    inst = re.search(r"conv_(?:gemm|chain)_kernel<[^>]*>|stem_pool_kernel", r[col["Kernel Name"]]).group(0)
     out.append(f"| {r[col['ID']]} | `{inst}` | {r[col['launch__grid_size']]} | {r[col['launch__registers_per_thread']]} | "
                f"{float(r[col['gpu__time_duration.sum']]):.1f} | {float(r[col['dram__bytes_read.sum']]):.1f} | "
                f"{float(r[col['dram__bytes_write.sum']]):.1f} | "
@@ -58,7 +58,7 @@ for o in ops["ops"]:
     tf = 2 * o["macs"] / o["ms"] / 1e9 if o["macs"] else 0
     out.append(f"| {o['layers'][0]} .. {o['layers'][-1]} | {o['shape']} | {o['ms']:.4f} | {tf:.1f} |")
 tot_ms = sum(o["ms"] for o in ops["ops"])
-conv_ms = sum(o["ms"] for o in ops["ops"] if o["kind"] in (1, 7))
+conv_ms = sum(o["ms"] for o in ops["ops"] if o["kind"] in (1, 7, 8))
 flop = 2 * sum(o["macs"] for o in ops["ops"])
 out.append(f"\nsum {tot_ms:.3f} ms (isolated launches: no overlap between consecutive layers); conv kernels {conv_ms:.3f} ms = "
            f"{100 * conv_ms / tot_ms:.1f}% -> {flop / conv_ms / 1e9:.1f} TFLOP/s algorithmic over the conv launches.  Inside "
