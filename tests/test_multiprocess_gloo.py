@@ -55,7 +55,7 @@ def _worker(rank, world, port, q):
         # third session: the dispatcher-local FIRST stage is lost.  The surviving stage lives in the other process and
         # cannot read this process's host inputs: the dispatcher copies them into that stage's slot itself (KIND_FED)
         inputs = [KO.synthetic_images(1, seed=930 + i, kind="normal") for i in range(7)]
-        defer = DEFER(["10.0.0.1", "10.0.0.2"], mode="fp32", max_batch=1, backend_factory=SharedHostBackend, heartbeat_timeout=0.5)
+        defer = DEFER(["10.0.0.1", "10.0.0.2"], mode="fp32", max_batch=1, backend_factory=SharedHostBackend, heartbeat_timeout=2.0)
         in_q, out_q = queue.Queue(), queue.Queue()
         t = threading.Thread(target=defer.run_defer, args=(model, ["conv3_block4_out"], in_q, out_q), daemon=True)
         t.start()
