@@ -240,6 +240,7 @@ class DEFER:
         self.models_to_dispatch: List[PartModel] = []
         self.part_at: List[str] = []
         self.handoff_gbs: List[Optional[float]] = []   # per cut, filled by collect_timing
+        self.stage_busy_ms: List[float] = []           # per stage, filled by collect_timing
         self.stats = {"delivered": 0, "replayed": 0, "failovers": 0, "failover_ms": [], "dropped_stale": 0, "rejoins": 0,
                       "stragglers": 0}
         self.latencies_ms: List[float] = []
@@ -685,6 +686,9 @@ class DEFER:
         # copy-engine hand-offs of the window's last micro-batch, one entry per cut (None: stored by the last kernel)
         self.handoff_gbs = [round(int(self.health.w[w, W_XFER_BYTES]) / int(self.health.w[w, W_XFER_NS]), 1)
                             if int(self.health.w[w, W_XFER_NS]) > 0 else None for w in self.order[:-1]]
+        # moving average of the device time each stage's program takes per micro-batch (events around the graph launch
+        # alone: no flag waits, no hand-off) -- the stage's own speed, next to the pipeline's step time
+        self.stage_busy_ms = [int(self.health.w[w, W_BUSY_US]) / 1000.0 for w in self.order]
         return [int(self.health.w[w, W_ELAPSED_US]) / 1000.0 for w in self.order]
 
     @property

@@ -145,6 +145,8 @@ def part_at_for(model, n: int, cuts: str = "balanced"):
 
     if n == 1:
         return []
+    if os.environ.get("ADAPT_BENCH_PART_AT"):      # developer override: comma-separated layer names
+        return os.environ["ADAPT_BENCH_PART_AT"].split(",")
     if cuts == "config" and n in CONFIG_PART_AT:
         return CONFIG_PART_AT[n]
     return balanced_part_at(model, n)
@@ -457,6 +459,7 @@ def run_ours(args) -> int:
     launches0 = defer.gpu_launches
     outs, stage_ms, wall_resident = main.resident_window(K)
     handoff_gbs = list(defer.handoff_gbs)
+    stage_busy_ms = [round(v, 4) for v in defer.stage_busy_ms]
     torch.cuda.synchronize()
     local_launches = defer.gpu_launches - launches0
     ms_total = max(stage_ms)
@@ -633,6 +636,8 @@ def run_ours(args) -> int:
                          "126 MB L2; input slots alternate", "handoff": "peer stores / copy engines over NVLink + stream memory ops",
                    "stage_ms_per_step": [round(m / K, 4) for m in stage_ms], "how": "CUDA events per stage stream, max over stages",
                    "untimed_before_window": f"{n_ramp} clock-ramp steps + {W} warm-up steps",
+                   "stage_busy_ms": stage_busy_ms,
+                   "stage_busy_how": "moving average of CUDA-event time around each stage's graph launch alone (no waits, no hand-off)",
                    "handoff_gbs": handoff_gbs,
                    "handoff_gbs_how": "per cut: bytes / CUDA-event time of the copy-engine hand-off of the window's last "
                                       "micro-batch (waits excluded); null = the last kernel stores straight into the peer's slot"},

@@ -7,5 +7,5 @@ echo "rc=$?"
 python - <<PY
 import json
 d=json.loads(open("gpurun_out/bench_n$N.json").read().strip().splitlines()[-1])
-print(d["value"], d["ms_per_step"], d["e2e"]["value"], d["config"]["part_at"], d["timing"]["stage_ms_per_step"], d["checks"]["mismatched_micro_batches"], d.get("failover"))
+print(d["value"], d["ms_per_step"], d["e2e"]["value"], d["config"]["part_at"], d["timing"]["stage_ms_per_step"], d["timing"]["stage_busy_ms"], d["checks"]["mismatched_micro_batches"], d.get("failover"))
 PY
