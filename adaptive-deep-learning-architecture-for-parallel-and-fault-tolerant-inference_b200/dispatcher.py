@@ -74,7 +74,15 @@ MEASURED_US_B128 = {
     (1, 2, 14, 1024, 512, False): 19.7, (1, 2, 14, 1024, 2048, False): 29.3, (3, 1, 7, 512, 512, False): 37.0,
     (1, 1, 7, 512, 2048, True): 24.8, (1, 1, 7, 2048, 512, False): 23.2,
 }
-IN_GRAPH_OVERLAP = 0.85   # consecutive launches overlap inside the stage's CUDA graph (programmatic dependent launch)
+# Consecutive launches overlap inside the stage's CUDA graph (programmatic dependent launch); how much depends on the
+# level: measured from the per-stage busy times of 2-stage runs with the cut at conv3_block2/3/4_out (bench.py,
+# `timing.stage_busy_ms`): stem + conv2 run at 0.88 of their isolated sum, the conv3 level at 1.0 (CTA-pair launches
+# start only when both SMs of a pair are free), conv4 / conv5 / head at 0.75.
+def in_graph_overlap(out_rows: int) -> float:
+    return 0.88 if out_rows >= 56 else (1.0 if out_rows >= 28 else 0.75)
+
+
+IN_GRAPH_OVERLAP = 0.85   # (shapes outside the measured table)
 MIN_LAUNCH_US = 6.0       # what a launch costs however small the batch
 
 
@@ -94,10 +102,10 @@ def estimate_layer_seconds(model, l, batch: int = 128) -> float:
         bn = cons[0] if len(cons) == 1 and cons[0].class_name == "BatchNormalization" else None
         fused_add = bn is not None and any(c.class_name == "Add" for c in model.layers if bn.name in c.inbound_names)
         if l.class_name == "Dense":
-            return max(34.1e-6 * batch / 128, 2 * MIN_LAUNCH_US * 1e-6) * IN_GRAPH_OVERLAP   # Dense + softmax launches
+            return max(34.1e-6 * batch / 128, 2 * MIN_LAUNCH_US * 1e-6) * in_graph_overlap(1)   # Dense + softmax launches
         key = (k, stride, int(src.output_shape[1]), int(src.output_shape[-1]), int(l.output_shape[-1]), bool(fused_add))
         if key in MEASURED_US_B128:
-            return max(MEASURED_US_B128[key] * batch / 128, MIN_LAUNCH_US) * 1e-6 * IN_GRAPH_OVERLAP
+            return max(MEASURED_US_B128[key] * batch / 128, MIN_LAUNCH_US) * 1e-6 * in_graph_overlap(int(l.output_shape[1]))
         byts = 2.0 * batch * (in_elems + out_elems * (2 if fused_add else 1))
         rate = 400e12 if (k == 3 and l.output_shape[-1] <= 64) else (650e12 if k == 3 else 700e12)
         return max(2.0 * macs / rate, byts / 5.0e12) + 4e-6
