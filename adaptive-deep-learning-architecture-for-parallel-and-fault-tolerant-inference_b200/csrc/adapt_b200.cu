@@ -511,6 +511,11 @@ int build_conv_launch(ConvLaunch* L, const ConvGeom& g, const void* in, const vo
     const bool pair_ok = a_mode != adapt::A_GATHER && !out_f32 && env_int("ADAPT_EPI_MODE", 1) != 0 && p.m_tiles >= 2 &&
                          (pair_env == 2 || (pair_env == 1 && (!memory_bound || (residual != nullptr && K >= 256))));
     if (bn == 0) bn = memory_bound ? (g.Cout >= 128 ? 128 : 64) : pick_block_n(p.m_tiles, g.Cout, num_sms, pair_ok);
+    // a layer of a handful of tiles (the Dense layer: 1 x 8; the deep layers at micro-batch 1) is paced by how fast ONE
+    // SM ingests its operand stream: narrower tiles put twice as many SMs on it
+    if (block_n_req <= 0 && g_force_block_n <= 0 && bn == 128 && memory_bound &&
+        (long long)p.m_tiles * ((g.Cout + 127) / 128) < num_sms / 4)
+        bn = 64;
     if (row3) {
         // a row-reuse stage holds three B tiles: 128-wide tiles on CTA pairs (8 KiB per tile and CTA), or
         // 64-wide tiles on single CTAs
