@@ -38,6 +38,7 @@ from .fabric import (G_EPOCH, G_PHASE, G_T0, G_T1, G_TIMING_REQ, KIND_DATA, KIND
 # blocked stream without having to get a copy scheduled behind it.
 F_IN_READY, F_OUT_FREE, F_H2D_DONE, F_IN_CONSUMED, F_OUT_READY, F_OUT_COPIED = 0, 2, 4, 6, 8, 10
 F_XFER_PART = 12   # + 2 * j + slot: piece j (1..XFER_STREAMS-1) of a split hand-off copy has landed
+BUSY_SAMPLE_EVERY = int(os.environ.get("ADAPT_BUSY_SAMPLE_EVERY", "4"))   # micro-batches per busy-time sample (2 event records)
 XFER_STREAMS = 1   # copy streams a large hand-off may be split over.  Measured on B200 (tools/handoff_bench.py, 205 MB
 #                    GPU 0 -> GPU 1): ONE copy reaches 737 GB/s, split in 2 / 4 / 8 concurrent pieces 693 / 602 / 488 GB/s
 #                    -- several copy engines on one link get in each other's way -- so the default is a single copy;
@@ -119,6 +120,7 @@ class StageWorker:
         self._stop = threading.Event()
         self._hb_thread: Optional[threading.Thread] = None
         self.launches = 0
+        self._busy_seen = 0
         self._timing_events = None
         self._xfer_events = None
         self._xfer_timed_bytes = 0
@@ -483,6 +485,11 @@ class StageWorker:
         if not hasattr(b, "event_done"):
             return None
         self._busy_poll()
+        # one micro-batch in BUSY_SAMPLE_EVERY carries the two event records (every one at the start of an epoch, so
+        # that the stage's baseline exists at once): the watchdog looks at a moving average over 0.5 s anyway
+        self._busy_seen += 1
+        if self._busy_seen > 8 and self._busy_seen % BUSY_SAMPLE_EVERY:
+            return None
         if self._busy_events:
             pair = self._busy_events.pop()
         elif len(self._busy_pending) < 16:
@@ -519,6 +526,7 @@ class StageWorker:
         self._busy_events += self._busy_pending  # (streams are drained when this runs)
         self._busy_pending = []
         self._busy_ewma, self._busy_n, self._busy_min = 0.0, 0, 0.0
+        self._busy_seen = 0
         self.health.w[self.wid, W_BUSY_US] = 0
         self.health.w[self.wid, W_BUSY_MIN_US] = 0
         self.health.w[self.wid, W_BUSY_N] = 0
