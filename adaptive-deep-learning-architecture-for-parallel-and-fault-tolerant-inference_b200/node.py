@@ -475,6 +475,17 @@ class StageWorker:
             ctypes.memmove(self.stage_addr[s], host_addr, nbytes)
             src = self.stage_addr[s]
         if k >= 2:
+            if hasattr(b, "abort_check"):
+                # synchronous (test) backend: its waits give up when THIS worker is killed -- which it is, that is why the
+                # dispatcher feeds on its behalf -- so the slot's previous micro-batch is waited for here, on the host
+                fl = self.flags_host[target_wid]
+                t0 = time.monotonic()
+                while ((int(fl[F_IN_CONSUMED + s]) - v_prev) & 0xFFFFFFFF) >= 0x80000000:
+                    if self.health.phase != PHASE_RUN or self._stop.is_set():
+                        return
+                    if time.monotonic() - t0 > 30:
+                        raise TimeoutError("first stage never consumed its input slot")
+                    time.sleep(20e-6)
             b.wait_flag(self.copy_stream, self.flag(target_wid, F_IN_CONSUMED + s), v_prev)
         b.h2d(self.in_buf(target_wid, s), src, nbytes, self.copy_stream)
         b.write_flag(self.copy_stream, self.flag(target_wid, F_H2D_DONE + s), v_done)
