@@ -510,3 +510,37 @@ def test_uint8_input_format(pkg, model50):
     o = oracle_for(model50)
     for x, y in zip(imgs, outs):
         np.testing.assert_allclose(y, o.predict(preprocess_input(x))[0], rtol=1e-5, atol=1e-7)
+
+
+def test_fused_ops_in_the_stage_program(pkg, model50, monkeypatch):
+    """What the bf16 stage program of the whole network looks like (host logic, no GPU): 58 fused layer groups, of which
+    the seven conv2 / conv3 bottleneck tails run as one CONV_CHAIN each and conv1_conv .. pool1_pool as one STEM_POOL;
+    a cut between the stem's convolution and its pool, the check mode and the switches leave the ops apart."""
+    from adapt_b200._native import MODE_BF16, OP_CONV, OP_CONV_CHAIN, OP_MAXPOOL, OP_STEM_POOL
+    from adapt_b200.dag_util import build_weight_table, compile_part, construct_model
+
+    _, windex = build_weight_table(model50)
+    first, last = model50.layers[0].name, model50.layers[-1].name
+    whole = construct_model(model50, first, last, "all")
+    ops = compile_part(whole, windex, MODE_BF16).ops
+    kinds = [o.kind for o in ops]
+    assert len(ops) == 50 and kinds.count(OP_CONV_CHAIN) == 7 and kinds.count(OP_STEM_POOL) == 1 and OP_MAXPOOL not in kinds
+    stem = ops[kinds.index(OP_STEM_POOL)]
+    assert stem.layers[0] == "conv1_conv" and stem.layers[-1] == "pool1_pool"
+    assert (stem.H, stem.W, stem.Cin, stem.Ho, stem.Wo, stem.Cout, stem.kh, stem.stride) == (115, 128, 16, 112, 112, 64, 4, 1)
+    # every layer is covered exactly once
+    covered = [n for o in ops for n in o.layers if not n.endswith(":softmax")]
+    assert len(covered) == len(set(covered)) and {"conv1_bn", "pool1_pad", "conv2_block1_2_conv", "conv2_block1_out"} <= set(covered)
+    # fp32 check mode: no fused kernels
+    kinds32 = [o.kind for o in compile_part(whole, windex, 1).ops]
+    assert OP_STEM_POOL not in kinds32 and OP_CONV_CHAIN not in kinds32 and OP_MAXPOOL in kinds32
+    # a cut at conv1_relu separates the convolution from its pool
+    head = construct_model(model50, first, "conv1_relu", "p1")
+    tail = construct_model(model50, "conv1_relu", "pool1_pool", "p2")
+    assert OP_STEM_POOL not in [o.kind for o in compile_part(head, windex, MODE_BF16).ops]
+    assert [o.kind for o in compile_part(tail, windex, MODE_BF16).ops] == [OP_MAXPOOL]
+    # the switches
+    monkeypatch.setenv("ADAPT_STEM_POOL", "0")
+    monkeypatch.setenv("ADAPT_CHAIN", "0")
+    kinds0 = [o.kind for o in compile_part(whole, windex, MODE_BF16).ops]
+    assert len(kinds0) == 58 and OP_STEM_POOL not in kinds0 and OP_CONV_CHAIN not in kinds0 and kinds0.count(OP_CONV) == 54
