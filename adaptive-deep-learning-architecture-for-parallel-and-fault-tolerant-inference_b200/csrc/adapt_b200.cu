@@ -715,6 +715,28 @@ bool pdl_enabled() {
     return v != 0;
 }
 
+// A SIMT kernel of the stage program launched like the convolution kernels: with the programmatic-serialization
+// attribute, so that its launch overlaps the tail of the kernel before it (the kernel waits with griddepcontrol).
+template <typename... KArgs, typename... Args>
+cudaError_t launch_simt_pdl(void (*kernel)(KArgs...), unsigned grid, unsigned block, cudaStream_t s, Args... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(block);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    unsigned n = 0;
+    static const int simt_pdl = env_int("ADAPT_PDL_SIMT", 1);
+    if (pdl_enabled() && simt_pdl) {
+        attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[n].val.programmaticStreamSerializationAllowed = 1;
+        ++n;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = n;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 template <int BN, int MODE, int CL, bool PAIR>
 cudaError_t launch_conv_ex(const ConvLaunch& L, cudaStream_t s) {
     cudaLaunchConfig_t cfg{};
@@ -1151,11 +1173,11 @@ int run_steps(adapt_stage* st, const std::vector<Step>& steps, cudaStream_t stre
                     const unsigned blocks = (unsigned)((outs + threads - 1) / threads);
                     __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(s.out);
                     if (u8)
-                        adapt::ingest_s2d_kernel<adapt::SrcU8Caffe><<<blocks, threads, 0, stream>>>(
-                            reinterpret_cast<const uint8_t*>(s.in), dst, B, o.H, o.W, o.Ho, o.Wo, o.pad);
+                        CUDA_TRY(launch_simt_pdl(adapt::ingest_s2d_kernel<adapt::SrcU8Caffe>, blocks, threads, stream,
+                                                 reinterpret_cast<const uint8_t*>(s.in), dst, B, o.H, o.W, o.Ho, o.Wo, o.pad));
                     else
-                        adapt::ingest_s2d_kernel<adapt::SrcF32><<<blocks, threads, 0, stream>>>(
-                            reinterpret_cast<const float*>(s.in), dst, B, o.H, o.W, o.Ho, o.Wo, o.pad);
+                        CUDA_TRY(launch_simt_pdl(adapt::ingest_s2d_kernel<adapt::SrcF32>, blocks, threads, stream,
+                                                 reinterpret_cast<const float*>(s.in), dst, B, o.H, o.W, o.Ho, o.Wo, o.pad));
                 } else if (st->mode == ADAPT_MODE_BF16) {
                     if (o.Cout != 8 || o.Cin > 8) return fail(ADAPT_EINVAL, "ingest: expects Cin<=8 -> 8 channels");
                     const unsigned blocks = (unsigned)((pixels + threads - 1) / threads);
@@ -1227,9 +1249,9 @@ int run_steps(adapt_stage* st, const std::vector<Step>& steps, cudaStream_t stre
                 const int threads = 128;
                 const unsigned blocks = (unsigned)((total + threads - 1) / threads);
                 if (st->mode == ADAPT_MODE_BF16)
-                    adapt::global_avgpool_bf16_kernel<<<(unsigned)((total + 63) / 64), 64, 0, stream>>>(
-                        reinterpret_cast<const __nv_bfloat16*>(s.in), reinterpret_cast<__nv_bfloat16*>(s.out), B, o.H * o.W,
-                        o.Cin);
+                    CUDA_TRY(launch_simt_pdl(adapt::global_avgpool_bf16_kernel, (unsigned)((total + 63) / 64), 64u, stream,
+                                             reinterpret_cast<const __nv_bfloat16*>(s.in), reinterpret_cast<__nv_bfloat16*>(s.out), B,
+                                             o.H * o.W, o.Cin));
                 else
                     adapt::global_avgpool_kernel<float, float><<<blocks, threads, 0, stream>>>(
                         reinterpret_cast<const float*>(s.in), reinterpret_cast<float*>(s.out), B, o.H * o.W, o.Cin);
@@ -1238,8 +1260,8 @@ int run_steps(adapt_stage* st, const std::vector<Step>& steps, cudaStream_t stre
             case ADAPT_OP_SOFTMAX: {
                 const int warps_per_block = 4;
                 const unsigned blocks = (unsigned)((B + warps_per_block - 1) / warps_per_block);
-                adapt::softmax_rows_kernel<<<blocks, warps_per_block * 32, 0, stream>>>(
-                    reinterpret_cast<const float*>(s.in), reinterpret_cast<float*>(s.out), B, o.Cin);
+                CUDA_TRY(launch_simt_pdl(adapt::softmax_rows_kernel, blocks, (unsigned)(warps_per_block * 32), stream,
+                                         reinterpret_cast<const float*>(s.in), reinterpret_cast<float*>(s.out), B, o.Cin));
                 break;
             }
             case ADAPT_OP_AFFINE: {

@@ -11,6 +11,14 @@
 
 namespace adapt {
 
+// Programmatic dependent launch (same protocol as the convolution kernels): let the next kernel of the stage start its
+// prologue now, then wait until the previous kernel has completed and its writes are visible.  Both are no-ops when
+// the kernel was launched without the programmatic-serialization attribute.
+__device__ __forceinline__ void simt_pdl_prologue() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 // ---------------------------------------------------------------------------------------------
 // Image sources of the ingest kernels.  SrcF32: the reference's queue contract, an already preprocessed fp32
 // image.  SrcU8Caffe: a raw uint8 RGB image with Keras' caffe-mode `preprocess_input` (RGB -> BGR, minus the
@@ -65,6 +73,7 @@ __global__ void ingest_u8_to_f32_kernel(const uint8_t* __restrict__ in, float* _
 template <typename Src>
 __global__ void ingest_s2d_kernel(const typename Src::T* __restrict__ in, __nv_bfloat16* __restrict__ out, int B, int H,
                                   int W, int Hs, int Ws, int pad) {
+    simt_pdl_prologue();
     const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
     const long long total = static_cast<long long>(B) * Hs * Ws;
     if (i >= total) return;
@@ -403,6 +412,7 @@ __global__ void global_avgpool_kernel(const TIn* __restrict__ in, TOut* __restri
 // seven with independent accumulators, so that seven 16-byte loads are in flight per thread (HW = 49 for ResNet).
 __global__ void global_avgpool_bf16_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, int B, int HW,
                                            int C) {
+    simt_pdl_prologue();
     const int cvecs = C / 8;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= B * cvecs) return;
@@ -469,6 +479,7 @@ __device__ __forceinline__ float warp_sum(float v) {
 }
 
 __global__ void softmax_rows_kernel(const float* __restrict__ logits, float* __restrict__ probs, int B, int N) {
+    simt_pdl_prologue();
     const int row = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
     const int lane = threadIdx.x % 32;
     if (row >= B) return;
